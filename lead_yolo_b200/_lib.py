@@ -1,0 +1,69 @@
+"""ctypes binding of libleadyolo.so (the C-ABI declared in include/leadyolo.h).
+
+The library handle is a process-global loaded lazily; nothing CUDA-related is stored on nn.Module
+instances, so models stay picklable / deep-copyable (reference: utils/torch_utils.py:412, train.py:390-399).
+There is no fallback: if the shared library is missing, every op raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = _PKG / "libleadyolo.so"
+_lib = None
+
+
+class LeadYoloError(RuntimeError):
+    pass
+
+
+class ConvDesc(C.Structure):
+    _fields_ = [
+        ("n_src", C.c_int),
+        ("src", C.c_void_p * 4),
+        ("src_c", C.c_int * 4),
+        ("src_ld", C.c_long * 4),
+        ("N", C.c_int), ("H", C.c_int), ("W", C.c_int),
+        ("kh", C.c_int), ("kw", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
+        ("Cout", C.c_int),
+        ("w_packed", C.c_void_p),
+        ("scale", C.c_void_p),
+        ("shift", C.c_void_p),
+        ("act", C.c_int),
+        ("residual", C.c_void_p),
+        ("res_ld", C.c_long),
+        ("out", C.c_void_p),
+        ("out_ld", C.c_long),
+        ("out_fp32", C.c_int),
+        ("patch_k", C.c_int), ("patch_c", C.c_int),
+    ]
+
+
+def lib() -> C.CDLL:
+    """Load libleadyolo.so (once). Raises if it has not been built — there is no fallback path."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise LeadYoloError(
+                f"{LIB_PATH} is missing: build it with `python -m lead_yolo_b200.build` "
+                "(no CPU / PyTorch fallback exists for the LEAD-YOLO kernels)")
+        h = C.CDLL(str(LIB_PATH))
+        h.ly_last_error.restype = C.c_char_p
+        _lib = h
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().ly_last_error().decode(errors="replace")
+        raise LeadYoloError(f"{what} failed ({rc}): {msg}")
+
+
+def stream_ptr() -> C.c_void_p:
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t) -> C.c_void_p | None:
+    return None if t is None else C.c_void_p(t.data_ptr())

@@ -1,0 +1,441 @@
+// Implicit-GEMM convolution on tcgen05 tensor cores (sm_100a).
+//
+//   grid  = (M tiles, N tiles);  block = 192 threads:
+//     warp 0      TMA producer   (A box: 64 channels x Wt x Ht pixels of one tap; B box: 64 x BN weights)
+//     warp 1      MMA issuer     (one lane issues 4 x tcgen05.mma K=16 per 64-wide K chunk)
+//     warps 2..5  epilogue       (TMEM -> registers -> scale/shift/activation/residual -> global)
+//   A and B tiles live in 128B-swizzled shared memory, accumulators (128 x BN fp32) in TMEM.
+//   Zero padding of a 3x3 convolution and ragged channel counts are TMA out-of-bounds zero fill.
+#include <string.h>
+
+#include <mutex>
+
+#include "ly_common.cuh"
+#include "ly_tc.cuh"
+#include "ly_tmap.h"
+
+namespace ly {
+
+constexpr int kMaxK = 96;      // K chunks of 64 per launch
+constexpr int kMaxStages = 4;
+constexpr int kAStage = 128 * 128;  // 128 rows x 128 B
+
+struct KEntry {
+  int16_t src;  // which A tensor map
+  int16_t c0;   // channel coordinate of the chunk
+  int8_t dw, dh, tz, pad_;
+};
+
+struct alignas(64) ConvGemmParams {
+  CUtensorMap a_map[4];
+  CUtensorMap b_map;
+  int tiles_w, tiles_h, n_img;
+  int Wt, Ht, Hout, Wout;
+  int num_k, Cout, BN, tmem_cols, stages;
+  int act, out_fp32, vec_ok, res_vec_ok;
+  uint32_t a_bytes;
+  int patch_k, patch_c;
+  const float* scale;
+  const float* shift;
+  const __nv_bfloat16* residual;
+  long res_ld;
+  void* out;
+  long out_ld;
+  KEntry sched[kMaxK];
+};
+
+__global__ void __launch_bounds__(192) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[kMaxStages];
+  __shared__ uint64_t empty_bar[kMaxStages];
+  __shared__ uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_base_s;
+  __shared__ float s_scale[256];
+  __shared__ float s_shift[256];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + p.stages * kAStage;
+  const int b_stage = p.BN * 128;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.b_map);
+    tma_prefetch_desc(&p.a_map[0]);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tmem_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_s;
+
+  const int bx = blockIdx.x;
+  const int tw = bx % p.tiles_w;
+  const int th = (bx / p.tiles_w) % p.tiles_h;
+  const int n = bx / (p.tiles_w * p.tiles_h);
+  const int w0 = tw * p.Wt, h0 = th * p.Ht;
+  const int n0 = blockIdx.y * p.BN;
+
+  if (warp == 0) {
+    // ---------------- TMA producer ----------------
+    for (int it = 0; it < p.num_k; ++it) {
+      const int s = it % p.stages;
+      const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+      mbar_wait(&empty_bar[s], ph ^ 1u);
+      if (lane == 0) {
+        const KEntry e = p.sched[it];
+        mbar_arrive_expect_tx(&full_bar[s], p.a_bytes + (uint32_t)b_stage);
+        tma_load_5d(sA + s * kAStage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
+        tma_load_2d(sB + s * b_stage, &p.b_map, &full_bar[s], it * 64, n0);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer ----------------
+    const uint32_t idesc = umma_idesc_bf16_f32(128, p.BN, 0, 0);
+    for (int it = 0; it < p.num_k; ++it) {
+      const int s = it % p.stages;
+      const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+      mbar_wait(&full_bar[s], ph);
+      tc_fence_after_sync();
+      if (lane == 0) {
+        const uint32_t a_base = smem_u32(sA + s * kAStage);
+        const uint32_t b_base = smem_u32(sB + s * b_stage);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t adesc = umma_smem_desc_sw128(a_base + k * 32, 16, 1024);
+          const uint64_t bdesc = umma_smem_desc_sw128(b_base + k * 32, 16, 1024);
+          umma_bf16(tmem_base, adesc, bdesc, idesc, (uint32_t)((it | k) != 0));
+        }
+        umma_commit(&empty_bar[s]);
+        if (it == p.num_k - 1) umma_commit(&tmem_full_bar);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ---------------- epilogue ----------------
+    const int et = threadIdx.x - 64;
+    for (int i = et; i < p.BN; i += 128) {
+      const int c = n0 + i;
+      s_scale[i] = (p.scale != nullptr && c < p.Cout) ? p.scale[c] : 1.f;
+      s_shift[i] = (p.shift != nullptr && c < p.Cout) ? p.shift[c] : 0.f;
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    const int r = q * 32 + lane;
+    const int hh = r / p.Wt;
+    const int ww = r - hh * p.Wt;
+    const int h = h0 + hh, w = w0 + ww;
+    const bool valid = (r < p.Wt * p.Ht) && (h < p.Hout) && (w < p.Wout);
+    const long pix = ((long)n * p.Hout + h) * p.Wout + w;
+    const int kC = p.patch_k * p.patch_c;
+
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after_sync();
+
+    for (int c0 = 0; c0 < p.BN; c0 += 16) {
+      uint32_t acc[16];
+      __syncwarp();
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, acc);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        if (!valid) break;
+        const int c = n0 + c0 + g * 8;
+        if (c >= p.Cout) break;
+        const int nv = min(8, p.Cout - c);
+        long o_off, r_off;
+        if (p.patch_k > 0) {
+          const int ky = c / kC, rem = c - ky * kC;
+          const long fp = ((long)n * p.Hout * p.patch_k + (long)h * p.patch_k + ky) * ((long)p.Wout * p.patch_k) +
+                          (long)w * p.patch_k;
+          o_off = fp * p.out_ld + rem;
+          r_off = fp * p.res_ld + rem;
+        } else {
+          o_off = pix * p.out_ld + c;
+          r_off = pix * p.res_ld + c;
+        }
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int ci = c0 + g * 8 + j;
+          v[j] = act_apply(fmaf(__uint_as_float(acc[g * 8 + j]), s_scale[ci], s_shift[ci]), p.act);
+        }
+        if (p.residual != nullptr) {
+          if (p.res_vec_ok && nv == 8) {
+            float rr[8];
+            unpack8(*reinterpret_cast<const uint4*>(p.residual + r_off), rr);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] += rr[j];
+          } else {
+            for (int j = 0; j < nv; ++j) v[j] += __bfloat162float(p.residual[r_off + j]);
+          }
+        }
+        if (p.out_fp32) {
+          float* o = reinterpret_cast<float*>(p.out) + o_off;
+          if (p.vec_ok && nv == 8) {
+            reinterpret_cast<float4*>(o)[0] = make_float4(v[0], v[1], v[2], v[3]);
+            reinterpret_cast<float4*>(o)[1] = make_float4(v[4], v[5], v[6], v[7]);
+          } else {
+            for (int j = 0; j < nv; ++j) o[j] = v[j];
+          }
+        } else {
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + o_off;
+          if (p.vec_ok && nv == 8) {
+            *reinterpret_cast<uint4*>(o) = pack8(v);
+          } else {
+            for (int j = 0; j < nv; ++j) o[j] = __float2bfloat16(v[j]);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+struct ConvGeom {
+  bool flat;       // 1x1: rows are the flattened pixels
+  bool patch;      // kernel == stride, no padding
+  int taps;        // K taps per source
+  int Hout, Wout;
+};
+
+static int conv_geometry(const ly_conv_desc* d, ConvGeom* g) {
+  LY_REQUIRE(d != nullptr, "null descriptor");
+  LY_REQUIRE(d->n_src >= 1 && d->n_src <= 4, "n_src=%d out of range", d->n_src);
+  LY_REQUIRE(d->N > 0 && d->H > 0 && d->W > 0 && d->Cout > 0, "bad sizes N=%d H=%d W=%d Cout=%d", d->N, d->H,
+             d->W, d->Cout);
+  g->flat = g->patch = false;
+  if (d->kh == 1 && d->kw == 1 && d->stride == 1 && d->pad == 0) {
+    g->flat = true;
+    g->taps = 1;
+    g->Hout = d->H;
+    g->Wout = d->W;
+  } else if (d->kh == 3 && d->kw == 3 && d->stride == 1 && d->pad == 1) {
+    g->taps = 9;
+    g->Hout = d->H;
+    g->Wout = d->W;
+  } else if (d->kh == d->kw && d->stride == d->kh && d->pad == 0 && (d->kh == 2 || d->kh == 4)) {
+    LY_REQUIRE(d->H % d->kh == 0 && d->W % d->kw == 0, "patch conv needs H,W divisible by k=%d", d->kh);
+    g->patch = true;
+    g->taps = d->kh;
+    g->Hout = d->H / d->kh;
+    g->Wout = d->W / d->kw;
+  } else {
+    return fail(LY_EUNSUPPORTED, "conv geometry k=%dx%d s=%d p=%d not supported", d->kh, d->kw, d->stride,
+                d->pad);
+  }
+  for (int s = 0; s < d->n_src; ++s) {
+    LY_REQUIRE(d->src[s] != nullptr, "source %d is null", s);
+    LY_REQUIRE(d->src_c[s] > 0 && d->src_c[s] % 8 == 0, "source %d: channels %d must be a multiple of 8", s,
+               d->src_c[s]);
+    LY_REQUIRE(d->src_ld[s] >= d->src_c[s] && d->src_ld[s] % 8 == 0, "source %d: ld %ld invalid", s,
+               d->src_ld[s]);
+    if (g->patch) LY_REQUIRE(d->src_ld[s] == d->src_c[s], "patch conv needs a dense source (ld == C)");
+  }
+  return LY_OK;
+}
+
+static int conv_chunks(const ly_conv_desc* d, const ConvGeom& g) {
+  int n = 0;
+  for (int s = 0; s < d->n_src; ++s) {
+    const int ceff = g.patch ? d->src_c[s] * d->kw : d->src_c[s];
+    n += g.taps * ceil_div(ceff, 64);
+  }
+  return n;
+}
+
+static void pick_tile(int Hout, int Wout, int* Wt, int* Ht) {
+  double best = -1.0;
+  int cand[7] = {8, 16, 32, 64, 128, Wout <= 128 ? Wout : 128, 0};
+  for (int i = 0; i < 6; ++i) {
+    int wt = cand[i];
+    if (wt <= 0 || wt > 128) continue;
+    int ht = 128 / wt;
+    if (ht > Hout) ht = Hout;
+    if (ht < 1) ht = 1;
+    double eff = (double)Hout * Wout / ((double)ceil_div(Wout, wt) * ceil_div(Hout, ht) * 128.0);
+    if (eff > best + 1e-9 || (eff > best - 1e-9 && wt > *Wt)) {
+      best = eff;
+      *Wt = wt;
+      *Ht = ht;
+    }
+  }
+}
+
+static int set_smem_attr_once() {
+  static std::once_flag flags[64];
+  int dev = 0;
+  LY_CUDA(cudaGetDevice(&dev));
+  cudaError_t err = cudaSuccess;
+  std::call_once(flags[dev & 63], [&] {
+    err = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024);
+  });
+  if (err != cudaSuccess) return fail(LY_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(err));
+  return LY_OK;
+}
+
+}  // namespace ly
+
+using namespace ly;
+
+extern "C" int ly_conv_num_chunks(const ly_conv_desc* d) {
+  ConvGeom g;
+  int rc = conv_geometry(d, &g);
+  if (rc != LY_OK) return rc;
+  return conv_chunks(d, g);
+}
+
+extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
+  ConvGeom g;
+  int rc = conv_geometry(d, &g);
+  if (rc != LY_OK) return rc;
+  LY_REQUIRE(d->w_packed != nullptr && d->out != nullptr, "null weight/out pointer");
+  const int num_k = conv_chunks(d, g);
+  LY_REQUIRE(num_k <= kMaxK, "K too large: %d chunks of 64 (max %d)", num_k, kMaxK);
+  if (d->patch_k > 0) {
+    LY_REQUIRE(g.flat, "patch scatter output needs a 1x1 GEMM");
+    LY_REQUIRE(d->patch_c % 8 == 0 && d->Cout == d->patch_k * d->patch_k * d->patch_c,
+               "patch scatter: Cout=%d != k*k*c", d->Cout);
+    LY_REQUIRE(d->out_ld == d->patch_c && (d->residual == nullptr || d->res_ld == d->patch_c),
+               "patch scatter needs dense output");
+  }
+
+  static_assert(sizeof(ConvGemmParams) <= 4000, "kernel parameter block too large");
+  ConvGemmParams p;
+  memset(&p, 0, sizeof(p));
+
+  // ---- tile geometry
+  const bool flat_rows = g.flat;
+  if (flat_rows) {
+    const long M = (long)d->N * d->H * d->W;
+    p.n_img = 1;
+    p.Hout = 1;
+    p.Wout = (int)M;
+    p.Wt = 128;
+    p.Ht = 1;
+    if (d->patch_k > 0) {
+      // scatter addressing needs (n, h, w): tile inside one image row-block instead
+      p.n_img = d->N;
+      p.Hout = d->H;
+      p.Wout = d->W;
+      pick_tile(p.Hout, p.Wout, &p.Wt, &p.Ht);
+    }
+  } else {
+    p.n_img = d->N;
+    p.Hout = g.Hout;
+    p.Wout = g.Wout;
+    pick_tile(p.Hout, p.Wout, &p.Wt, &p.Ht);
+  }
+  p.tiles_w = ceil_div(p.Wout, p.Wt);
+  p.tiles_h = ceil_div(p.Hout, p.Ht);
+  p.a_bytes = (uint32_t)(64 * p.Wt * p.Ht * 2);
+
+  // ---- A tensor maps + K schedule
+  int it = 0;
+  for (int s = 0; s < d->n_src; ++s) {
+    const long ld = d->src_ld[s];
+    uint64_t dims[5], str[4];
+    uint32_t box[5] = {64, (uint32_t)p.Wt, 1, (uint32_t)p.Ht, 1};
+    int ceff = d->src_c[s];
+    if (flat_rows && d->patch_k == 0) {
+      const uint64_t M = (uint64_t)d->N * d->H * d->W;
+      dims[0] = (uint64_t)d->src_c[s]; dims[1] = M; dims[2] = 1; dims[3] = 1; dims[4] = 1;
+      str[0] = (uint64_t)ld * 2; str[1] = M * ld * 2; str[2] = str[1]; str[3] = str[1];
+    } else if (g.patch) {
+      const int k = d->kh;
+      ceff = d->src_c[s] * k;
+      dims[0] = (uint64_t)ceff; dims[1] = (uint64_t)g.Wout; dims[2] = (uint64_t)k; dims[3] = (uint64_t)g.Hout;
+      dims[4] = (uint64_t)d->N;
+      str[0] = (uint64_t)ceff * 2;
+      str[1] = (uint64_t)d->W * ld * 2;
+      str[2] = (uint64_t)k * d->W * ld * 2;
+      str[3] = (uint64_t)d->H * d->W * ld * 2;
+    } else {
+      dims[0] = (uint64_t)d->src_c[s]; dims[1] = (uint64_t)d->W; dims[2] = 1; dims[3] = (uint64_t)d->H;
+      dims[4] = (uint64_t)d->N;
+      str[0] = (uint64_t)ld * 2;
+      str[1] = (uint64_t)d->W * ld * 2;
+      str[2] = str[1];
+      str[3] = (uint64_t)d->H * d->W * ld * 2;
+    }
+    rc = tmap_encode_bf16(&p.a_map[s], d->src[s], 5, dims, str, box);
+    if (rc != LY_OK) return rc;
+    for (int t = 0; t < g.taps; ++t) {
+      for (int c0 = 0; c0 < ceff; c0 += 64) {
+        KEntry e;
+        e.src = (int16_t)s;
+        e.c0 = (int16_t)c0;
+        e.pad_ = 0;
+        if (g.patch) {
+          e.dw = 0; e.dh = 0; e.tz = (int8_t)t;
+        } else {
+          e.dw = (int8_t)(t % d->kw - d->pad);
+          e.dh = (int8_t)(t / d->kw - d->pad);
+          e.tz = 0;
+        }
+        p.sched[it++] = e;
+      }
+    }
+  }
+  p.num_k = it;
+
+  // ---- N tiling, B map
+  const int cout_r = (d->Cout + 15) / 16 * 16;
+  const int ny = ceil_div(cout_r, 256);
+  p.BN = (ceil_div(cout_r, ny) + 15) / 16 * 16;
+  p.Cout = d->Cout;
+  p.tmem_cols = 32;
+  while (p.tmem_cols < p.BN) p.tmem_cols *= 2;
+  {
+    uint64_t dims[2] = {(uint64_t)num_k * 64, (uint64_t)d->Cout};
+    uint64_t str[1] = {(uint64_t)num_k * 64 * 2};
+    uint32_t box[2] = {64, (uint32_t)p.BN};
+    rc = tmap_encode_bf16(&p.b_map, d->w_packed, 2, dims, str, box);
+    if (rc != LY_OK) return rc;
+  }
+  const int stage_bytes = kAStage + p.BN * 128;
+  p.stages = num_k < kMaxStages ? num_k : kMaxStages;
+  while (p.stages > 1 && p.stages * stage_bytes > 200 * 1024) --p.stages;
+  const size_t smem_bytes = (size_t)p.stages * stage_bytes + 1024;
+
+  // ---- epilogue
+  p.act = d->act;
+  p.scale = d->scale;
+  p.shift = d->shift;
+  p.residual = reinterpret_cast<const __nv_bfloat16*>(d->residual);
+  p.res_ld = d->res_ld;
+  p.out = d->out;
+  p.out_ld = d->out_ld;
+  p.out_fp32 = d->out_fp32;
+  p.patch_k = d->patch_k;
+  p.patch_c = d->patch_c;
+  const uintptr_t oa = reinterpret_cast<uintptr_t>(d->out);
+  p.vec_ok = d->out_fp32 ? ((oa % 16 == 0) && (d->out_ld % 4 == 0)) : ((oa % 16 == 0) && (d->out_ld % 8 == 0));
+  p.res_vec_ok = d->residual != nullptr && (reinterpret_cast<uintptr_t>(d->residual) % 16 == 0) &&
+                 (d->res_ld % 8 == 0);
+
+  rc = set_smem_attr_once();
+  if (rc != LY_OK) return rc;
+  dim3 grid((unsigned)(p.tiles_w * p.tiles_h * p.n_img), (unsigned)ny, 1);
+  conv_gemm_kernel<<<grid, 192, smem_bytes, (cudaStream_t)stream>>>(p);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
