@@ -73,6 +73,97 @@ typedef struct {
 int ly_conv_num_chunks(const ly_conv_desc* d); /* number of 64-wide K chunks (Kp / 64); <0 on error */
 int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream);
 
+/* Weight gradient of the convolution described by `d` (autograd of nn.Conv2d; the reference relies on PyTorch
+ * autograd).  dz: bf16 NHWC output gradient [N,Hout,Wout,Cout] with pixel stride dz_ld.
+ * dw: fp32 [Cout][Kp] in the packed-K layout; partial sums are ADDED (zero it first).  tcgen05, MN-major. */
+int ly_conv_wgrad(const ly_conv_desc* d, const void* dz, long dz_ld, float* dw, ly_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * BatchNorm2d / activation streaming kernels on an NHWC bf16 matrix [M pixels][C], C % 8 == 0.
+ * Reference: nn.BatchNorm2d at models/common.py:91,1462,1533,1551,1591, models/rfa.py:104,111 with
+ * eps/momentum from utils/torch_utils.py:217-219; activations common.py:84 (SiLU), 1463 (ReLU), 1565-1580.
+ * ------------------------------------------------------------------------------------------------------ */
+/* sum[c] += Σ_m x[m][c];  sq[c] += Σ_m x[m][c]^2 (sq may be NULL).  Accumulates: zero the outputs first. */
+int ly_col_stats(const void* x, long ld, long M, int C, float* sum, float* sq, ly_stream_t stream);
+/* Training-mode statistics -> mean, rstd, scale = gamma*rstd, shift = beta - mean*scale; updates the running
+ * statistics in place (unbiased variance, momentum) when running_mean/var are non-NULL. */
+int ly_bn_finalize(const float* sum, const float* sq, int C, long n, float eps, float momentum, const float* gamma,
+                   const float* beta, float* running_mean, float* running_var, float* mean_out, float* rstd_out,
+                   float* scale_out, float* shift_out, ly_stream_t stream);
+/* Inference fold: scale = gamma/sqrt(running_var+eps), shift = beta - running_mean*scale (+ conv_bias*scale). */
+int ly_bn_fold(int C, float eps, const float* gamma, const float* beta, const float* running_mean,
+               const float* running_var, const float* conv_bias, float* mean_out, float* rstd_out, float* scale_out,
+               float* shift_out, ly_stream_t stream);
+/* y = act(x*scale[c] + shift[c]) */
+int ly_scale_shift_act(const void* x, long ldx, long M, int C, const float* scale, const float* shift, int act,
+                       void* y, long ldy, ly_stream_t stream);
+/* Backward of y = act(scale*z + shift): s1 += Σ dact, s2 += Σ dact*xhat (= dbeta, dgamma); dz per BatchNorm
+ * backward (training: batch statistics; otherwise dz = scale*dact).  s1/s2 must be zeroed by the caller. */
+int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz, long M, int C, const float* scale,
+                  const float* shift, const float* mean, const float* rstd, int act, int training, float* s1,
+                  float* s2, void* dz, long lddz, ly_stream_t stream);
+/* dz = dy * act'(.) with the derivative taken from the activation OUTPUT y (none / relu / sigmoid). */
+int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, long ldy, long M, int C, int act, void* dz,
+                        long lddz, ly_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Stem: PatchEmbed_FasterNet.proj on the raw image (models/common.py:1531,1537): 4x4/s4 conv, 3 -> Cout,
+ * NCHW fp32 (or uint8 with in_scale = 1/255, train.py:295) -> NHWC bf16; out = scale*conv + shift.
+ * wk: fp32 [48][Cout], k = (c*4+ky)*4+kx.  ly_stem_wgrad ADDS the weight gradient into dwk (same layout).
+ * ------------------------------------------------------------------------------------------------------ */
+int ly_stem_fwd(const void* img, int img_is_u8, int N, int H, int W, int Cout, const float* wk, const float* scale,
+                const float* shift, float in_scale, void* out, long ld_out, ly_stream_t stream);
+int ly_stem_wgrad(const void* img, int img_is_u8, int N, int H, int W, int Cout, const void* dz, long ld_dz,
+                  float in_scale, float* dwk, ly_stream_t stream);
+
+/* SPPF pooling (models/common.py:356,364-367): 5x5 / stride 1 / pad 2 max pool on an NHWC channel slice.
+ * idx (optional, uint8 [pixels][C]) records the arg-max tap for ly_maxpool5_bwd. */
+int ly_maxpool5_fwd(const void* x, long ldx, int N, int H, int W, int C, void* y, long ldy, uint8_t* idx,
+                    ly_stream_t stream);
+int ly_maxpool5_bwd(const void* dy, long lddy, const uint8_t* idx, int N, int H, int W, int C, void* dx, long lddx,
+                    int accumulate, ly_stream_t stream);
+
+/* nn.Upsample(None, 2, 'nearest') / Concat (LEAD-YOLO.yaml:29-34, models/common.py:531-538): copy an NHWC
+ * tensor into a channel slice of a wider buffer, optionally replicating 2x2 (up = 2); and its backward. */
+int ly_copy_upsample(const void* src, long lds, int N, int Hs, int Ws, int C, int up, void* dst, long ldd,
+                     ly_stream_t stream);
+int ly_downsum2(const void* src, long lds, int N, int H, int W, int C, void* dst, long ldd, ly_stream_t stream);
+
+/* rfa.SE global average pool (models/rfa.py:80,90): bf16 [N][C] <- mean over HW. */
+int ly_gap(const void* x, long ldx, int N, int HW, int C, void* out, long ldo, ly_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * CoordAtt (models/common.py:1595-1609).  "HW rows" matrix: [N*H + N*W][C]; row n*H+h = mean_w x[n,h,:,c],
+ * row N*H + n*W + w = mean_h x[n,:,w,c].  Gates use the same row layout.
+ * ------------------------------------------------------------------------------------------------------ */
+int ly_ca_pool(const void* x, long ldx, int N, int H, int W, int C, void* pooled, long ldp, ly_stream_t stream);
+int ly_ca_apply(const void* x, long ldx, const void* gates, long ldg, int N, int H, int W, int C, void* out,
+                long ldo, ly_stream_t stream); /* out = x * a_h[n,h,c] * a_w[n,w,c] */
+int ly_ca_gate_grad(const void* x, long ldx, const void* dy, long lddy, const void* gates, long ldg, int N, int H,
+                    int W, int C, void* dgates, long ldd, ly_stream_t stream);
+int ly_ca_pool_bwd(const void* dpooled, long ldp, int N, int H, int W, int C, void* dx, long ldx,
+                   ly_stream_t stream); /* dx = dP_h[n,h,c]/W + dP_w[n,w,c]/H */
+
+/* ------------------------------------------------------------------------------------------------------
+ * RFCBAMConv (models/rfa.py:95-129).  G/A: bf16 [N*ho*wo][k*k*C], column t*C+c (t = n1*k+n2);
+ * maps fp32 [N][ho*k][wo*k][2] (max, mean over c); amax int16 [N][ho*k][wo*k]; att fp32 [N][ho*k][wo*k];
+ * wgk fp32 [k*k][k*k][C] = generate.0.weight[c*k*k+t, 0, i, j] at [t][i*k+j][c]; wa fp32 [2][3][3].
+ * ------------------------------------------------------------------------------------------------------ */
+int ly_rf_generate(const void* x, long ldx, int N, int H, int W, int C, int k, int s, int ho, int wo,
+                   const float* wgk, const float* scale, const float* shift, int act, void* G, ly_stream_t stream);
+int ly_rf_attention(const void* G, int N, int ho, int wo, int C, int k, const float* wa, float* maps, int16_t* amax,
+                    float* att, ly_stream_t stream);
+int ly_rf_gate(const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse, const float* att,
+               void* A, ly_stream_t stream); /* A = G * se[n,c] * att */
+int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse,
+                   const float* att, void* dG, float* dse, float* datt, ly_stream_t stream);
+int ly_rf_attention_bwd(const float* datt, const float* att, const float* maps, const int16_t* amax, int N, int ho,
+                        int wo, int C, int k, const float* wa, float* dmaps, float* dwa, void* dG,
+                        ly_stream_t stream); /* dG += route(dmax) + dmean/C ; dwa += */
+int ly_rf_generate_bwd(const void* dZ, const void* x, long ldx, int N, int H, int W, int C, int k, int s, int ho,
+                       int wo, const float* wgk, const float* extra, void* dx, long lddx, float* dwgk,
+                       ly_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,344 @@
+// Per-channel streaming kernels over NHWC bf16 matrices [M pixels][C channels] (pixel stride ld):
+// BatchNorm statistics / finalize / apply (+activation) and their backward passes.
+//
+// Access pattern shared by all kernels here: the matrix is a flat stream of 16-byte vectors (8 channels).
+// The launch makes (gridDim.x * blockDim.x) a multiple of V = C/8, so every thread keeps ONE fixed channel
+// vector (its scale/shift/mean live in registers) while consecutive threads touch consecutive vectors
+// (fully coalesced).  HBM-bound: algorithmic bytes = each operand read or written once.
+#include "ly_common.cuh"
+
+namespace ly {
+
+static int gcd_i(int a, int b) { return b == 0 ? a : gcd_i(b, a % b); }
+
+// grid size whose total thread count is a multiple of V
+int flat_grid(long M, int V, int block) {
+  const int m = V / gcd_i(V, block);
+  long want = (M * V + (long)block * 4 - 1) / ((long)block * 4);
+  const long cap = (long)device_sm_count() * 8;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  long g = (want + m - 1) / m * m;
+  return (int)g;
+}
+
+#define LY_FLAT_SETUP(V)                                                         \
+  const long T_ = (long)gridDim.x * blockDim.x;                                  \
+  const long t_ = (long)blockIdx.x * blockDim.x + threadIdx.x;                   \
+  const int v = (int)(t_ % (V));                                                 \
+  const long row0 = t_ / (V);                                                    \
+  const long rstep = T_ / (V);
+
+__device__ __forceinline__ uint4 ld16(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void st16(__nv_bfloat16* p, const uint4& u) { *reinterpret_cast<uint4*>(p) = u; }
+
+// ------------------------------------------------------------------------------------------------
+// sum[c] += Σ x, sq[c] += Σ x²   (sq may be null)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) col_stats_kernel(const __nv_bfloat16* __restrict__ x, long ld, long M, int V,
+                                                        float* __restrict__ sum, float* __restrict__ sq) {
+  extern __shared__ float sm[];  // [2][C]
+  const int C = V * 8;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  LY_FLAT_SETUP(V)
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  long row = row0;
+  for (; row + 3 * rstep < M; row += 4 * rstep) {
+    uint4 u0 = ld16(x + row * ld + v * 8);
+    uint4 u1 = ld16(x + (row + rstep) * ld + v * 8);
+    uint4 u2 = ld16(x + (row + 2 * rstep) * ld + v * 8);
+    uint4 u3 = ld16(x + (row + 3 * rstep) * ld + v * 8);
+    float f[8];
+    unpack8(u0, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+    unpack8(u1, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+    unpack8(u2, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+    unpack8(u3, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+  }
+  for (; row < M; row += rstep) {
+    float f[8];
+    unpack8(ld16(x + row * ld + v * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    atomicAdd(&sm[v * 8 + j], s[j]);
+    atomicAdd(&sm[C + v * 8 + j], q[j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(&sum[i], sm[i]);
+    if (sq != nullptr) atomicAdd(&sq[i], sm[C + i]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// BatchNorm finalize: batch mean / biased var -> (mean, rstd, scale, shift) and running-stat update.
+// nn.BatchNorm2d semantics: running_var gets the unbiased variance.
+// ------------------------------------------------------------------------------------------------
+__global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sq, int C, float n,
+                                   float eps, float momentum, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* running_mean, float* running_var,
+                                   float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                   float* __restrict__ scale_out, float* __restrict__ shift_out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mean = sum[c] / n;
+  const float var = fmaxf(sq[c] / n - mean * mean, 0.f);
+  const float rstd = rsqrtf(var + eps);
+  const float g = gamma != nullptr ? gamma[c] : 1.f;
+  const float b = beta != nullptr ? beta[c] : 0.f;
+  mean_out[c] = mean;
+  rstd_out[c] = rstd;
+  scale_out[c] = g * rstd;
+  shift_out[c] = b - mean * g * rstd;
+  if (running_mean != nullptr) {
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    const float unbiased = n > 1.f ? var * n / (n - 1.f) : var;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+  }
+}
+
+// Inference fold: scale = gamma / sqrt(running_var + eps); shift = beta - running_mean*scale + bias*scale
+__global__ void bn_fold_kernel(int C, float eps, const float* __restrict__ gamma, const float* __restrict__ beta,
+                               const float* __restrict__ rmean, const float* __restrict__ rvar,
+                               const float* __restrict__ conv_bias, float* __restrict__ mean_out,
+                               float* __restrict__ rstd_out, float* __restrict__ scale_out,
+                               float* __restrict__ shift_out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float rstd = rsqrtf(rvar[c] + eps);
+  const float sc = gamma[c] * rstd;
+  float sh = beta[c] - rmean[c] * sc;
+  if (conv_bias != nullptr) sh += conv_bias[c] * sc;
+  if (mean_out != nullptr) mean_out[c] = rmean[c];
+  if (rstd_out != nullptr) rstd_out[c] = rstd;
+  scale_out[c] = sc;
+  shift_out[c] = sh;
+}
+
+// ------------------------------------------------------------------------------------------------
+// y = act(x * scale[c] + shift[c])
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) scale_shift_act_kernel(const __nv_bfloat16* __restrict__ x, long ldx, long M,
+                                                              int V, const float* __restrict__ scale,
+                                                              const float* __restrict__ shift, int act,
+                                                              __nv_bfloat16* __restrict__ y, long ldy) {
+  LY_FLAT_SETUP(V)
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale != nullptr ? scale[v * 8 + j] : 1.f;
+    sh[j] = shift != nullptr ? shift[v * 8 + j] : 0.f;
+  }
+  for (long row = row0; row < M; row += rstep) {
+    float f[8];
+    unpack8(ld16(x + row * ldx + v * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = act_apply(fmaf(f[j], sc[j], sh[j]), act);
+    st16(y + row * ldy + v * 8, pack8(f));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward of y = act(scale*z + shift) with scale = gamma*rstd, shift = beta - mean*scale.
+// pass 1: s1[c] += Σ dact, s2[c] += Σ dact * xhat     (dact = dy * act'(scale*z+shift), xhat = (z-mean)*rstd)
+// pass 2: dz = scale * (dact - s1/n - xhat*s2/n)      (training) |  dz = scale * dact  (eval / plain affine)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) bn_act_bwd_reduce_kernel(
+    const __nv_bfloat16* __restrict__ dy, long lddy, const __nv_bfloat16* __restrict__ z, long ldz, long M, int V,
+    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
+    const float* __restrict__ rstd, int act, float* __restrict__ s1, float* __restrict__ s2) {
+  extern __shared__ float sm[];
+  const int C = V * 8;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  LY_FLAT_SETUP(V)
+  float sc[8], sh[8], mu[8], rs[8], a1[8], a2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale[v * 8 + j]; sh[j] = shift[v * 8 + j];
+    mu[j] = mean[v * 8 + j]; rs[j] = rstd[v * 8 + j];
+    a1[j] = a2[j] = 0.f;
+  }
+  for (long row = row0; row < M; row += rstep) {
+    float g[8], f[8];
+    unpack8(ld16(dy + row * lddy + v * 8), g);
+    unpack8(ld16(z + row * ldz + v * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = g[j] * act_grad(fmaf(f[j], sc[j], sh[j]), act);
+      a1[j] += d;
+      a2[j] = fmaf(d, (f[j] - mu[j]) * rs[j], a2[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    atomicAdd(&sm[v * 8 + j], a1[j]);
+    atomicAdd(&sm[C + v * 8 + j], a2[j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(&s1[i], sm[i]);
+    atomicAdd(&s2[i], sm[C + i]);
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(
+    const __nv_bfloat16* __restrict__ dy, long lddy, const __nv_bfloat16* __restrict__ z, long ldz, long M, int V,
+    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
+    const float* __restrict__ rstd, int act, const float* __restrict__ s1, const float* __restrict__ s2,
+    float inv_n, int training, __nv_bfloat16* __restrict__ dz, long lddz) {
+  LY_FLAT_SETUP(V)
+  float sc[8], sh[8], mu[8], rs[8], m1[8], m2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale[v * 8 + j]; sh[j] = shift[v * 8 + j];
+    mu[j] = mean != nullptr ? mean[v * 8 + j] : 0.f;
+    rs[j] = rstd != nullptr ? rstd[v * 8 + j] : 1.f;
+    m1[j] = training ? s1[v * 8 + j] * inv_n : 0.f;
+    m2[j] = training ? s2[v * 8 + j] * inv_n : 0.f;
+  }
+  for (long row = row0; row < M; row += rstep) {
+    float g[8], f[8];
+    unpack8(ld16(dy + row * lddy + v * 8), g);
+    unpack8(ld16(z + row * ldz + v * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = g[j] * act_grad(fmaf(f[j], sc[j], sh[j]), act);
+      const float xh = (f[j] - mu[j]) * rs[j];
+      f[j] = sc[j] * (d - m1[j] - xh * m2[j]);
+    }
+    st16(dz + row * lddz + v * 8, pack8(f));
+  }
+}
+
+// dz = dy * act'(.) where the derivative is taken from the OUTPUT y (relu, sigmoid, none).
+__global__ void __launch_bounds__(256) act_bwd_from_out_kernel(const __nv_bfloat16* __restrict__ dy, long lddy,
+                                                               const __nv_bfloat16* __restrict__ y, long ldy, long M,
+                                                               int V, int act, __nv_bfloat16* __restrict__ dz,
+                                                               long lddz) {
+  LY_FLAT_SETUP(V)
+  for (long row = row0; row < M; row += rstep) {
+    float g[8], f[8];
+    unpack8(ld16(dy + row * lddy + v * 8), g);
+    unpack8(ld16(y + row * ldy + v * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float d = 1.f;
+      if (act == LY_ACT_RELU) d = f[j] > 0.f ? 1.f : 0.f;
+      else if (act == LY_ACT_SIGMOID) d = f[j] * (1.f - f[j]);
+      g[j] *= d;
+    }
+    st16(dz + row * lddz + v * 8, pack8(g));
+  }
+}
+
+static int check_mat(const void* p, long ld, long M, int C, const char* what) {
+  LY_REQUIRE(p != nullptr, "%s: null pointer", what);
+  LY_REQUIRE(M > 0 && C > 0 && C % 8 == 0, "%s: bad shape M=%ld C=%d (C must be a multiple of 8)", what, M, C);
+  LY_REQUIRE(ld >= C && ld % 8 == 0, "%s: ld=%ld invalid", what, ld);
+  LY_REQUIRE(reinterpret_cast<uintptr_t>(p) % 16 == 0, "%s: pointer not 16-byte aligned", what);
+  LY_REQUIRE(C <= 4096, "%s: C=%d too large", what, C);
+  return LY_OK;
+}
+
+}  // namespace ly
+
+using namespace ly;
+
+extern "C" int ly_col_stats(const void* x, long ld, long M, int C, float* sum, float* sq, ly_stream_t st) {
+  int rc = check_mat(x, ld, M, C, "ly_col_stats");
+  if (rc) return rc;
+  LY_REQUIRE(sum != nullptr, "ly_col_stats: null sum");
+  const int V = C / 8;
+  col_stats_kernel<<<flat_grid(M, V, 256), 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
+      (const __nv_bfloat16*)x, ld, M, V, sum, sq);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_bn_finalize(const float* sum, const float* sq, int C, long n, float eps, float momentum,
+                              const float* gamma, const float* beta, float* running_mean, float* running_var,
+                              float* mean_out, float* rstd_out, float* scale_out, float* shift_out,
+                              ly_stream_t st) {
+  LY_REQUIRE(sum && sq && mean_out && rstd_out && scale_out && shift_out && C > 0 && n > 0, "ly_bn_finalize: bad args");
+  bn_finalize_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)st>>>(sum, sq, C, (float)n, eps, momentum, gamma,
+                                                                      beta, running_mean, running_var, mean_out,
+                                                                      rstd_out, scale_out, shift_out);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_bn_fold(int C, float eps, const float* gamma, const float* beta, const float* running_mean,
+                          const float* running_var, const float* conv_bias, float* mean_out, float* rstd_out,
+                          float* scale_out, float* shift_out, ly_stream_t st) {
+  LY_REQUIRE(C > 0 && gamma && beta && running_mean && running_var && scale_out && shift_out, "ly_bn_fold: bad args");
+  bn_fold_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)st>>>(C, eps, gamma, beta, running_mean, running_var,
+                                                                  conv_bias, mean_out, rstd_out, scale_out, shift_out);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_scale_shift_act(const void* x, long ldx, long M, int C, const float* scale, const float* shift,
+                                  int act, void* y, long ldy, ly_stream_t st) {
+  int rc = check_mat(x, ldx, M, C, "ly_scale_shift_act(x)");
+  if (rc) return rc;
+  rc = check_mat(y, ldy, M, C, "ly_scale_shift_act(y)");
+  if (rc) return rc;
+  const int V = C / 8;
+  scale_shift_act_kernel<<<flat_grid(M, V, 256), 256, 0, (cudaStream_t)st>>>(
+      (const __nv_bfloat16*)x, ldx, M, V, scale, shift, act, (__nv_bfloat16*)y, ldy);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz, long M, int C, const float* scale,
+                             const float* shift, const float* mean, const float* rstd, int act, int training,
+                             float* s1, float* s2, void* dz, long lddz, ly_stream_t st) {
+  int rc = check_mat(dy, lddy, M, C, "ly_bn_act_bwd(dy)");
+  if (rc) return rc;
+  rc = check_mat(z, ldz, M, C, "ly_bn_act_bwd(z)");
+  if (rc) return rc;
+  rc = check_mat(dz, lddz, M, C, "ly_bn_act_bwd(dz)");
+  if (rc) return rc;
+  LY_REQUIRE(scale && shift && mean && rstd && s1 && s2, "ly_bn_act_bwd: null statistics");
+  const int V = C / 8;
+  const int grid = flat_grid(M, V, 256);
+  bn_act_bwd_reduce_kernel<<<grid, 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
+      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2);
+  LY_LAUNCH_CHECK();
+  bn_act_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(
+      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2,
+      1.f / (float)M, training, (__nv_bfloat16*)dz, lddz);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, long ldy, long M, int C, int act,
+                                   void* dz, long lddz, ly_stream_t st) {
+  int rc = check_mat(dy, lddy, M, C, "ly_act_bwd_from_out(dy)");
+  if (rc) return rc;
+  rc = check_mat(y, ldy, M, C, "ly_act_bwd_from_out(y)");
+  if (rc) return rc;
+  rc = check_mat(dz, lddz, M, C, "ly_act_bwd_from_out(dz)");
+  if (rc) return rc;
+  LY_REQUIRE(act == LY_ACT_NONE || act == LY_ACT_RELU || act == LY_ACT_SIGMOID,
+             "ly_act_bwd_from_out: activation %d has no output-only derivative", act);
+  const int V = C / 8;
+  act_bwd_from_out_kernel<<<flat_grid(M, V, 256), 256, 0, (cudaStream_t)st>>>(
+      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)y, ldy, M, V, act, (__nv_bfloat16*)dz, lddz);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}

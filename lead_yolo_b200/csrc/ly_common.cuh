@@ -29,6 +29,8 @@ int fail(int code, const char* fmt, ...);
 #define LY_LAUNCH_CHECK() LY_CUDA(cudaGetLastError())
 
 int device_sm_count();
+// grid size (blocks of `block` threads) whose total thread count is a multiple of V (see elementwise.cu)
+int flat_grid(long M, int V, int block);
 
 static inline int ceil_div(long a, long b) { return (int)((a + b - 1) / b); }
 

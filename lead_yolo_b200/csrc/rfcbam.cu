@@ -1,0 +1,533 @@
+// RFCBAMConv (reference models/rfa.py:95-129) — receptive-field feature generation,
+// channel max/mean, 3x3 spatial-attention conv and gating, forward and backward.  The final k x k / stride k
+// convolution over the unfolded map is a plain GEMM with K = k*k*C on the gated matrix (conv_gemm.cu).
+//
+// Layouts (h, w = output resolution; t = n1*k + n2 the position inside the k x k receptive field):
+//   G / A  : bf16 [N*h*w][k*k*C], column t*C + c   == U[b, c, h*k+n1, w*k+n2] of the reference
+//   maps   : fp32 [N][h*k][w*k][2]  (0: max over c, 1: mean over c), argmax int16 [N][h*k][w*k]
+//   att    : fp32 [N][h*k][w*k]
+//   wgk    : fp32 [k*k (t)][k*k (i*k+j)][C]  (generate.0.weight[c*k*k+t, 0, i, j])
+#include "ly_common.cuh"
+
+namespace ly {
+
+__device__ __forceinline__ uint4 ldg16(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+// ------------------------------------------------------------------------------------------------
+// generate: depthwise k x k, stride s, pad k/2, C -> k*k*C, optional folded BN + ReLU epilogue.
+// One thread per (output pixel, 8-channel vector); computes all k*k taps t for those 8 channels.
+// ------------------------------------------------------------------------------------------------
+template <int K>
+__global__ void __launch_bounds__(128) rf_generate_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int N,
+                                                          int H, int W, int V, int s, int ho, int wo,
+                                                          const float* __restrict__ wgk,
+                                                          const float* __restrict__ scale,
+                                                          const float* __restrict__ shift, int act,
+                                                          __nv_bfloat16* __restrict__ G) {
+  constexpr int KK = K * K;
+  const int C = V * 8;
+  const long total = (long)N * ho * wo * V;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int v = (int)(tid % V);
+  const long m = tid / V;
+  const int w = (int)(m % wo), h = (int)((m / wo) % ho), n = (int)(m / ((long)wo * ho));
+  float xin[KK][8];
+#pragma unroll
+  for (int i = 0; i < K; ++i)
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      const int yy = h * s + i - K / 2, xx = w * s + j - K / 2;
+      if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+        unpack8(ldg16(x + (((long)n * H + yy) * W + xx) * ldx + v * 8), xin[i * K + j]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) xin[i * K + j][e] = 0.f;
+      }
+    }
+  __nv_bfloat16* grow = G + m * (long)KK * C + v * 8;
+#pragma unroll 1
+  for (int t = 0; t < KK; ++t) {
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+    for (int ij = 0; ij < KK; ++ij) {
+      const float4 w0 = __ldg(reinterpret_cast<const float4*>(wgk + ((long)t * KK + ij) * C + v * 8));
+      const float4 w1 = __ldg(reinterpret_cast<const float4*>(wgk + ((long)t * KK + ij) * C + v * 8 + 4));
+      acc[0] = fmaf(xin[ij][0], w0.x, acc[0]); acc[1] = fmaf(xin[ij][1], w0.y, acc[1]);
+      acc[2] = fmaf(xin[ij][2], w0.z, acc[2]); acc[3] = fmaf(xin[ij][3], w0.w, acc[3]);
+      acc[4] = fmaf(xin[ij][4], w1.x, acc[4]); acc[5] = fmaf(xin[ij][5], w1.y, acc[5]);
+      acc[6] = fmaf(xin[ij][6], w1.z, acc[6]); acc[7] = fmaf(xin[ij][7], w1.w, acc[7]);
+    }
+    if (scale != nullptr) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        acc[e] = act_apply(fmaf(acc[e], __ldg(scale + t * C + v * 8 + e), __ldg(shift + t * C + v * 8 + e)), act);
+    }
+    *reinterpret_cast<uint4*>(grow + (long)t * C) = pack8(acc);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// channel max / mean of G per (pixel, tap): one warp per (m, t)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rf_poolc_kernel(const __nv_bfloat16* __restrict__ G, long M, int KK, int K,
+                                                       int V, int ho, int wo, float* __restrict__ maps,
+                                                       int16_t* __restrict__ amax) {
+  const int lane = threadIdx.x & 31;
+  const long wid = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (wid >= M * KK) return;
+  const int t = (int)(wid % KK);
+  const long m = wid / KK;
+  const int C = V * 8;
+  const __nv_bfloat16* row = G + (m * KK + t) * (long)C;
+  float mx = -INFINITY, sum = 0.f;
+  int mi = 0;
+  for (int v = lane; v < V; v += 32) {
+    float f[8];
+    unpack8(ldg16(row + v * 8), f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      sum += f[e];
+      if (f[e] > mx) { mx = f[e]; mi = v * 8 + e; }
+    }
+  }
+  sum = warp_sum(sum);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, mi, o);
+    if (om > mx || (om == mx && oi < mi)) { mx = om; mi = oi; }
+  }
+  if (lane == 0) {
+    const int w = (int)(m % wo), h = (int)((m / wo) % ho);
+    const long n = m / ((long)wo * ho);
+    const int n1 = t / K, n2 = t % K;
+    const long pos = (n * (ho * K) + (h * K + n1)) * (long)(wo * K) + (w * K + n2);
+    maps[pos * 2] = mx;
+    maps[pos * 2 + 1] = sum / (float)C;
+    if (amax != nullptr) amax[pos] = (int16_t)mi;
+  }
+}
+
+// att = sigmoid(conv3x3_{2->1, pad 1}(maps))   (get_weight, rfa.py:106,127)
+__global__ void __launch_bounds__(256) rf_att_kernel(const float* __restrict__ maps, int N, int HK, int WK,
+                                                     const float* __restrict__ wa /*[2][3][3]*/,
+                                                     float* __restrict__ att) {
+  const long total = (long)N * HK * WK;
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int x = (int)(t % WK), y = (int)((t / WK) % HK);
+  const long n = t / ((long)WK * HK);
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int yy = y + i - 1, xx = x + j - 1;
+      if (yy < 0 || yy >= HK || xx < 0 || xx >= WK) continue;
+      const float2 mm = __ldg(reinterpret_cast<const float2*>(maps + ((n * HK + yy) * (long)WK + xx) * 2));
+      acc = fmaf(mm.x, __ldg(wa + i * 3 + j), acc);
+      acc = fmaf(mm.y, __ldg(wa + 9 + i * 3 + j), acc);
+    }
+  att[t] = 1.f / (1.f + __expf(-acc));
+}
+
+// A = G * se[n, c] * att[n, h*k+n1, w*k+n2]     (also used for dG1 = dA * se * att)
+__global__ void __launch_bounds__(256) rf_gate_kernel(const __nv_bfloat16* __restrict__ G, long M, int KK, int K,
+                                                      int V, int ho, int wo, const __nv_bfloat16* __restrict__ se,
+                                                      long ldse, const float* __restrict__ att,
+                                                      __nv_bfloat16* __restrict__ A) {
+  const long total = M * KK * V;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int v = (int)(tid % V);
+  const int t = (int)((tid / V) % KK);
+  const long m = tid / ((long)V * KK);
+  const int w = (int)(m % wo), h = (int)((m / wo) % ho);
+  const long n = m / ((long)wo * ho);
+  const int n1 = t / K, n2 = t % K;
+  const float a = __ldg(att + (n * (ho * K) + (h * K + n1)) * (long)(wo * K) + (w * K + n2));
+  float g[8], s8[8];
+  unpack8(ldg16(G + tid * 8), g);
+  unpack8(ldg16(se + n * ldse + v * 8), s8);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) g[e] *= s8[e] * a;
+  *reinterpret_cast<uint4*>(A + tid * 8) = pack8(g);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward of the gating: given dA, G, se, att ->
+//   dG1 = dA*se*att (written to dG), dse[n,c] += Σ dA*G*att, datt[pos] = Σ_c dA*G*se.
+// grid = (blocks per image, N); each warp strides over the (m, t) pairs of its image.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rf_gate_bwd_kernel(const __nv_bfloat16* __restrict__ dA,
+                                                          const __nv_bfloat16* __restrict__ G, int KK, int K, int V,
+                                                          int ho, int wo, const __nv_bfloat16* __restrict__ se,
+                                                          long ldse, const float* __restrict__ att,
+                                                          __nv_bfloat16* __restrict__ dG, float* __restrict__ dse,
+                                                          float* __restrict__ datt) {
+  const int lane = threadIdx.x & 31;
+  const int n = blockIdx.y;
+  const int C = V * 8;
+  const long per_img = (long)ho * wo * KK;
+  const long warps = ((long)gridDim.x * blockDim.x) >> 5;
+  const long w0 = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  // each lane owns up to 2 channel vectors (C <= 512)
+  float s8[2][8], ds[2][8];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int v = lane + q * 32;
+    if (v < V) unpack8(ldg16(se + (long)n * ldse + v * 8), s8[q]);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ds[q][e] = 0.f;
+  }
+  for (long i = w0; i < per_img; i += warps) {
+    const int t = (int)(i % KK);
+    const long ml = i / KK;  // pixel within image
+    const int w = (int)(ml % wo), h = (int)(ml / wo);
+    const int n1 = t / K, n2 = t % K;
+    const long pos = ((long)n * (ho * K) + (h * K + n1)) * (long)(wo * K) + (w * K + n2);
+    const float a = __ldg(att + pos);
+    const long rowoff = (((long)n * ho * wo + ml) * KK + t) * (long)C;
+    float da_att = 0.f;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int v = lane + q * 32;
+      if (v < V) {
+        float d[8], g[8];
+        unpack8(ldg16(dA + rowoff + v * 8), d);
+        unpack8(ldg16(G + rowoff + v * 8), g);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float dg = d[e] * g[e];
+          ds[q][e] = fmaf(dg, a, ds[q][e]);
+          da_att = fmaf(dg, s8[q][e], da_att);
+          d[e] *= s8[q][e] * a;
+        }
+        *reinterpret_cast<uint4*>(dG + rowoff + v * 8) = pack8(d);
+      }
+    }
+    da_att = warp_sum(da_att);
+    if (lane == 0) datt[pos] = da_att;
+  }
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int v = lane + q * 32;
+    if (v < V) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) atomicAdd(&dse[(long)n * C + v * 8 + e], ds[q][e]);
+    }
+  }
+}
+
+// Backward of att = sigmoid(conv3x3(maps)): dmaps (transposed conv) and dWa (18 values, atomics).
+__global__ void __launch_bounds__(256) rf_att_bwd_kernel(const float* __restrict__ datt, const float* __restrict__ att,
+                                                         const float* __restrict__ maps, int N, int HK, int WK,
+                                                         const float* __restrict__ wa, float* __restrict__ dmaps,
+                                                         float* __restrict__ dwa) {
+  __shared__ float sw[18];
+  if (threadIdx.x < 18) sw[threadIdx.x] = 0.f;
+  __syncthreads();
+  const long total = (long)N * HK * WK;
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  float lw[18];
+#pragma unroll
+  for (int q = 0; q < 18; ++q) lw[q] = 0.f;
+  if (t < total) {
+    const int x = (int)(t % WK), y = (int)((t / WK) % HK);
+    const long n = t / ((long)WK * HK);
+    // dpre at this position (for dWa) and at neighbours (for dmaps)
+    const float a0 = att[t];
+    const float dp0 = datt[t] * a0 * (1.f - a0);
+    float dm0 = 0.f, dm1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        // forward: pre[y,x] += wa[ch,i,j] * maps[y+i-1, x+j-1, ch]
+        const int yy = y + i - 1, xx = x + j - 1;
+        if (yy >= 0 && yy < HK && xx >= 0 && xx < WK) {
+          const float2 mm = __ldg(reinterpret_cast<const float2*>(maps + ((n * HK + yy) * (long)WK + xx) * 2));
+          lw[i * 3 + j] = dp0 * mm.x;
+          lw[9 + i * 3 + j] = dp0 * mm.y;
+        }
+        // transposed: dmaps[y,x,ch] += wa[ch,i,j] * dpre[y-i+1, x-j+1]
+        const int yo = y - i + 1, xo = x - j + 1;
+        if (yo >= 0 && yo < HK && xo >= 0 && xo < WK) {
+          const long o = (n * HK + yo) * (long)WK + xo;
+          const float ao = __ldg(att + o);
+          const float dpo = __ldg(datt + o) * ao * (1.f - ao);
+          dm0 = fmaf(__ldg(wa + i * 3 + j), dpo, dm0);
+          dm1 = fmaf(__ldg(wa + 9 + i * 3 + j), dpo, dm1);
+        }
+      }
+    dmaps[t * 2] = dm0;
+    dmaps[t * 2 + 1] = dm1;
+  }
+#pragma unroll
+  for (int q = 0; q < 18; ++q) {
+    const float s = warp_sum(lw[q]);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&sw[q], s);
+  }
+  __syncthreads();
+  if (threadIdx.x < 18) atomicAdd(&dwa[threadIdx.x], sw[threadIdx.x]);
+}
+
+// dG += dmean/C + [c == argmax] * dmax       (in place on dG)
+__global__ void __launch_bounds__(256) rf_poolc_bwd_kernel(__nv_bfloat16* __restrict__ dG, long M, int KK, int K,
+                                                           int V, int ho, int wo, const float* __restrict__ dmaps,
+                                                           const int16_t* __restrict__ amax) {
+  const long total = M * KK * V;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int v = (int)(tid % V);
+  const int t = (int)((tid / V) % KK);
+  const long m = tid / ((long)V * KK);
+  const int w = (int)(m % wo), h = (int)((m / wo) % ho);
+  const long n = m / ((long)wo * ho);
+  const int n1 = t / K, n2 = t % K;
+  const long pos = (n * (ho * K) + (h * K + n1)) * (long)(wo * K) + (w * K + n2);
+  const float2 dm = __ldg(reinterpret_cast<const float2*>(dmaps + pos * 2));
+  const int am = amax[pos];
+  const float dmean = dm.y / (float)(V * 8);
+  float d[8];
+  unpack8(*reinterpret_cast<const uint4*>(dG + tid * 8), d);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) d[e] += dmean + ((v * 8 + e) == am ? dm.x : 0.f);
+  *reinterpret_cast<uint4*>(dG + tid * 8) = pack8(d);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward of generate w.r.t. the input: dx[n,y,x,c] = Σ_{t,i,j} wgk[t][i*k+j][c] * dZ[m(h,w)][t*C+c]
+// over the (h,w) with h*s + i - k/2 == y, w*s + j - k/2 == x;  plus extra[n,c] (SE pooling gradient, already
+// divided by H*W) when given.  One thread per (input pixel, 8-channel vector).
+// ------------------------------------------------------------------------------------------------
+template <int K>
+__global__ void __launch_bounds__(128) rf_generate_dx_kernel(const __nv_bfloat16* __restrict__ dZ, int N, int H, int W,
+                                                             int V, int s, int ho, int wo,
+                                                             const float* __restrict__ wgk,
+                                                             const float* __restrict__ extra,
+                                                             __nv_bfloat16* __restrict__ dx, long lddx) {
+  constexpr int KK = K * K;
+  const int C = V * 8;
+  const long total = (long)N * H * W * V;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int v = (int)(tid % V);
+  const long pix = tid / V;
+  const int x = (int)(pix % W), y = (int)((pix / W) % H), n = (int)(pix / ((long)W * H));
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = extra != nullptr ? __ldg(extra + (long)n * C + v * 8 + e) : 0.f;
+#pragma unroll
+  for (int i = 0; i < K; ++i) {
+    const int hn = y + K / 2 - i;
+    if (hn < 0 || hn % s != 0) continue;
+    const int h = hn / s;
+    if (h >= ho) continue;
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      const int wn = x + K / 2 - j;
+      if (wn < 0 || wn % s != 0) continue;
+      const int w = wn / s;
+      if (w >= wo) continue;
+      const long m = ((long)n * ho + h) * wo + w;
+      const int ij = i * K + j;
+#pragma unroll 1
+      for (int t = 0; t < KK; ++t) {
+        float d[8];
+        unpack8(ldg16(dZ + (m * KK + t) * (long)C + v * 8), d);
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(wgk + ((long)t * KK + ij) * C + v * 8));
+        const float4 w1 = __ldg(reinterpret_cast<const float4*>(wgk + ((long)t * KK + ij) * C + v * 8 + 4));
+        acc[0] = fmaf(d[0], w0.x, acc[0]); acc[1] = fmaf(d[1], w0.y, acc[1]);
+        acc[2] = fmaf(d[2], w0.z, acc[2]); acc[3] = fmaf(d[3], w0.w, acc[3]);
+        acc[4] = fmaf(d[4], w1.x, acc[4]); acc[5] = fmaf(d[5], w1.y, acc[5]);
+        acc[6] = fmaf(d[6], w1.z, acc[6]); acc[7] = fmaf(d[7], w1.w, acc[7]);
+      }
+    }
+  }
+  *reinterpret_cast<uint4*>(dx + pix * lddx + v * 8) = pack8(acc);
+}
+
+// dwgk[t][ij][c] += Σ_m dZ[m][t*C+c] * x[n, h*s+i-k/2, w*s+j-k/2, c].  One thread per (v, t) and pixel lane.
+template <int K>
+__global__ void __launch_bounds__(256) rf_generate_wgrad_kernel(const __nv_bfloat16* __restrict__ dZ,
+                                                                const __nv_bfloat16* __restrict__ x, long ldx, int N,
+                                                                int H, int W, int V, int s, int ho, int wo,
+                                                                float* __restrict__ dwgk) {
+  constexpr int KK = K * K;
+  const int C = V * 8;
+  const long M = (long)N * ho * wo;
+  const long work = (long)V * KK;  // (v, t) pairs
+  const long T = (long)gridDim.x * blockDim.x;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  // thread layout: consecutive threads -> consecutive v (coalesced), then t, then pixel lane
+  const long lanes = T / work;
+  if (lanes == 0 || tid >= lanes * work) return;
+  const int v = (int)(tid % V);
+  const int t = (int)((tid / V) % KK);
+  const long pl = tid / work;
+  float acc[KK][8];
+#pragma unroll
+  for (int q = 0; q < KK; ++q)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[q][e] = 0.f;
+  for (long m = pl; m < M; m += lanes) {
+    const int w = (int)(m % wo), h = (int)((m / wo) % ho), n = (int)(m / ((long)wo * ho));
+    float d[8];
+    unpack8(ldg16(dZ + (m * KK + t) * (long)C + v * 8), d);
+#pragma unroll
+    for (int i = 0; i < K; ++i)
+#pragma unroll
+      for (int j = 0; j < K; ++j) {
+        const int yy = h * s + i - K / 2, xx = w * s + j - K / 2;
+        if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+        float f[8];
+        unpack8(ldg16(x + (((long)n * H + yy) * W + xx) * ldx + v * 8), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[i * K + j][e] = fmaf(d[e], f[e], acc[i * K + j][e]);
+      }
+  }
+#pragma unroll
+  for (int q = 0; q < KK; ++q)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) atomicAdd(&dwgk[((long)t * KK + q) * C + v * 8 + e], acc[q][e]);
+}
+
+struct RfGeo {
+  int N, H, W, C, K, s, ho, wo;
+};
+
+static int rf_check(const RfGeo& g, const char* what) {
+  LY_REQUIRE(g.N > 0 && g.H > 0 && g.W > 0, "%s: bad spatial size", what);
+  LY_REQUIRE(g.C > 0 && g.C % 8 == 0 && g.C <= 512, "%s: C=%d must be a multiple of 8 and <= 512", what, g.C);
+  LY_REQUIRE((g.K == 1 && g.s == 1) || (g.K == 3 && (g.s == 1 || g.s == 2)), "%s: k=%d s=%d unsupported", what, g.K,
+             g.s);
+  LY_REQUIRE(g.ho == (g.H + 2 * (g.K / 2) - g.K) / g.s + 1 && g.wo == (g.W + 2 * (g.K / 2) - g.K) / g.s + 1,
+             "%s: output size mismatch", what);
+  return LY_OK;
+}
+
+}  // namespace ly
+
+using namespace ly;
+
+#define LY_ALIGNED16(p) (reinterpret_cast<uintptr_t>(p) % 16 == 0)
+
+extern "C" int ly_rf_generate(const void* x, long ldx, int N, int H, int W, int C, int k, int s, int ho, int wo,
+                              const float* wgk, const float* scale, const float* shift, int act, void* G,
+                              ly_stream_t st) {
+  RfGeo g{N, H, W, C, k, s, ho, wo};
+  int rc = rf_check(g, "ly_rf_generate");
+  if (rc) return rc;
+  LY_REQUIRE(x && wgk && G && LY_ALIGNED16(x) && LY_ALIGNED16(G) && LY_ALIGNED16(wgk) && ldx % 8 == 0 && ldx >= C,
+             "ly_rf_generate: bad pointers / ld");
+  LY_REQUIRE((scale == nullptr) == (shift == nullptr), "ly_rf_generate: scale and shift go together");
+  const int V = C / 8;
+  const long total = (long)N * ho * wo * V;
+  if (k == 1)
+    rf_generate_kernel<1><<<ceil_div(total, 128), 128, 0, (cudaStream_t)st>>>(
+        (const __nv_bfloat16*)x, ldx, N, H, W, V, s, ho, wo, wgk, scale, shift, act, (__nv_bfloat16*)G);
+  else
+    rf_generate_kernel<3><<<ceil_div(total, 128), 128, 0, (cudaStream_t)st>>>(
+        (const __nv_bfloat16*)x, ldx, N, H, W, V, s, ho, wo, wgk, scale, shift, act, (__nv_bfloat16*)G);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_rf_attention(const void* G, int N, int ho, int wo, int C, int k, const float* wa, float* maps,
+                               int16_t* amax, float* att, ly_stream_t st) {
+  LY_REQUIRE(G && wa && maps && att && LY_ALIGNED16(G) && C % 8 == 0 && C > 0, "ly_rf_attention: bad args");
+  const int V = C / 8, KK = k * k;
+  const long M = (long)N * ho * wo;
+  rf_poolc_kernel<<<ceil_div(M * KK * 32, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)G, M, KK, k, V, ho,
+                                                                          wo, maps, amax);
+  LY_LAUNCH_CHECK();
+  const long total = (long)N * ho * k * wo * k;
+  rf_att_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(maps, N, ho * k, wo * k, wa, att);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_rf_gate(const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse,
+                          const float* att, void* A, ly_stream_t st) {
+  LY_REQUIRE(G && se && att && A && LY_ALIGNED16(G) && LY_ALIGNED16(A) && LY_ALIGNED16(se) && C % 8 == 0 &&
+                 ldse % 8 == 0,
+             "ly_rf_gate: bad args");
+  const int V = C / 8, KK = k * k;
+  const long M = (long)N * ho * wo;
+  rf_gate_kernel<<<ceil_div(M * KK * V, 256), 256, 0, (cudaStream_t)st>>>(
+      (const __nv_bfloat16*)G, M, KK, k, V, ho, wo, (const __nv_bfloat16*)se, ldse, att, (__nv_bfloat16*)A);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int wo, int C, int k, const void* se,
+                              long ldse, const float* att, void* dG, float* dse, float* datt, ly_stream_t st) {
+  LY_REQUIRE(dA && G && se && att && dG && dse && datt && C % 8 == 0 && C <= 512, "ly_rf_gate_bwd: bad args");
+  const int V = C / 8, KK = k * k;
+  const long per_img = (long)ho * wo * KK;
+  int bx = ceil_div(per_img, 8 * 16);  // 8 warps per block, ~16 rows per warp
+  const int cap = ceil_div((long)device_sm_count() * 8, N);
+  if (bx > cap) bx = cap;
+  if (bx < 1) bx = 1;
+  dim3 grid(bx, N);
+  rf_gate_bwd_kernel<<<grid, 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)dA, (const __nv_bfloat16*)G, KK, k, V,
+                                                        ho, wo, (const __nv_bfloat16*)se, ldse, att,
+                                                        (__nv_bfloat16*)dG, dse, datt);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_rf_attention_bwd(const float* datt, const float* att, const float* maps, const int16_t* amax, int N,
+                                   int ho, int wo, int C, int k, const float* wa, float* dmaps, float* dwa, void* dG,
+                                   ly_stream_t st) {
+  LY_REQUIRE(datt && att && maps && amax && wa && dmaps && dwa && dG && C % 8 == 0, "ly_rf_attention_bwd: bad args");
+  const int V = C / 8, KK = k * k;
+  const long M = (long)N * ho * wo;
+  const long total = (long)N * ho * k * wo * k;
+  rf_att_bwd_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(datt, att, maps, N, ho * k, wo * k, wa, dmaps,
+                                                                       dwa);
+  LY_LAUNCH_CHECK();
+  rf_poolc_bwd_kernel<<<ceil_div(M * KK * V, 256), 256, 0, (cudaStream_t)st>>>((__nv_bfloat16*)dG, M, KK, k, V, ho, wo,
+                                                                              dmaps, amax);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_rf_generate_bwd(const void* dZ, const void* x, long ldx, int N, int H, int W, int C, int k, int s,
+                                  int ho, int wo, const float* wgk, const float* extra, void* dx, long lddx,
+                                  float* dwgk, ly_stream_t st) {
+  RfGeo g{N, H, W, C, k, s, ho, wo};
+  int rc = rf_check(g, "ly_rf_generate_bwd");
+  if (rc) return rc;
+  LY_REQUIRE(dZ && x && wgk && LY_ALIGNED16(dZ) && LY_ALIGNED16(x), "ly_rf_generate_bwd: bad pointers");
+  const int V = C / 8, KK = k * k;
+  if (dx != nullptr) {
+    LY_REQUIRE(LY_ALIGNED16(dx) && lddx % 8 == 0 && lddx >= C, "ly_rf_generate_bwd: bad dx");
+    const long total = (long)N * H * W * V;
+    if (k == 1)
+      rf_generate_dx_kernel<1><<<ceil_div(total, 128), 128, 0, (cudaStream_t)st>>>(
+          (const __nv_bfloat16*)dZ, N, H, W, V, s, ho, wo, wgk, extra, (__nv_bfloat16*)dx, lddx);
+    else
+      rf_generate_dx_kernel<3><<<ceil_div(total, 128), 128, 0, (cudaStream_t)st>>>(
+          (const __nv_bfloat16*)dZ, N, H, W, V, s, ho, wo, wgk, extra, (__nv_bfloat16*)dx, lddx);
+    LY_LAUNCH_CHECK();
+  }
+  if (dwgk != nullptr) {
+    const long work = (long)V * KK;
+    long lanes = ((long)device_sm_count() * 4 * 256) / work;
+    if (lanes < 1) lanes = 1;
+    const int grid = ceil_div(lanes * work, 256);
+    if (k == 1)
+      rf_generate_wgrad_kernel<1><<<grid, 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x,
+                                                                      ldx, N, H, W, V, s, ho, wo, dwgk);
+    else
+      rf_generate_wgrad_kernel<3><<<grid, 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x,
+                                                                      ldx, N, H, W, V, s, ho, wo, dwgk);
+    LY_LAUNCH_CHECK();
+  }
+  return LY_OK;
+}

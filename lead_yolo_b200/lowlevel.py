@@ -10,6 +10,32 @@ from . import _lib
 from ._lib import ConvDesc, check, lib, ptr, stream_ptr
 
 CL = torch.channels_last
+COUNT = [0]        # kernels launched through the C-ABI (bench.py: gpu_launches)
+PROFILE = None     # when a list: (entry point, start event, end event, algorithmic bytes, flops) per call
+_LAUNCHES = {"ly_bn_act_bwd": 2, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 2}
+
+
+class _Prof:
+    __slots__ = ("name", "nbytes", "flops", "e0")
+
+    def __init__(self, name, nbytes=0.0, flops=0.0):
+        self.name, self.nbytes, self.flops = name, nbytes, flops
+
+    def __enter__(self):
+        COUNT[0] += _LAUNCHES.get(self.name, 1)
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *a):
+        if PROFILE is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            PROFILE.append((self.name, self.e0, e1, self.nbytes, self.flops))
+        return False
+
+
 ACT = {"none": 0, "relu": 1, "silu": 2, "hswish": 3, "sigmoid": 4}
 
 
@@ -106,5 +132,97 @@ def conv_gemm(srcs, w_packed, cout, k=1, stride=1, pad=0, scale=None, shift=None
         assert tuple(residual.shape) == oshape
         d.residual = residual.data_ptr()
         d.res_ld = rld
-    check(lib().ly_conv_fwd(C.byref(d), stream_ptr()), "ly_conv_fwd")
+    m_out = out.numel() // out.shape[1]
+    cin = sum(int(x.shape[1]) for x in keep[:len(srcs)])
+    nbytes = sum(x.numel() * 2 for x in keep) + out.numel() * out.element_size() + w_packed.numel() * 2
+    with _Prof("ly_conv_fwd", nbytes, 2.0 * (n * ho * wo) * cin * k * k * cout):
+        check(lib().ly_conv_fwd(C.byref(d), stream_ptr()), "ly_conv_fwd")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Generic typed call into the C-ABI.  Signature letters: p = device pointer (torch tensor or None),
+# i = int, l = long, f = float, s = stream (appended automatically).
+# ---------------------------------------------------------------------------------------------------------
+_SIGS = {
+    "ly_col_stats": "pllipp",
+    "ly_bn_finalize": "ppilffpppppppp",
+    "ly_bn_fold": "ifppppppppp",
+    "ly_scale_shift_act": "pllippipl",
+    "ly_bn_act_bwd": "plpllippppiipppl",
+    "ly_act_bwd_from_out": "plplliipl",
+    "ly_stem_fwd": "piiiiipppfpl",
+    "ly_stem_wgrad": "piiiiiplfp",
+    "ly_maxpool5_fwd": "pliiiiplp",
+    "ly_maxpool5_bwd": "plpiiiipli",
+    "ly_copy_upsample": "pliiiiipl",
+    "ly_downsum2": "pliiiipl",
+    "ly_gap": "pliiipl",
+    "ly_ca_pool": "pliiiipl",
+    "ly_ca_apply": "plpliiiipl",
+    "ly_ca_gate_grad": "plplpliiiipl",
+    "ly_ca_pool_bwd": "pliiiipl",
+    "ly_rf_generate": "pliiiiiiiipppip",
+    "ly_rf_attention": "piiiiipppp",
+    "ly_rf_gate": "piiiiiplpp",
+    "ly_rf_gate_bwd": "ppiiiiiplpppp",
+    "ly_rf_attention_bwd": "ppppiiiiipppp",
+    "ly_rf_generate_bwd": "ppliiiiiiiippplp",
+}
+_CT = {"p": C.c_void_p, "i": C.c_int, "l": C.c_long, "f": C.c_float}
+_prepared = {}
+
+
+def call(name, *args):
+    fn = _prepared.get(name)
+    sig = _SIGS[name]
+    if fn is None:
+        fn = getattr(lib(), name)
+        fn.argtypes = [_CT[ch] for ch in sig] + [C.c_void_p]
+        fn.restype = C.c_int
+        _prepared[name] = fn
+    assert len(args) == len(sig), f"{name}: expected {len(sig)} args, got {len(args)}"
+    conv = []
+    for ch, a in zip(sig, args):
+        if ch == "p":
+            conv.append(None if a is None else a.data_ptr())
+        elif ch == "f":
+            conv.append(float(a))
+        else:
+            conv.append(int(a))
+    nbytes = 0.0
+    if PROFILE is not None:
+        nbytes = float(sum(a.numel() * a.element_size() for a in args if isinstance(a, torch.Tensor)))
+    with _Prof(name, nbytes, 0.0):
+        check(fn(*conv, torch.cuda.current_stream().cuda_stream), name)
+
+
+def conv_wgrad(srcs, dz, cout, k=1, stride=1, pad=0):
+    """fp32 [Cout, Kp] packed weight gradient of conv(cat(srcs)) given the output gradient dz (bf16 NHWC)."""
+    from .packing import packed_k
+    d = ConvDesc()
+    keep = []
+    n, _, h, w = srcs[0].shape
+    d.n_src = len(srcs)
+    for i, s in enumerate(srcs):
+        s, ld = as_nhwc(s)
+        keep.append(s)
+        d.src[i] = s.data_ptr()
+        d.src_c[i] = s.shape[1]
+        d.src_ld[i] = ld
+    d.N, d.H, d.W = n, h, w
+    d.kh = d.kw = k
+    d.stride, d.pad = stride, pad
+    d.Cout = cout
+    dz, dld = as_nhwc(dz)
+    kp = packed_k([s.shape[1] for s in srcs], k, k, patch=(stride == k and k > 1))
+    dw = torch.zeros((cout, kp), dtype=torch.float32, device=dz.device)
+    fn = lib().ly_conv_wgrad
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p]
+    fn.restype = C.c_int
+    cin = sum(int(x.shape[1]) for x in keep)
+    nbytes = sum(x.numel() * 2 for x in keep) + dz.numel() * 2 + dw.numel() * 4
+    with _Prof("ly_conv_wgrad", nbytes, 2.0 * (dz.numel() // dz.shape[1]) * cin * k * k * cout):
+        check(fn(C.byref(d), dz.data_ptr(), dld, dw.data_ptr(), torch.cuda.current_stream().cuda_stream),
+              "ly_conv_wgrad")
+    return dw

@@ -1,0 +1,497 @@
+"""Primitive operators of the LEAD-YOLO hot path as torch.autograd.Functions over the C-ABI kernels.
+
+Every tensor that crosses these functions is a logical-NCHW, channels_last (NHWC in memory) bf16 tensor.
+Parameters stay fp32 `nn.Parameter`s owned by stock submodules; packed bf16 copies for the tensor
+cores are derived per call (training) or cached per parameter version (inference).
+"""
+from __future__ import annotations
+
+import weakref
+
+import torch
+
+from . import lowlevel as ll
+from .packing import pack_conv_weight, unpack_conv_weight
+
+BF16 = torch.bfloat16
+CL = torch.channels_last
+
+# ---------------------------------------------------------------------------------------------------------
+# small caches (never stored on nn.Module instances: modules stay picklable / deepcopy-able)
+# ---------------------------------------------------------------------------------------------------------
+_cache = {}
+
+
+def cached(key_tensors, tag, builder):
+    """Memoise `builder()` on the identity + version of `key_tensors` (inference-time weight packing)."""
+    key = (tag,) + tuple(id(t) for t in key_tensors)
+    ver = tuple((t._version, t.data_ptr()) for t in key_tensors)
+    hit = _cache.get(key)
+    if hit is not None and hit[0] == ver and all(r() is t for r, t in zip(hit[1], key_tensors)):
+        return hit[2]
+    val = builder()
+    if len(_cache) > 4096:
+        _cache.clear()
+    _cache[key] = (ver, [weakref.ref(t) for t in key_tensors], val)
+    return val
+
+
+def to_act(x: torch.Tensor) -> torch.Tensor:
+    """Any float NCHW tensor -> bf16 channels_last activation."""
+    if x.dtype == BF16 and ll.pixel_ld(x) is not None:
+        return x
+    return x.to(dtype=BF16, memory_format=CL)
+
+
+def _rows(x):
+    n, c, h, w = x.shape
+    return n * h * w
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Convolution (implicit GEMM) with autograd
+# ---------------------------------------------------------------------------------------------------------
+def _geom(k, s):
+    patch = (s == k and k > 1)
+    pad = 0 if (patch or k == 1) else k // 2
+    return patch, pad
+
+
+def _dgrad_weight(w_s: torch.Tensor, k: int, patch: bool):
+    """OIHW weight of the convolution that maps dZ -> dX_s ('Backward adds')."""
+    if patch:
+        cout, cs = w_s.shape[:2]
+        # GEMM columns (ky, kx, c), K = Cout
+        return w_s.permute(2, 3, 1, 0).reshape(k * k * cs, cout, 1, 1)
+    if k == 1:
+        return w_s.transpose(0, 1)
+    return w_s.flip(2, 3).transpose(0, 1)
+
+
+class ConvFn(torch.autograd.Function):
+    """y = act(conv(cat(srcs), weight) + bias) (+ residual).  act in {none, relu, sigmoid} (derivative from y)."""
+
+    @staticmethod
+    def forward(ctx, weight, bias, residual, k, s, act, out_fp32, *srcs):
+        patch, pad = _geom(k, s)
+        srcs = [to_act(x) for x in srcs]
+        chans = [x.shape[1] for x in srcs]
+        cout = weight.shape[0]
+        wp = pack_conv_weight(weight, chans, patch=patch)
+        shift = bias.detach().float().contiguous() if bias is not None else None
+        res = to_act(residual) if residual is not None else None
+        y = ll.conv_gemm(srcs, wp, cout, k=k, stride=s, pad=pad, shift=shift, act=act, residual=res,
+                         out_fp32=out_fp32)
+        ctx.cfg = (k, s, act, patch, pad, chans, out_fp32, bias is not None, residual is not None)
+        need_y = act != "none"
+        ctx.save_for_backward(weight, y if need_y else None, *srcs)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        k, s, act, patch, pad, chans, out_fp32, has_bias, has_res = ctx.cfg
+        weight, y, *srcs = ctx.saved_tensors
+        cout = weight.shape[0]
+        dy = to_act(dy)
+        d_res = dy if (has_res and ctx.needs_input_grad[2]) else None
+        if act != "none":
+            assert not has_res, "activation + residual backward is not needed on this path"
+            dz = torch.empty_like(dy, memory_format=CL)
+            ll.call("ly_act_bwd_from_out", dy, ll.pixel_ld(dy), y, ll.pixel_ld(y), _rows(dy), cout, ll.ACT[act],
+                    dz, ll.pixel_ld(dz))
+        else:
+            dz = dy
+        # channel counts that are not a multiple of 8 (Detect: 18) are zero-padded for the tensor-core kernels
+        cpad = (cout + 7) // 8 * 8
+        if cpad != cout:
+            dzp = dz.new_zeros((dz.shape[0], cpad, dz.shape[2], dz.shape[3])).contiguous(memory_format=CL)
+            dzp[:, :cout] = dz
+            dz = dzp
+        d_bias = None
+        if has_bias and ctx.needs_input_grad[1]:
+            sums = torch.zeros(cpad, dtype=torch.float32, device=dz.device)
+            ll.call("ly_col_stats", dz, ll.pixel_ld(dz), _rows(dz), cpad, sums, None)
+            d_bias = sums[:cout]
+        wf = weight.detach().float()
+        if cpad != cout:
+            wf = torch.nn.functional.pad(wf, (0, 0, 0, 0, 0, 0, 0, cpad - cout))
+        d_srcs = []
+        off = 0
+        for i, x in enumerate(srcs):
+            cs = chans[i]
+            if ctx.needs_input_grad[7 + i]:
+                wd = _dgrad_weight(wf[:, off:off + cs], k, patch)
+                if patch:
+                    wdp = pack_conv_weight(wd, [cpad])
+                    dx = ll.conv_gemm([dz], wdp, k * k * cs, k=1, patch_scatter=(k, cs))
+                else:
+                    wdp = pack_conv_weight(wd, [cpad])
+                    dx = ll.conv_gemm([dz], wdp, cs, k=k, stride=1, pad=pad)
+                d_srcs.append(dx)
+            else:
+                d_srcs.append(None)
+            off += cs
+        d_w = None
+        if ctx.needs_input_grad[0]:
+            dwp = ll.conv_wgrad(srcs, dz, cpad, k=k, stride=s, pad=pad)
+            d_w = unpack_conv_weight(dwp, cpad, chans, k, k, patch=patch)[:cout].to(weight.dtype)
+        return (d_w, d_bias, d_res, None, None, None, None, *d_srcs)
+
+
+def conv(srcs, weight, bias=None, k=1, s=1, act="none", residual=None, out_fp32=False):
+    return ConvFn.apply(weight, bias, residual, k, s, act, out_fp32, *srcs)
+
+
+def conv_infer(srcs, wp, cout, k=1, s=1, scale=None, shift=None, act="none", residual=None, out=None,
+               out_fp32=False):
+    """Inference-only convolution with pre-packed weights and folded BN scale/shift (no autograd)."""
+    patch, pad = _geom(k, s)
+    return ll.conv_gemm([to_act(x) for x in srcs], wp, cout, k=k, stride=s, pad=pad, scale=scale, shift=shift,
+                        act=act, residual=None if residual is None else to_act(residual), out=out,
+                        out_fp32=out_fp32)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# BatchNorm (+ activation)
+# ---------------------------------------------------------------------------------------------------------
+class BnActFn(torch.autograd.Function):
+    """y = act(BN(z)); batch statistics + running-stat update when `training`, running statistics otherwise."""
+
+    @staticmethod
+    def forward(ctx, z, gamma, beta, running_mean, running_var, eps, momentum, act, training):
+        z = to_act(z)
+        c = z.shape[1]
+        m = _rows(z)
+        dev = z.device
+        stats = torch.empty((4, c), dtype=torch.float32, device=dev)  # mean, rstd, scale, shift
+        g32, b32 = gamma.detach().float(), beta.detach().float()
+        if training:
+            acc = torch.zeros((2, c), dtype=torch.float32, device=dev)
+            ll.call("ly_col_stats", z, ll.pixel_ld(z), m, c, acc[0], acc[1])
+            ll.call("ly_bn_finalize", acc[0], acc[1], c, m, eps, momentum, g32, b32, running_mean, running_var,
+                    stats[0], stats[1], stats[2], stats[3])
+        else:
+            ll.call("ly_bn_fold", c, eps, g32, b32, running_mean, running_var, None, stats[0], stats[1], stats[2],
+                    stats[3])
+        y = torch.empty_like(z, memory_format=CL)
+        ll.call("ly_scale_shift_act", z, ll.pixel_ld(z), m, c, stats[2], stats[3], ll.ACT[act], y, ll.pixel_ld(y))
+        ctx.cfg = (act, training)
+        ctx.save_for_backward(z, stats)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        act, training = ctx.cfg
+        z, stats = ctx.saved_tensors
+        dy = to_act(dy)
+        c = z.shape[1]
+        m = _rows(z)
+        s12 = torch.zeros((2, c), dtype=torch.float32, device=z.device)
+        dz = torch.empty_like(z, memory_format=CL)
+        ll.call("ly_bn_act_bwd", dy, ll.pixel_ld(dy), z, ll.pixel_ld(z), m, c, stats[2], stats[3], stats[0],
+                stats[1], ll.ACT[act], 1 if training else 0, s12[0], s12[1], dz, ll.pixel_ld(dz))
+        return dz, s12[1], s12[0], None, None, None, None, None, None
+
+
+def bn_act(z, bn, act="none", gamma=None, beta=None, rmean=None, rvar=None):
+    """Apply nn.BatchNorm2d `bn` (+activation) with reference semantics, reading eps/momentum from the module."""
+    training = bn.training or bn.running_mean is None
+    gamma = bn.weight if gamma is None else gamma
+    beta = bn.bias if beta is None else beta
+    rmean = bn.running_mean if rmean is None else rmean
+    rvar = bn.running_var if rvar is None else rvar
+    mom = 0.1 if bn.momentum is None else bn.momentum
+    y = BnActFn.apply(z, gamma, beta, rmean, rvar, float(bn.eps), float(mom), act, training)
+    if training and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked += 1
+    return y
+
+
+def bn_fold(bn, conv_bias=None, perm=None):
+    """(scale, shift) of an eval-mode BatchNorm folded behind a convolution (cached per parameter version)."""
+    keys = [bn.weight, bn.bias, bn.running_mean, bn.running_var] + ([conv_bias] if conv_bias is not None else [])
+
+    def build():
+        c = bn.weight.numel()
+        g, b, rm, rv = (t.detach().float() for t in (bn.weight, bn.bias, bn.running_mean, bn.running_var))
+        cb = conv_bias.detach().float() if conv_bias is not None else None
+        if perm is not None:
+            g, b, rm, rv = g[perm].contiguous(), b[perm].contiguous(), rm[perm].contiguous(), rv[perm].contiguous()
+        out = torch.empty((2, c), dtype=torch.float32, device=g.device)
+        ll.call("ly_bn_fold", c, float(bn.eps), g, b, rm, rv, cb, None, None, out[0], out[1])
+        return out[0], out[1]
+
+    return cached(keys, ("bnfold", perm is not None), build)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Stem
+# ---------------------------------------------------------------------------------------------------------
+class StemFn(torch.autograd.Function):
+    """4x4/s4 patch embedding straight from the NCHW image (fp32, or uint8 with the /255 folded in)."""
+
+    @staticmethod
+    def forward(ctx, img, weight, scale, shift):
+        assert img.dim() == 4 and img.shape[1] == 3 and tuple(weight.shape[1:]) == (3, 4, 4)
+        is_u8 = img.dtype == torch.uint8
+        if not is_u8 and img.dtype != torch.float32:
+            img = img.float()
+        img = img.contiguous()
+        n, _, h, w = img.shape
+        cout = weight.shape[0]
+        wk = weight.detach().float().reshape(cout, 48).t().contiguous()
+        out = ll.empty_cl(n, cout, h // 4, w // 4, device=img.device)
+        in_scale = 1.0 / 255.0 if is_u8 else 1.0
+        ll.call("ly_stem_fwd", img, 1 if is_u8 else 0, n, h, w, cout, wk, scale, shift, in_scale, out, cout)
+        ctx.save_for_backward(img)
+        ctx.cfg = (is_u8, in_scale, cout, weight.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dz):
+        (img,) = ctx.saved_tensors
+        is_u8, in_scale, cout, wdt = ctx.cfg
+        dz = to_act(dz)
+        n, _, h, w = img.shape
+        dwk = torch.zeros((48, cout), dtype=torch.float32, device=dz.device)
+        ll.call("ly_stem_wgrad", img, 1 if is_u8 else 0, n, h, w, cout, dz, ll.pixel_ld(dz), in_scale, dwk)
+        return None, dwk.t().reshape(cout, 3, 4, 4).to(wdt), None, None
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Pooling / resampling
+# ---------------------------------------------------------------------------------------------------------
+class MaxPool5Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = to_act(x)
+        n, c, h, w = x.shape
+        y = torch.empty_like(x, memory_format=CL)
+        need = x.requires_grad and torch.is_grad_enabled()
+        idx = torch.empty((n * h * w, c), dtype=torch.uint8, device=x.device)
+        ll.call("ly_maxpool5_fwd", x, ll.pixel_ld(x), n, h, w, c, y, c, idx)
+        ctx.save_for_backward(idx)
+        ctx.shape = (n, c, h, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        n, c, h, w = ctx.shape
+        dy = to_act(dy)
+        dx = ll.empty_cl(n, c, h, w, device=dy.device)
+        ll.call("ly_maxpool5_bwd", dy, ll.pixel_ld(dy), idx, n, h, w, c, dx, c, 0)
+        return dx
+
+
+def maxpool5_into(x, out):
+    """Inference: 5x5 max pool of x written into `out` (a channel slice of a wider NHWC buffer)."""
+    n, c, h, w = x.shape
+    ll.call("ly_maxpool5_fwd", x, ll.pixel_ld(x), n, h, w, c, out, ll.pixel_ld(out), None)
+    return out
+
+
+class UpsampleCatFn(torch.autograd.Function):
+    """cat([up2x?(a), b, ...], dim=1) materialised by slice copies; `ups` marks the tensors to upsample 2x."""
+
+    @staticmethod
+    def forward(ctx, ups, *xs):
+        xs = [to_act(x) for x in xs]
+        n = xs[0].shape[0]
+        h = xs[0].shape[2] * (2 if ups[0] else 1)
+        w = xs[0].shape[3] * (2 if ups[0] else 1)
+        ctot = sum(x.shape[1] for x in xs)
+        out = ll.empty_cl(n, ctot, h, w, device=xs[0].device)
+        off = 0
+        for x, u in zip(xs, ups):
+            c = x.shape[1]
+            ll.call("ly_copy_upsample", x, ll.pixel_ld(x), n, x.shape[2], x.shape[3], c, 2 if u else 1,
+                    out[:, off:off + c], ctot)
+            off += c
+        ctx.cfg = (ups, [x.shape for x in xs])
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        ups, shapes = ctx.cfg
+        dy = to_act(dy)
+        grads, off = [], 0
+        for u, shp in zip(ups, shapes):
+            c = shp[1]
+            sl = dy[:, off:off + c]
+            if u:
+                dx = ll.empty_cl(*shp, device=dy.device)
+                ll.call("ly_downsum2", sl, ll.pixel_ld(sl), shp[0], shp[2], shp[3], c, dx, c)
+                grads.append(dx)
+            else:
+                grads.append(sl)
+            off += c
+        return (None, *grads)
+
+
+class GapFn(torch.autograd.Function):
+    """Global average pool -> (N, C, 1, 1) bf16."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = to_act(x)
+        n, c, h, w = x.shape
+        out = ll.empty_cl(n, c, 1, 1, device=x.device)
+        ll.call("ly_gap", x, ll.pixel_ld(x), n, h * w, c, out, c)
+        ctx.shape = (n, c, h, w)
+        return out
+
+    @staticmethod
+    def backward(ctx, d):
+        n, c, h, w = ctx.shape
+        return (d.float() / float(h * w)).to(BF16).expand(n, c, h, w)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CoordAtt pieces
+# ---------------------------------------------------------------------------------------------------------
+class CaPoolFn(torch.autograd.Function):
+    """x (N,C,H,W) -> pooled "HW rows" matrix as a (1, C, N*H + N*W, 1) activation."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = to_act(x)
+        n, c, h, w = x.shape
+        p = ll.empty_cl(1, c, n * (h + w), 1, device=x.device)
+        ll.call("ly_ca_pool", x, ll.pixel_ld(x), n, h, w, c, p, c)
+        ctx.shape = (n, c, h, w)
+        return p
+
+    @staticmethod
+    def backward(ctx, dp):
+        n, c, h, w = ctx.shape
+        dp = to_act(dp)
+        dx = ll.empty_cl(n, c, h, w, device=dp.device)
+        ll.call("ly_ca_pool_bwd", dp, ll.pixel_ld(dp), n, h, w, c, dx, c)
+        return dx
+
+
+class CaApplyFn(torch.autograd.Function):
+    """out = x * a_h * a_w with the gates in "HW rows" layout."""
+
+    @staticmethod
+    def forward(ctx, x, gates):
+        x, gates = to_act(x), to_act(gates)
+        n, c, h, w = x.shape
+        out = torch.empty_like(x, memory_format=CL)
+        ll.call("ly_ca_apply", x, ll.pixel_ld(x), gates, ll.pixel_ld(gates), n, h, w, c, out, c)
+        ctx.save_for_backward(x, gates)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gates = ctx.saved_tensors
+        dy = to_act(dy)
+        n, c, h, w = x.shape
+        dx = torch.empty_like(x, memory_format=CL)
+        ll.call("ly_ca_apply", dy, ll.pixel_ld(dy), gates, ll.pixel_ld(gates), n, h, w, c, dx, c)
+        dg = torch.empty_like(gates, memory_format=CL)
+        ll.call("ly_ca_gate_grad", x, ll.pixel_ld(x), dy, ll.pixel_ld(dy), gates, ll.pixel_ld(gates), n, h, w, c,
+                dg, c)
+        return dx, dg
+
+
+# ---------------------------------------------------------------------------------------------------------
+# RFCBAM pieces
+# ---------------------------------------------------------------------------------------------------------
+def rf_out_size(h, w, k, s):
+    p = k // 2
+    return (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1
+
+
+def rf_pack_generate_weight(wg, c, k):
+    """generate.0.weight [c*k*k, 1, k, k] -> fp32 [k*k (t)][k*k (ij)][c]."""
+    return wg.detach().float().reshape(c, k * k, k * k).permute(1, 2, 0).contiguous()
+
+
+def rf_channel_perm(c, k, device):
+    """index p with G-column (t*c + ch) <- reference channel (ch*k*k + t)."""
+    t = torch.arange(k * k, device=device).view(-1, 1)
+    ch = torch.arange(c, device=device).view(1, -1)
+    return (ch * (k * k) + t).reshape(-1)
+
+
+class RfGenerateFn(torch.autograd.Function):
+    """Depthwise receptive-field features z (N, k*k*C, ho, wo), channel t*C+c; optional fused affine+act."""
+
+    @staticmethod
+    def forward(ctx, x, wg, k, s, scale, shift, act):
+        x = to_act(x)
+        n, c, h, w = x.shape
+        ho, wo = rf_out_size(h, w, k, s)
+        wgk = rf_pack_generate_weight(wg, c, k)
+        g = ll.empty_cl(n, k * k * c, ho, wo, device=x.device)
+        ll.call("ly_rf_generate", x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, scale, shift, ll.ACT[act], g)
+        ctx.save_for_backward(x, wgk)
+        ctx.cfg = (k, s, ho, wo, wg.dtype, scale is not None)
+        return g
+
+    @staticmethod
+    def backward(ctx, dz):
+        x, wgk = ctx.saved_tensors
+        k, s, ho, wo, wdt, fused = ctx.cfg
+        assert not fused, "fused affine epilogue is inference-only"
+        dz = to_act(dz).contiguous(memory_format=CL)
+        n, c, h, w = x.shape
+        dx = ll.empty_cl(n, c, h, w, device=x.device) if ctx.needs_input_grad[0] else None
+        dwgk = torch.zeros_like(wgk) if ctx.needs_input_grad[1] else None
+        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, dx, c, dwgk)
+        dwg = None
+        if dwgk is not None:
+            dwg = dwgk.permute(2, 0, 1).reshape(c * k * k, 1, k, k).to(wdt)
+        return dx, dwg, None, None, None, None, None
+
+
+class RfGateAttFn(torch.autograd.Function):
+    """A = G * se[n,c] * sigmoid(conv3x3([max_c G; mean_c G])) — rfa.py:124-128 on the unfolded grid."""
+
+    @staticmethod
+    def forward(ctx, g, se, wa, k):
+        g, se = to_act(g), to_act(se)
+        n, kkc, ho, wo = g.shape
+        c = kkc // (k * k)
+        dev = g.device
+        maps = torch.empty((n, ho * k, wo * k, 2), dtype=torch.float32, device=dev)
+        amax = torch.empty((n, ho * k, wo * k), dtype=torch.int16, device=dev)
+        att = torch.empty((n, ho * k, wo * k), dtype=torch.float32, device=dev)
+        wa32 = wa.detach().float().reshape(18).contiguous()
+        ll.call("ly_rf_attention", g, n, ho, wo, c, k, wa32, maps, amax, att)
+        a = torch.empty_like(g, memory_format=CL)
+        ll.call("ly_rf_gate", g, n, ho, wo, c, k, se, ll.pixel_ld(se), att, a)
+        ctx.save_for_backward(g, se, wa32, maps, amax, att)
+        ctx.cfg = (k, c, wa.dtype)
+        return a
+
+    @staticmethod
+    def backward(ctx, da):
+        g, se, wa32, maps, amax, att = ctx.saved_tensors
+        k, c, wdt = ctx.cfg
+        da = to_act(da).contiguous(memory_format=CL)
+        n, kkc, ho, wo = g.shape
+        dev = g.device
+        dg = torch.empty_like(g, memory_format=CL)
+        dse = torch.zeros((n, c), dtype=torch.float32, device=dev)
+        datt = torch.empty_like(att)
+        ll.call("ly_rf_gate_bwd", da, g, n, ho, wo, c, k, se, ll.pixel_ld(se), att, dg, dse, datt)
+        dmaps = torch.empty_like(maps)
+        dwa = torch.zeros(18, dtype=torch.float32, device=dev)
+        ll.call("ly_rf_attention_bwd", datt, att, maps, amax, n, ho, wo, c, k, wa32, dmaps, dwa, dg)
+        return dg, dse.to(BF16).view(n, c, 1, 1), dwa.view(1, 2, 3, 3).to(wdt), None
+
+
+def rf_gate_att_infer(g, se, wa, k):
+    n, kkc, ho, wo = g.shape
+    c = kkc // (k * k)
+    dev = g.device
+    maps = torch.empty((n, ho * k, wo * k, 2), dtype=torch.float32, device=dev)
+    att = torch.empty((n, ho * k, wo * k), dtype=torch.float32, device=dev)
+    wa32 = cached([wa], "wa32", lambda: wa.detach().float().reshape(18).contiguous())
+    ll.call("ly_rf_attention", g, n, ho, wo, c, k, wa32, maps, None, att)
+    a = torch.empty_like(g, memory_format=CL)
+    ll.call("ly_rf_gate", g, n, ho, wo, c, k, se, ll.pixel_ld(se), att, a)
+    return a
