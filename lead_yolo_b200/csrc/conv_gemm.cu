@@ -44,6 +44,69 @@ struct alignas(64) ConvGemmParams {
   KEntry sched[kMaxK];
 };
 
+// One epilogue thread = one output pixel (TMEM lane).  Columns are drained 32 at a time (two tcgen05.ld in flight).
+template <int ACT>
+__device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t trow, bool valid, int n, int h, int w,
+                                              long pix, int n0, const float* s_scale, const float* s_shift) {
+  const int kC = p.patch_k * p.patch_c;
+  for (int c0 = 0; c0 < p.BN; c0 += 32) {
+    uint32_t acc[2][16];
+    __syncwarp();
+    tmem_ld16(trow + (uint32_t)c0, acc[0]);
+    if (c0 + 16 < p.BN) tmem_ld16(trow + (uint32_t)(c0 + 16), acc[1]);
+    tmem_ld_wait();
+    if (!valid) continue;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int cl = c0 + g * 8;       // column inside the tile
+      const int c = n0 + cl;           // output channel
+      if (cl >= p.BN || c >= p.Cout) break;
+      const int nv = min(8, p.Cout - c);
+      long o_off, r_off;
+      if (p.patch_k > 0) {
+        const int ky = c / kC, rem = c - ky * kC;
+        const long fp = ((long)n * p.Hout * p.patch_k + (long)h * p.patch_k + ky) * ((long)p.Wout * p.patch_k) +
+                        (long)w * p.patch_k;
+        o_off = fp * p.out_ld + rem;
+        r_off = fp * p.res_ld + rem;
+      } else {
+        o_off = pix * p.out_ld + c;
+        r_off = pix * p.res_ld + c;
+      }
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        v[j] = act_apply_t<ACT>(fmaf(__uint_as_float(acc[g >> 1][(g & 1) * 8 + j]), s_scale[cl + j], s_shift[cl + j]));
+      if (p.residual != nullptr) {
+        if (p.res_vec_ok && nv == 8) {
+          float rr[8];
+          unpack8(*reinterpret_cast<const uint4*>(p.residual + r_off), rr);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] += rr[j];
+        } else {
+          for (int j = 0; j < nv; ++j) v[j] += __bfloat162float(p.residual[r_off + j]);
+        }
+      }
+      if (p.out_fp32) {
+        float* o = reinterpret_cast<float*>(p.out) + o_off;
+        if (p.vec_ok && nv == 8) {
+          reinterpret_cast<float4*>(o)[0] = make_float4(v[0], v[1], v[2], v[3]);
+          reinterpret_cast<float4*>(o)[1] = make_float4(v[4], v[5], v[6], v[7]);
+        } else {
+          for (int j = 0; j < nv; ++j) o[j] = v[j];
+        }
+      } else {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + o_off;
+        if (p.vec_ok && nv == 8) {
+          *reinterpret_cast<uint4*>(o) = pack8(v);
+        } else {
+          for (int j = 0; j < nv; ++j) o[j] = __float2bfloat16(v[j]);
+        }
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(192) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[kMaxStages];
@@ -139,66 +202,15 @@ __global__ void __launch_bounds__(192) conv_gemm_kernel(const __grid_constant__ 
     const int h = h0 + hh, w = w0 + ww;
     const bool valid = (r < p.Wt * p.Ht) && (h < p.Hout) && (w < p.Wout);
     const long pix = ((long)n * p.Hout + h) * p.Wout + w;
-    const int kC = p.patch_k * p.patch_c;
-
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after_sync();
-
-    for (int c0 = 0; c0 < p.BN; c0 += 16) {
-      uint32_t acc[16];
-      __syncwarp();
-      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, acc);
-      tmem_ld_wait();
-#pragma unroll
-      for (int g = 0; g < 2; ++g) {
-        if (!valid) break;
-        const int c = n0 + c0 + g * 8;
-        if (c >= p.Cout) break;
-        const int nv = min(8, p.Cout - c);
-        long o_off, r_off;
-        if (p.patch_k > 0) {
-          const int ky = c / kC, rem = c - ky * kC;
-          const long fp = ((long)n * p.Hout * p.patch_k + (long)h * p.patch_k + ky) * ((long)p.Wout * p.patch_k) +
-                          (long)w * p.patch_k;
-          o_off = fp * p.out_ld + rem;
-          r_off = fp * p.res_ld + rem;
-        } else {
-          o_off = pix * p.out_ld + c;
-          r_off = pix * p.res_ld + c;
-        }
-        float v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int ci = c0 + g * 8 + j;
-          v[j] = act_apply(fmaf(__uint_as_float(acc[g * 8 + j]), s_scale[ci], s_shift[ci]), p.act);
-        }
-        if (p.residual != nullptr) {
-          if (p.res_vec_ok && nv == 8) {
-            float rr[8];
-            unpack8(*reinterpret_cast<const uint4*>(p.residual + r_off), rr);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] += rr[j];
-          } else {
-            for (int j = 0; j < nv; ++j) v[j] += __bfloat162float(p.residual[r_off + j]);
-          }
-        }
-        if (p.out_fp32) {
-          float* o = reinterpret_cast<float*>(p.out) + o_off;
-          if (p.vec_ok && nv == 8) {
-            reinterpret_cast<float4*>(o)[0] = make_float4(v[0], v[1], v[2], v[3]);
-            reinterpret_cast<float4*>(o)[1] = make_float4(v[4], v[5], v[6], v[7]);
-          } else {
-            for (int j = 0; j < nv; ++j) o[j] = v[j];
-          }
-        } else {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + o_off;
-          if (p.vec_ok && nv == 8) {
-            *reinterpret_cast<uint4*>(o) = pack8(v);
-          } else {
-            for (int j = 0; j < nv; ++j) o[j] = __float2bfloat16(v[j]);
-          }
-        }
-      }
+    const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
+    switch (p.act) {  // activation resolved once per tile: the column loop is branch-free
+      case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
+      case LY_ACT_SILU: epilogue_cols<LY_ACT_SILU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
+      case LY_ACT_HSWISH: epilogue_cols<LY_ACT_HSWISH>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
+      case LY_ACT_SIGMOID: epilogue_cols<LY_ACT_SIGMOID>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
+      default: epilogue_cols<LY_ACT_NONE>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
     }
   }
 
@@ -412,8 +424,10 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
     if (rc != LY_OK) return rc;
   }
   const int stage_bytes = kAStage + p.BN * 128;
+  // at most ~100 KB of shared memory per CTA: two or more CTAs per SM, so one CTA's epilogue overlaps another's
+  // TMA/MMA main loop (TMEM: 2 x 256 columns still fit)
   p.stages = num_k < kMaxStages ? num_k : kMaxStages;
-  while (p.stages > 1 && p.stages * stage_bytes > 200 * 1024) --p.stages;
+  while (p.stages > 2 && p.stages * stage_bytes > 100 * 1024) --p.stages;
   const size_t smem_bytes = (size_t)p.stages * stage_bytes + 1024;
 
   // ---- epilogue

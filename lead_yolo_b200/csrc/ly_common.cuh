@@ -35,12 +35,26 @@ int flat_grid(long M, int V, int block);
 static inline int ceil_div(long a, long b) { return (int)((a + b - 1) / b); }
 
 #if defined(__CUDACC__)
+// sigmoid through the hardware tanh: one MUFU op instead of ex2 + rcp (relative error ~2^-11, below bf16)
+__device__ __forceinline__ float fast_sigmoid(float v) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * v));
+  return fmaf(0.5f, t, 0.5f);
+}
+template <int ACT>
+__device__ __forceinline__ float act_apply_t(float v) {
+  if (ACT == LY_ACT_RELU) return fmaxf(v, 0.f);
+  if (ACT == LY_ACT_SILU) return v * fast_sigmoid(v);
+  if (ACT == LY_ACT_HSWISH) return v * fminf(fmaxf(v + 3.f, 0.f), 6.f) * (1.f / 6.f);
+  if (ACT == LY_ACT_SIGMOID) return fast_sigmoid(v);
+  return v;
+}
 __device__ __forceinline__ float act_apply(float v, int act) {
   switch (act) {
-    case LY_ACT_RELU: return fmaxf(v, 0.f);
-    case LY_ACT_SILU: return v / (1.f + __expf(-v));
-    case LY_ACT_HSWISH: return v * fminf(fmaxf(v + 3.f, 0.f), 6.f) * (1.f / 6.f);
-    case LY_ACT_SIGMOID: return 1.f / (1.f + __expf(-v));
+    case LY_ACT_RELU: return act_apply_t<LY_ACT_RELU>(v);
+    case LY_ACT_SILU: return act_apply_t<LY_ACT_SILU>(v);
+    case LY_ACT_HSWISH: return act_apply_t<LY_ACT_HSWISH>(v);
+    case LY_ACT_SIGMOID: return act_apply_t<LY_ACT_SIGMOID>(v);
     default: return v;
   }
 }
@@ -49,7 +63,7 @@ __device__ __forceinline__ float act_grad(float v, int act) {
   switch (act) {
     case LY_ACT_RELU: return v > 0.f ? 1.f : 0.f;
     case LY_ACT_SILU: {
-      float s = 1.f / (1.f + __expf(-v));
+      float s = fast_sigmoid(v);
       return s * (1.f + v * (1.f - s));
     }
     case LY_ACT_HSWISH: {
@@ -57,7 +71,7 @@ __device__ __forceinline__ float act_grad(float v, int act) {
       return r + ((v > -3.f && v < 3.f) ? v * (1.f / 6.f) : 0.f);
     }
     case LY_ACT_SIGMOID: {
-      float s = 1.f / (1.f + __expf(-v));
+      float s = fast_sigmoid(v);
       return s * (1.f - s);
     }
     default: return 1.f;

@@ -28,6 +28,10 @@ CASES = {
     "patch2_80_160": (2, 16, 24, [80], 160, 2, 2, 0, "none", False, False, True),
     "patch4_8_24": (2, 32, 32, [8], 24, 4, 4, 0, "none", False, False, True),
     "big_1x1_bs64": (64, 40, 40, [256], 128, 1, 1, 0, "silu", False, False, True),
+    "l12_cv12": (64, 40, 40, [336], 256, 1, 1, 0, "silu", False, False, True),
+    "l1_pconv": (64, 160, 160, [8], 8, 3, 1, 1, "none", False, False, False),
+    "l1_mlp3": (64, 160, 160, [48], 24, 1, 1, 0, "none", True, False, False),
+    "l12_3x3": (64, 40, 40, [128], 128, 3, 1, 1, "silu", False, False, True),
 }
 
 
