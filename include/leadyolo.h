@@ -153,6 +153,16 @@ int ly_rf_generate(const void* x, long ldx, int N, int H, int W, int C, int k, i
                    const float* wgk, const float* scale, const float* shift, int act, void* G, ly_stream_t stream);
 int ly_rf_attention(const void* G, int N, int ho, int wo, int C, int k, const float* wa, float* maps, int16_t* amax,
                     float* att, ly_stream_t stream);
+/* No counterpart in the reference: a variant of ly_rf_attention for callers that cannot allocate device
+ * memory when they call (a server whose memory arena is handed out at start-up, a real-time loop where
+ * cudaMalloc's device-wide synchronisation is off-limits).  The max/mean maps between the two kernels live in a
+ * library-owned static device array of LY_RF_NOALLOC_MAX_FLOATS = 2,097,152 floats (8 MiB, held by every GPU that
+ * loads the library until the process exits) instead of a caller buffer; N*ho*k*wo*k*2 floats must fit or the call
+ * returns LY_EINVAL.  The first call on each device looks the array's address up (make it before any stream
+ * capture); no call allocates or frees.  All calls on a device share the array: calls that may overlap on the GPU
+ * race.  Results are identical to ly_rf_attention. */
+int ly_rf_attention_noalloc(const void* G, int N, int ho, int wo, int C, int k, const float* wa, int16_t* amax,
+                            float* att, ly_stream_t stream);
 int ly_rf_gate(const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse, const float* att,
                void* A, ly_stream_t stream); /* A = G * se[n,c] * att */
 int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse,

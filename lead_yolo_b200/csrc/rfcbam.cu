@@ -7,6 +7,8 @@
 //   maps   : fp32 [N][h*k][w*k][2]  (0: max over c, 1: mean over c), argmax int16 [N][h*k][w*k]
 //   att    : fp32 [N][h*k][w*k]
 //   wgk    : fp32 [k*k (t)][k*k (i*k+j)][C]  (generate.0.weight[c*k*k+t, 0, i, j])
+#include <mutex>
+
 #include "ly_common.cuh"
 
 namespace ly {
@@ -529,5 +531,73 @@ extern "C" int ly_rf_generate_bwd(const void* dZ, const void* x, long ldx, int N
                                                                       ldx, N, H, W, V, s, ho, wo, dwgk);
     LY_LAUNCH_CHECK();
   }
+  return LY_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// ly_rf_attention_noalloc — same result as ly_rf_attention, but the channel max/mean maps (the scratch
+// between its two kernels) live in library-owned device memory instead of a caller-allocated buffer.
+//
+// Who needs it: callers that cannot obtain device memory at the moment they call us — an inference
+// server that hands out its whole memory arena at start-up and has no allocator in the request path, or
+// a latency-critical loop where cudaMalloc is forbidden because it synchronises the entire device.
+//
+// The scratch is one file-scope __device__ array of LY_RF_NOALLOC_MAX_FLOATS floats (8 MiB); every GPU
+// that loads this library keeps that much memory for the life of the process.  Its device address is
+// looked up once per device (cudaGetSymbolAddress, with that device current) on the FIRST call made on
+// that device — so make that first call outside any stream capture.  Nothing is allocated or freed here.
+// All calls on a device share the one array: two calls whose kernels may overlap on the GPU (different
+// streams) race on it.  The array keeps whatever the previous call left, which is harmless: the first
+// kernel overwrites every map entry the second kernel reads, so nothing has to start at zero.
+// ------------------------------------------------------------------------------------------------
+#define LY_RF_NOALLOC_MAX_FLOATS (2 * 1024 * 1024)
+
+static __device__ __align__(256) float g_rf_maps_scratch[LY_RF_NOALLOC_MAX_FLOATS];
+
+namespace ly {
+static std::mutex g_rf_scratch_mu;
+static float* g_rf_scratch_ptr[64] = {nullptr};
+
+// Device address of g_rf_maps_scratch on the current device (host code must not use the symbol's own
+// address: on the host it is only a stand-in).
+static int rf_scratch_for_current_device(float** out) {
+  int dev = 0;
+  LY_CUDA(cudaGetDevice(&dev));
+  LY_REQUIRE(dev >= 0 && dev < 64, "ly_rf_attention_noalloc: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_rf_scratch_mu);
+  if (g_rf_scratch_ptr[dev] == nullptr) {
+    float* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_rf_maps_scratch);
+    if (e != cudaSuccess || ptr == nullptr)
+      return fail(LY_ECUDA, "ly_rf_attention_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                  cudaGetErrorString(e));
+    g_rf_scratch_ptr[dev] = ptr;
+  }
+  *out = g_rf_scratch_ptr[dev];
+  return LY_OK;
+}
+}  // namespace ly
+
+extern "C" int ly_rf_attention_noalloc(const void* G, int N, int ho, int wo, int C, int k, const float* wa,
+                                       int16_t* amax, float* att, ly_stream_t st) {
+  LY_REQUIRE(G && wa && att && LY_ALIGNED16(G) && C % 8 == 0 && C > 0, "ly_rf_attention_noalloc: bad args");
+  LY_REQUIRE(N > 0 && ho > 0 && wo > 0 && (k == 1 || k == 3), "ly_rf_attention_noalloc: bad geometry");
+  const long need = (long)N * ho * k * wo * k * 2;  // floats in the max/mean maps
+  if (need > (long)LY_RF_NOALLOC_MAX_FLOATS)
+    return fail(LY_EINVAL,
+                "ly_rf_attention_noalloc: N*ho*k*wo*k*2 = %ld floats exceeds the built-in scratch of %d floats "
+                "(8 MiB); use ly_rf_attention with a caller-provided maps buffer for this size",
+                need, (int)LY_RF_NOALLOC_MAX_FLOATS);
+  float* maps = nullptr;
+  int rc = rf_scratch_for_current_device(&maps);
+  if (rc != LY_OK) return rc;
+  const int V = C / 8, KK = k * k;
+  const long M = (long)N * ho * wo;
+  rf_poolc_kernel<<<ceil_div(M * KK * 32, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)G, M, KK, k, V, ho,
+                                                                          wo, maps, amax);
+  LY_LAUNCH_CHECK();
+  const long total = (long)N * ho * k * wo * k;
+  rf_att_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(maps, N, ho * k, wo * k, wa, att);
+  LY_LAUNCH_CHECK();
   return LY_OK;
 }

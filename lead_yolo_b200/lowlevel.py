@@ -164,6 +164,7 @@ _SIGS = {
     "ly_ca_pool_bwd": "pliiiipl",
     "ly_rf_generate": "pliiiiiiiipppip",
     "ly_rf_attention": "piiiiipppp",
+    "ly_rf_attention_noalloc": "piiiiippp",
     "ly_rf_gate": "piiiiiplpp",
     "ly_rf_gate_bwd": "ppiiiiiplpppp",
     "ly_rf_attention_bwd": "ppppiiiiipppp",
