@@ -116,6 +116,12 @@ int ly_stem_fwd(const void* img, int img_is_u8, int N, int H, int W, int Cout, c
 int ly_stem_wgrad(const void* img, int img_is_u8, int N, int H, int W, int Cout, const void* dz, long ld_dz,
                   float in_scale, float* dwk, ly_stream_t stream);
 
+/* FasterNet partial 3x3 convolution, inference (models/common.py:1416,1432-1437): out[p][co] = sum over the 3x3
+ * taps and the first `cpp` channels of x (8-aligned slice; real width dim//4, the rest has zero weights).
+ * wk: fp32 [9][cpp][cpp] (tap, ci, co); cpp in {8,16,24,32,40}.  CUDA cores, warp-uniform weights. */
+int ly_pconv3x3_fwd(const void* x, long ldx, int N, int H, int W, int cpp, const float* wk, void* out, long ldo,
+                    ly_stream_t stream);
+
 /* SPPF pooling (models/common.py:356,364-367): 5x5 / stride 1 / pad 2 max pool on an NHWC channel slice.
  * idx (optional, uint8 [pixels][C]) records the arg-max tap for ly_maxpool5_bwd. */
 int ly_maxpool5_fwd(const void* x, long ldx, int N, int H, int W, int C, void* y, long ldy, uint8_t* idx,
@@ -165,6 +171,15 @@ int ly_rf_attention_noalloc(const void* G, int N, int ho, int wo, int C, int k, 
                             float* att, ly_stream_t stream);
 int ly_rf_gate(const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse, const float* att,
                void* A, ly_stream_t stream); /* A = G * se[n,c] * att */
+/* Inference front half of RFCBAMConv (rfa.py:113-128) without materialising G: pass 1 recomputes the receptive-field
+ * features and emits only the channel max/mean maps and the SE sums, a tiny kernel evaluates the SE gate
+ * (w1 [R][C], w2 [C][R] = se.fc weights) and the 3x3 spatial attention, pass 2 recomputes the features and writes the
+ * gated GEMM operand A once.  Workspaces (fp32, caller-allocated): maps [N][ho*k][wo*k][2], gap_sum [N][C],
+ * se [N][C], att [N][ho*k][wo*k].  scale/shift: folded generate BatchNorm in G-column order (t*C + c).  C <= 256. */
+int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int W, int C, int k, int s, int ho, int wo,
+                          const float* wgk, const float* scale, const float* shift, const float* w1, const float* w2,
+                          int R, const float* wa, float* maps, float* gap_sum, float* se, float* att, void* A,
+                          ly_stream_t stream);
 int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse,
                    const float* att, void* dG, float* dse, float* datt, ly_stream_t stream);
 int ly_rf_attention_bwd(const float* datt, const float* att, const float* maps, const int16_t* amax, int N, int ho,

@@ -1,0 +1,346 @@
+// Inference pipeline of RFCBAMConv (reference models/rfa.py:113-128) without materialising the receptive-field
+// matrix G in HBM:
+//   pass 1  rf_stats_kernel   recomputes g = relu(bn(dwconv(x))) on the fly and emits only max_c / mean_c per
+//                             (pixel, tap) plus the per-(image, channel) sums of x for the SE gate
+//   tiny    rf_se_att_kernel  SE gate s = sigmoid(W2 relu(W1 mean(x)))  and  att = sigmoid(conv3x3(maps))
+//   pass 2  rf_apply_kernel   recomputes g, multiplies by s*att and writes the GEMM operand A (bf16) once
+// HBM traffic: x twice + A once (the GEMM reads A once more) instead of five G-sized passes.
+//
+// Thread mapping of both passes: a warp = 32 consecutive output pixels x ONE 8-channel vector, so the k*k x k*k
+// depthwise weights, BN scale/shift of that vector are warp-uniform loads (one sector per warp instead of one per
+// lane); the kernels are then bound by the FMA pipe (k^4 MACs per output channel), not by weight traffic.
+#include "ly_common.cuh"
+
+namespace ly {
+
+__device__ __forceinline__ uint4 ldx16(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+template <int K>
+__device__ __forceinline__ void rf_load_inputs(const __nv_bfloat16* __restrict__ x, long ldx, int H, int W, int s,
+                                               int n, int h, int w, int v, bool act, float (&xin)[K * K][8]) {
+#pragma unroll
+  for (int i = 0; i < K; ++i)
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      const int yy = h * s + i - K / 2, xx = w * s + j - K / 2;
+      if (act && yy >= 0 && yy < H && xx >= 0 && xx < W) {
+        unpack8(ldx16(x + (((long)n * H + yy) * W + xx) * ldx + v * 8), xin[i * K + j]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) xin[i * K + j][e] = 0.f;
+      }
+    }
+}
+
+// Shared-memory copy of the depthwise weights / folded BN of the block's VB channel vectors:
+//   wsm[(t*KK + ij)*VB*8 + vl*8 + e],  ssm[(t*VB + vl)*8 + e] (scale), hsm[...] (shift)      (vl = local vector index)
+// Reads are warp-uniform (broadcast): one shared-memory wavefront feeds 4 FMA instructions.
+template <int K>
+__device__ __forceinline__ void rf_stage_weights(const float* __restrict__ wgk, const float* __restrict__ scale,
+                                                 const float* __restrict__ shift, int C, int v0, int VB, int V,
+                                                 float* wsm, float* ssm, float* hsm) {
+  constexpr int KK = K * K;
+  const int n8 = VB * 8;
+  for (int i = threadIdx.x; i < KK * KK * n8; i += blockDim.x) {
+    const int r = i / n8, c = i % n8;
+    wsm[i] = (v0 * 8 + c < C) ? wgk[(long)r * C + v0 * 8 + c] : 0.f;
+  }
+  for (int i = threadIdx.x; i < KK * n8; i += blockDim.x) {
+    const int t = i / n8, c = i % n8;
+    const bool ok = v0 * 8 + c < C;
+    ssm[i] = ok ? scale[(long)t * C + v0 * 8 + c] : 0.f;
+    hsm[i] = ok ? shift[(long)t * C + v0 * 8 + c] : 0.f;
+  }
+}
+
+// g[e] for tap t of this thread's 8 channels (folded BN + ReLU, rounded to bf16 like the stored operand)
+template <int K>
+__device__ __forceinline__ void rf_tap(const float (&xin)[K * K][8], const float* wsm, const float* ssm,
+                                       const float* hsm, int VB, int vl, int t, float (&g)[8]) {
+  constexpr int KK = K * K;
+  const int n8 = VB * 8;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) g[e] = 0.f;
+#pragma unroll
+  for (int ij = 0; ij < KK; ++ij) {
+    const float4 a0 = *reinterpret_cast<const float4*>(wsm + (t * KK + ij) * n8 + vl * 8);
+    const float4 a1 = *reinterpret_cast<const float4*>(wsm + (t * KK + ij) * n8 + vl * 8 + 4);
+    g[0] = fmaf(xin[ij][0], a0.x, g[0]); g[1] = fmaf(xin[ij][1], a0.y, g[1]);
+    g[2] = fmaf(xin[ij][2], a0.z, g[2]); g[3] = fmaf(xin[ij][3], a0.w, g[3]);
+    g[4] = fmaf(xin[ij][4], a1.x, g[4]); g[5] = fmaf(xin[ij][5], a1.y, g[5]);
+    g[6] = fmaf(xin[ij][6], a1.z, g[6]); g[7] = fmaf(xin[ij][7], a1.w, g[7]);
+  }
+  const float4 s0 = *reinterpret_cast<const float4*>(ssm + t * n8 + vl * 8);
+  const float4 s1 = *reinterpret_cast<const float4*>(ssm + t * n8 + vl * 8 + 4);
+  const float4 h0 = *reinterpret_cast<const float4*>(hsm + t * n8 + vl * 8);
+  const float4 h1 = *reinterpret_cast<const float4*>(hsm + t * n8 + vl * 8 + 4);
+  const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+  const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+  for (int e = 0; e < 8; ++e)
+    g[e] = __bfloat162float(__float2bfloat16(fmaxf(fmaf(g[e], sc[e], sh[e]), 0.f)));
+}
+
+// grid = (persistent blocks, channel-vector groups); block = WPB warps, warp w owns vector blockIdx.y*WPB + w and
+// the block strides over groups of 32 pixels.  Dynamic smem: weights + scale/shift of the block's WPB vectors.
+template <int K>
+__global__ void __launch_bounds__(512, 1) rf_stats_kernel(const __nv_bfloat16* __restrict__ x, long ldx, long M, int H,
+                                                          int W, int V, int WPB, int s, int ho, int wo,
+                                                          const float* __restrict__ wgk,
+                                                          const float* __restrict__ scale,
+                                                          const float* __restrict__ shift, float* __restrict__ maps,
+                                                          float* __restrict__ gap_sum, int use_atomics) {
+  constexpr int KK = K * K;
+  extern __shared__ float dsm[];
+  __shared__ int smax[KK][32];
+  __shared__ float ssum[KK][32];
+  const int C = V * 8;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* wsm = dsm;
+  float* ssm = wsm + KK * KK * WPB * 8;
+  float* hsm = ssm + KK * WPB * 8;
+  rf_stage_weights<K>(wgk, scale, shift, C, blockIdx.y * WPB, WPB, V, wsm, ssm, hsm);
+  const int v = blockIdx.y * WPB + warp;
+  const bool vact = v < V;
+  const long groups = (M + 31) / 32;
+  for (long pg = blockIdx.x; pg < groups; pg += gridDim.x) {
+    __syncthreads();  // staged weights visible / previous iteration's smax, ssum consumed
+    for (int i = threadIdx.x; i < KK * 32; i += blockDim.x) {
+      smax[i / 32][i % 32] = 0;  // features are >= 0 after ReLU: 0 is the identity of the max
+      ssum[i / 32][i % 32] = 0.f;
+    }
+    __syncthreads();
+    const long m = pg * 32 + lane;
+    const bool pact = m < M;
+    const int w = pact ? (int)(m % wo) : 0, h = pact ? (int)((m / wo) % ho) : 0;
+    const int n = pact ? (int)(m / ((long)wo * ho)) : 0;
+    if (vact) {
+      float xin[KK][8];
+      rf_load_inputs<K>(x, ldx, H, W, s, n, h, w, v, pact, xin);
+      // SE pooling: every input pixel is summed exactly once, by the output pixel whose s x s block contains it
+      float gsum[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) gsum[e] = 0.f;
+#pragma unroll
+      for (int i = 0; i < K; ++i)
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          const bool own = (K == 1) || (i >= K / 2 && i < K / 2 + s && j >= K / 2 && j < K / 2 + s);
+          if (own) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) gsum[e] += xin[i * K + j][e];
+          }
+        }
+      const int n_first = __shfl_sync(0xffffffffu, n, 0);
+      const int n_last = __shfl_sync(0xffffffffu, pact ? n : -1, 31);
+      if (n_first == n_last) {  // whole warp inside one image: reduce over the 32 pixels first
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float r = warp_sum(gsum[e]);
+          if (lane == 0) atomicAdd(&gap_sum[(long)n * C + v * 8 + e], r);
+        }
+      } else if (pact) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(&gap_sum[(long)n * C + v * 8 + e], gsum[e]);
+      }
+#pragma unroll 1
+      for (int t = 0; t < KK; ++t) {
+        float g[8];
+        rf_tap<K>(xin, wsm, ssm, hsm, WPB, warp, t, g);
+        float mx = g[0], sm = g[0];
+#pragma unroll
+        for (int e = 1; e < 8; ++e) { mx = fmaxf(mx, g[e]); sm += g[e]; }
+        atomicMax(&smax[t][lane], __float_as_int(mx));
+        atomicAdd(&ssum[t][lane], sm);
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < KK * 32; i += blockDim.x) {
+      const int t = i / 32, l = i % 32;
+      const long mm = pg * 32 + l;
+      if (mm >= M) continue;
+      const int ww = (int)(mm % wo), hh = (int)((mm / wo) % ho);
+      const long nn = mm / ((long)wo * ho);
+      const int n1 = t / K, n2 = t % K;
+      const long pos = (nn * (ho * K) + (hh * K + n1)) * (long)(wo * K) + (ww * K + n2);
+      const float mean_part = ssum[t][l] / (float)C;
+      if (use_atomics) {
+        atomicMax(reinterpret_cast<int*>(maps + pos * 2), smax[t][l]);
+        atomicAdd(maps + pos * 2 + 1, mean_part);
+      } else {
+        *reinterpret_cast<float2*>(maps + pos * 2) = make_float2(__int_as_float(smax[t][l]), mean_part);
+      }
+    }
+  }
+}
+
+// blocks [0, N): SE gate of image n;  blocks [N, ...): spatial attention map
+__global__ void __launch_bounds__(256) rf_se_att_kernel(const float* __restrict__ gap_sum, int N, int C, float inv_hw,
+                                                        const float* __restrict__ w1 /*[R][C]*/,
+                                                        const float* __restrict__ w2 /*[C][R]*/, int R,
+                                                        float* __restrict__ se, const float* __restrict__ maps,
+                                                        int HK, int WK, const float* __restrict__ wa,
+                                                        float* __restrict__ att) {
+  if ((int)blockIdx.x < N) {
+    __shared__ float mean[512];
+    __shared__ float hid[64];
+    const int n = blockIdx.x;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) mean[c] = gap_sum[(long)n * C + c] * inv_hw;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int r = warp; r < R; r += (blockDim.x >> 5)) {
+      float a = 0.f;
+      for (int c = lane; c < C; c += 32) a = fmaf(w1[(long)r * C + c], mean[c], a);
+      a = warp_sum(a);
+      if (lane == 0) hid[r] = fmaxf(a, 0.f);
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      float a = 0.f;
+      for (int r = 0; r < R; ++r) a = fmaf(w2[(long)c * R + r], hid[r], a);
+      se[(long)n * C + c] = 1.f / (1.f + __expf(-a));
+    }
+    return;
+  }
+  const long total = (long)N * HK * WK;
+  const long t = (long)(blockIdx.x - N) * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int xq = (int)(t % WK), y = (int)((t / WK) % HK);
+  const long n = t / ((long)WK * HK);
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int yy = y + i - 1, xx = xq + j - 1;
+      if (yy < 0 || yy >= HK || xx < 0 || xx >= WK) continue;
+      const float2 mm = __ldg(reinterpret_cast<const float2*>(maps + ((n * HK + yy) * (long)WK + xx) * 2));
+      acc = fmaf(mm.x, __ldg(wa + i * 3 + j), acc);
+      acc = fmaf(mm.y, __ldg(wa + 9 + i * 3 + j), acc);
+    }
+  att[t] = 1.f / (1.f + __expf(-acc));
+}
+
+// pass 2: A[m][t*C+c] = g * se[n,c] * att[n, h*k+n1, w*k+n2].  grid = (persistent blocks, groups of 8 channel
+// vectors); block = 8 warps, warp w owns vector blockIdx.y*8 + w (8 x 16 B = one full 128 B line per (pixel, tap)).
+template <int K>
+__global__ void __launch_bounds__(256) rf_apply_kernel(const __nv_bfloat16* __restrict__ x, long ldx, long M, int H,
+                                                       int W, int V, int s, int ho, int wo,
+                                                       const float* __restrict__ wgk,
+                                                       const float* __restrict__ scale,
+                                                       const float* __restrict__ shift,
+                                                       const float* __restrict__ se, const float* __restrict__ att,
+                                                       __nv_bfloat16* __restrict__ A) {
+  constexpr int KK = K * K;
+  constexpr int VB = 8;
+  extern __shared__ float dsm[];
+  const int C = V * 8;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* wsm = dsm;
+  float* ssm = wsm + KK * KK * VB * 8;
+  float* hsm = ssm + KK * VB * 8;
+  rf_stage_weights<K>(wgk, scale, shift, C, blockIdx.y * VB, VB, V, wsm, ssm, hsm);
+  __syncthreads();
+  const int v = blockIdx.y * VB + warp;
+  if (v >= V) return;
+  const long groups = (M + 31) / 32;
+  for (long pg = blockIdx.x; pg < groups; pg += gridDim.x) {
+    const long m = pg * 32 + lane;
+    const bool pact = m < M;
+    const int w = pact ? (int)(m % wo) : 0, h = pact ? (int)((m / wo) % ho) : 0;
+    const int n = pact ? (int)(m / ((long)wo * ho)) : 0;
+    float xin[KK][8];
+    rf_load_inputs<K>(x, ldx, H, W, s, n, h, w, v, pact, xin);
+    if (!pact) continue;
+    float s8[8];
+    {
+      const float4 a0 = __ldg(reinterpret_cast<const float4*>(se + (long)n * C + v * 8));
+      const float4 a1 = __ldg(reinterpret_cast<const float4*>(se + (long)n * C + v * 8 + 4));
+      s8[0] = a0.x; s8[1] = a0.y; s8[2] = a0.z; s8[3] = a0.w; s8[4] = a1.x; s8[5] = a1.y; s8[6] = a1.z; s8[7] = a1.w;
+    }
+    __nv_bfloat16* arow = A + m * (long)KK * C + v * 8;
+#pragma unroll 1
+    for (int t = 0; t < KK; ++t) {
+      float g[8];
+      rf_tap<K>(xin, wsm, ssm, hsm, VB, warp, t, g);
+      const int n1 = t / K, n2 = t % K;
+      const float a = __ldg(att + ((long)n * (ho * K) + (h * K + n1)) * (long)(wo * K) + (w * K + n2));
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] *= s8[e] * a;
+      *reinterpret_cast<uint4*>(arow + (long)t * C) = pack8(g);
+    }
+  }
+}
+
+}  // namespace ly
+
+using namespace ly;
+
+extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int W, int C, int k, int s, int ho,
+                                     int wo, const float* wgk, const float* scale, const float* shift,
+                                     const float* w1, const float* w2, int R, const float* wa, float* maps,
+                                     float* gap_sum, float* se, float* att, void* A, ly_stream_t st) {
+  LY_REQUIRE(x && wgk && scale && shift && w1 && w2 && wa && maps && gap_sum && se && att && A,
+             "ly_rfcbam_front_infer: null pointer");
+  LY_REQUIRE(N > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0 && C <= 512, "ly_rfcbam_front_infer: bad sizes (C=%d)", C);
+  LY_REQUIRE((k == 1 && s == 1) || (k == 3 && (s == 1 || s == 2)), "ly_rfcbam_front_infer: k=%d s=%d unsupported", k, s);
+  LY_REQUIRE(ho == (H + 2 * (k / 2) - k) / s + 1 && wo == (W + 2 * (k / 2) - k) / s + 1,
+             "ly_rfcbam_front_infer: output size mismatch");
+  // the SE sums visit every input pixel exactly once only if the s x s blocks tile the input
+  LY_REQUIRE(s == 1 || (H % 2 == 0 && W % 2 == 0), "ly_rfcbam_front_infer: stride 2 needs even H, W");
+  const auto al16 = [](const void* p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+  LY_REQUIRE(al16(x) && al16(A) && al16(wgk) && al16(se) && al16(scale) && al16(shift) && al16(maps) &&
+                 ldx % 8 == 0 && ldx >= C,
+             "ly_rfcbam_front_infer: alignment / ld");
+  LY_REQUIRE(R > 0 && R <= 64, "ly_rfcbam_front_infer: R=%d out of range", R);
+  cudaStream_t stream = (cudaStream_t)st;
+  const int V = C / 8;
+  const long M = (long)N * ho * wo;
+  const int vgroups = ceil_div(V, 16);
+  const int WPB = ceil_div(V, vgroups);
+  LY_CUDA(cudaMemsetAsync(gap_sum, 0, sizeof(float) * (size_t)N * C, stream));
+  if (vgroups > 1) LY_CUDA(cudaMemsetAsync(maps, 0, sizeof(float) * (size_t)N * ho * k * wo * k * 2, stream));
+  const int KK = k * k;
+  const long groups = (M + 31) / 32;
+  const int sms = device_sm_count();
+  {
+    long bx = groups < (long)sms ? groups : (long)sms;      // one block per SM (512 threads, 128 registers)
+    dim3 grid1((unsigned)bx, (unsigned)vgroups);
+    const size_t sm1 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * WPB * 8;
+    if (k == 1) {
+      rf_stats_kernel<1><<<grid1, WPB * 32, sm1, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, WPB, s, ho, wo,
+                                                          wgk, scale, shift, maps, gap_sum, vgroups > 1);
+    } else {
+      static bool attr_done[64] = {false};
+      int dev = 0;
+      LY_CUDA(cudaGetDevice(&dev));
+      if (!attr_done[dev & 63]) {
+        LY_CUDA(cudaFuncSetAttribute(rf_stats_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        attr_done[dev & 63] = true;
+      }
+      rf_stats_kernel<3><<<grid1, WPB * 32, sm1, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, WPB, s, ho, wo,
+                                                          wgk, scale, shift, maps, gap_sum, vgroups > 1);
+    }
+    LY_LAUNCH_CHECK();
+  }
+  const long tot_att = (long)N * ho * k * wo * k;
+  rf_se_att_kernel<<<N + ceil_div(tot_att, 256), 256, 0, stream>>>(gap_sum, N, C, 1.f / (float)(H * W), w1, w2, R, se,
+                                                                  maps, ho * k, wo * k, wa, att);
+  LY_LAUNCH_CHECK();
+  {
+    const int vg8 = ceil_div(V, 8);
+    long bx = ceil_div((long)sms * 4, vg8);                 // ~4 resident blocks of 256 threads per SM
+    if (bx > groups) bx = groups;
+    if (bx < 1) bx = 1;
+    dim3 grid2((unsigned)bx, (unsigned)vg8);
+    const size_t sm2 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * 8 * 8;
+    if (k == 1)
+      rf_apply_kernel<1><<<grid2, 256, sm2, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, s, ho, wo, wgk, scale,
+                                                     shift, se, att, (__nv_bfloat16*)A);
+    else
+      rf_apply_kernel<3><<<grid2, 256, sm2, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, s, ho, wo, wgk, scale,
+                                                     shift, se, att, (__nv_bfloat16*)A);
+  }
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}

@@ -12,7 +12,7 @@ from ._lib import ConvDesc, check, lib, ptr, stream_ptr
 CL = torch.channels_last
 COUNT = [0]        # kernels launched through the C-ABI (bench.py: gpu_launches)
 PROFILE = None     # when a list: (entry point, start event, end event, algorithmic bytes, flops) per call
-_LAUNCHES = {"ly_bn_act_bwd": 2, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 2}
+_LAUNCHES = {"ly_rfcbam_front_infer": 3, "ly_bn_act_bwd": 2, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 2}
 
 
 class _Prof:
@@ -153,6 +153,7 @@ _SIGS = {
     "ly_act_bwd_from_out": "plplliipl",
     "ly_stem_fwd": "piiiiipppfpl",
     "ly_stem_wgrad": "piiiiiplfp",
+    "ly_pconv3x3_fwd": "pliiiippl",
     "ly_maxpool5_fwd": "pliiiiplp",
     "ly_maxpool5_bwd": "plpiiiipli",
     "ly_copy_upsample": "pliiiiipl",
@@ -166,6 +167,7 @@ _SIGS = {
     "ly_rf_attention": "piiiiipppp",
     "ly_rf_attention_noalloc": "piiiiippp",
     "ly_rf_gate": "piiiiiplpp",
+    "ly_rfcbam_front_infer": "pliiiiiiiipppppipppppp",
     "ly_rf_gate_bwd": "ppiiiiiplpppp",
     "ly_rf_attention_bwd": "ppppiiiiipppp",
     "ly_rf_generate_bwd": "ppliiiiiiiippplp",

@@ -131,9 +131,16 @@ class LeadYolo(nn.Module):
 
     def forward(self, x):
         y = []
+        lazy_cat = (not torch.is_grad_enabled()) and (not self.training)
         for m in self.model:
             if m.f != -1:
                 x = y[m.f] if isinstance(m.f, int) else [x if j == -1 else y[j] for j in m.f]
+            if lazy_cat and isinstance(m, M.Concat) and m.i not in self.save and m.i + 1 < len(self.model) and \
+                    isinstance(self.model[m.i + 1], (M.C3, M.C3_CA)) and self.model[m.i + 1].f == -1:
+                # inference: the only consumer is a CSP block whose 1x1 convs read the pieces as K segments of one
+                # GEMM, so the concat is never materialised
+                y.append(None)
+                continue
             x = m(x)
             y.append(x if m.i in self.save else None)
         return x

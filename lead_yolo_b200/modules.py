@@ -161,21 +161,24 @@ def _csp_forward(mod, x):
     if _fast(mod) and hasattr(mod.cv1, "bn") and hasattr(mod.cv2, "bn") and \
             type(mod.cv1.act) is type(mod.cv2.act):
         c_ = mod.cv1.conv.out_channels
-        x = ops.to_act(x)
-        cin = x.shape[1]
+        # a list input is a not-yet-materialised channel concat (see LeadYolo.forward): read it as K segments
+        srcs = [ops.to_act(t) for t in x] if isinstance(x, (list, tuple)) else [ops.to_act(x)]
+        chans = tuple(int(t.shape[1]) for t in srcs)
         keys = [mod.cv1.conv.weight, mod.cv2.conv.weight]
 
         def build():
             w = torch.cat([mod.cv1.conv.weight.detach().float(), mod.cv2.conv.weight.detach().float()], 0)
-            return pack_conv_weight(w, [cin])
+            return pack_conv_weight(w, list(chans))
 
-        wp = ops.cached(keys, ("csp12", cin), build)
+        wp = ops.cached(keys, ("csp12", chans), build)
         s1, h1 = ops.bn_fold(mod.cv1.bn)
         s2, h2 = ops.bn_fold(mod.cv2.bn)
         ss = ops.cached([s1, s2, h1, h2], "csp12ss", lambda: (torch.cat([s1, s2]), torch.cat([h1, h2])))
-        buf = ops.conv_infer([x], wp, 2 * c_, k=1, s=1, scale=ss[0], shift=ss[1], act=_act_name(mod.cv1.act))
+        buf = ops.conv_infer(srcs, wp, 2 * c_, k=1, s=1, scale=ss[0], shift=ss[1], act=_act_name(mod.cv1.act))
         a = mod.m(buf[:, :c_])
         return mod.cv3.run([a, buf[:, c_:]])
+    if isinstance(x, (list, tuple)):
+        x = ops.UpsampleCatFn.apply(tuple(False for _ in x), *x)
     a = mod.m(mod.cv1(x))
     b = mod.cv2(x)
     return mod.cv3.run([a, b])
@@ -264,6 +267,14 @@ class Partial_conv3(nn.Module):
         w = self.partial_conv3.weight
         if x.shape[1] < cpp:
             raise LeadYoloError("Partial_conv3: channel count too small for the 8-aligned slice")
+        if fast and cpp in (8, 16, 24, 32, 40):
+            wk = ops.cached([w], ("pconvk", cpp), lambda: nn.functional.pad(
+                w.detach().float(), (0, 0, 0, 0, 0, cpp - cp, 0, cpp - cp)).permute(2, 3, 1, 0).reshape(
+                    9, cpp, cpp).contiguous())
+            n, _, h, wd = x.shape
+            t1 = ll.empty_cl(n, cpp, h, wd, device=x.device)
+            ll.call("ly_pconv3x3_fwd", x, ll.pixel_ld(x), n, h, wd, cpp, wk, t1, cpp)
+            return t1
         if fast:
             wp = ops.cached([w], ("pconv", cpp), lambda: pack_conv_weight(
                 nn.functional.pad(w.detach().float(), (0, 0, 0, 0, 0, cpp - cp, 0, cpp - cp)), [cpp]))
@@ -546,9 +557,18 @@ class RFCBAMConv(nn.Module):
         n, c, h, w = x.shape
         conv, cbn = self.conv[0], self.conv[1]
         cout = conv.out_channels
-        se = self.se(x)
         perm = ops.cached([gen.weight], ("rfperm", c, k), lambda: ops.rf_channel_perm(c, k, x.device)) \
             if k > 1 else None
+        if fast and c <= 256 and (gen.stride[0] == 1 or (h % 2 == 0 and w % 2 == 0)):
+            # two passes over x, no receptive-field matrix in HBM (ly_rfcbam_front_infer)
+            gscale, gshift = ops.bn_fold(gbn, None, perm=perm)
+            a = ops.rfcbam_front_infer(x, gen.weight, k, s, gscale, gshift, self.se.fc[0].weight,
+                                       self.se.fc[2].weight, self.get_weight[0].weight)
+            wp = ops.cached([conv.weight], ("rfconv", c, k), lambda: pack_conv_weight(
+                conv.weight.detach().float().permute(0, 2, 3, 1).reshape(cout, k * k * c, 1, 1), None))
+            scale, shift = ops.bn_fold(cbn, conv.bias)
+            return ops.conv_infer([a], wp, cout, scale=scale, shift=shift, act="relu")
+        se = self.se(x)
         if fast:
             gscale, gshift = ops.bn_fold(gbn, None, perm=perm)
             g = ops.RfGenerateFn.apply(x, gen.weight, k, s, gscale, gshift, "relu")

@@ -484,6 +484,27 @@ class RfGateAttFn(torch.autograd.Function):
         return dg, dse.to(BF16).view(n, c, 1, 1), dwa.view(1, 2, 3, 3).to(wdt), None
 
 
+def rfcbam_front_infer(x, wg, k, s, gscale, gshift, w1, w2, wa):
+    """Inference: x -> gated GEMM operand A (N, k*k*C, ho, wo) in two passes over x (ly_rfcbam_front_infer)."""
+    x = to_act(x)
+    n, c, h, w = x.shape
+    ho, wo = rf_out_size(h, w, k, s)
+    dev = x.device
+    wgk = cached([wg], ("wgk", c, k), lambda: rf_pack_generate_weight(wg, c, k))
+    w1f = cached([w1], "sew1", lambda: w1.detach().float().contiguous())
+    w2f = cached([w2], "sew2", lambda: w2.detach().float().contiguous())
+    wa32 = cached([wa], "wa32", lambda: wa.detach().float().reshape(18).contiguous())
+    nm = n * ho * k * wo * k
+    nmp = (nm + 3) // 4 * 4          # keep every segment 16-byte aligned
+    ws = torch.empty(3 * nmp + 2 * n * c, dtype=torch.float32, device=dev)
+    maps, att = ws[:2 * nm], ws[2 * nmp:2 * nmp + nm]
+    gap, se = ws[3 * nmp:3 * nmp + n * c], ws[3 * nmp + n * c:]
+    a = ll.empty_cl(n, k * k * c, ho, wo, device=dev)
+    ll.call("ly_rfcbam_front_infer", x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, gscale, gshift, w1f, w2f,
+            int(w1.shape[0]), wa32, maps, gap, se, att, a)
+    return a
+
+
 def rf_gate_att_infer(g, se, wa, k):
     n, kkc, ho, wo = g.shape
     c = kkc // (k * k)
