@@ -1,9 +1,10 @@
 // Implicit-GEMM convolution on tcgen05 tensor cores (sm_100a).
 //
-//   grid  = (M tiles, N tiles);  block = 192 threads:
+//   persistent grid (one CTA per SM, static tile striding);  block = 320 threads:
 //     warp 0      TMA producer   (A box: 64 channels x Wt x Ht pixels of one tap; B box: 64 x BN weights)
 //     warp 1      MMA issuer     (one lane issues 4 x tcgen05.mma K=16 per 64-wide K chunk)
-//     warps 2..5  epilogue       (TMEM -> registers -> scale/shift/activation/residual -> global)
+//     warps 2..9  epilogue       (TMEM -> registers -> scale/shift/activation/residual -> global); the accumulator
+//                                is double-buffered in TMEM so tile i drains while tile i+1 is being multiplied
 //   A and B tiles live in 128B-swizzled shared memory, accumulators (128 x BN fp32) in TMEM.
 //   Zero padding of a 3x3 convolution and ragged channel counts are TMA out-of-bounds zero fill.
 #include <string.h>
@@ -17,7 +18,8 @@
 namespace ly {
 
 constexpr int kMaxK = 96;      // K chunks of 64 per launch
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 8;
+constexpr int kMaxCout = 2560;  // scale/shift staged in shared memory
 constexpr int kAStage = 128 * 128;  // 128 rows x 128 B
 
 struct KEntry {
@@ -29,9 +31,9 @@ struct KEntry {
 struct alignas(64) ConvGemmParams {
   CUtensorMap a_map[4];
   CUtensorMap b_map;
-  int tiles_w, tiles_h, n_img;
+  int tiles_w, tiles_h, n_img, tiles_n;
   int Wt, Ht, Hout, Wout;
-  int num_k, Cout, BN, tmem_cols, stages;
+  int num_k, Cout, BN, tmem_cols, stages, nbuf;
   int act, out_fp32, vec_ok, res_vec_ok;
   uint32_t a_bytes;
   int patch_k, patch_c;
@@ -44,20 +46,20 @@ struct alignas(64) ConvGemmParams {
   KEntry sched[kMaxK];
 };
 
-// One epilogue thread = one output pixel (TMEM lane).  Columns are drained 32 at a time (two tcgen05.ld in flight).
+// One epilogue thread = one output pixel (TMEM lane).  Columns [c_begin, BN) are drained 16 at a time, stride c_step.
 template <int ACT>
 __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t trow, bool valid, int n, int h, int w,
-                                              long pix, int n0, const float* s_scale, const float* s_shift) {
+                                              long pix, int n0, const float* s_scale, const float* s_shift,
+                                              int c_begin, int c_step) {
   const int kC = p.patch_k * p.patch_c;
-  for (int c0 = 0; c0 < p.BN; c0 += 32) {
-    uint32_t acc[2][16];
+  for (int c0 = c_begin; c0 < p.BN; c0 += c_step) {
+    uint32_t acc[16];
     __syncwarp();
-    tmem_ld16(trow + (uint32_t)c0, acc[0]);
-    if (c0 + 16 < p.BN) tmem_ld16(trow + (uint32_t)(c0 + 16), acc[1]);
+    tmem_ld16(trow + (uint32_t)c0, acc);
     tmem_ld_wait();
     if (!valid) continue;
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
+    for (int g = 0; g < 2; ++g) {
       const int cl = c0 + g * 8;       // column inside the tile
       const int c = n0 + cl;           // output channel
       if (cl >= p.BN || c >= p.Cout) break;
@@ -73,10 +75,16 @@ __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t 
         o_off = pix * p.out_ld + c;
         r_off = pix * p.res_ld + c;
       }
+      const float4 sc0 = *reinterpret_cast<const float4*>(s_scale + c);
+      const float4 sc1 = *reinterpret_cast<const float4*>(s_scale + c + 4);
+      const float4 sh0 = *reinterpret_cast<const float4*>(s_shift + c);
+      const float4 sh1 = *reinterpret_cast<const float4*>(s_shift + c + 4);
+      const float sc[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
+      const float sh[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
       float v[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j)
-        v[j] = act_apply_t<ACT>(fmaf(__uint_as_float(acc[g >> 1][(g & 1) * 8 + j]), s_scale[cl + j], s_shift[cl + j]));
+        v[j] = act_apply_t<ACT>(fmaf(__uint_as_float(acc[g * 8 + j]), sc[j], sh[j]));
       if (p.residual != nullptr) {
         if (p.res_vec_ok && nv == 8) {
           float rr[8];
@@ -107,14 +115,25 @@ __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t 
   }
 }
 
-__global__ void __launch_bounds__(192) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
+// Persistent, warp-specialised kernel: one CTA per SM walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...
+//   warp 0      TMA producer   (smem ring of `stages` {A box, B box} slots, continuous across tiles)
+//   warp 1      MMA issuer     (accumulates tile i into TMEM buffer i & 1)
+//   warps 2..17 epilogue       four groups of 4 warps (one per TMEM lane quadrant); group g drains tiles g, g+4, ...
+//                              from TMEM buffer i % nbuf while the MMA warp fills the other buffers, so up to four
+//                              tiles' TMEM->global latencies overlap on one SM
+constexpr int kEpiGroups = 4;                 // epilogue warp groups, each drains a different tile
+constexpr int kThreads = 64 + kEpiGroups * 128;
+constexpr int kMaxTmemBufs = 4;
+
+__global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[kMaxStages];
   __shared__ uint64_t empty_bar[kMaxStages];
-  __shared__ uint64_t tmem_full_bar;
+  __shared__ uint64_t tmem_full_bar[kMaxTmemBufs];
+  __shared__ uint64_t tmem_empty_bar[kMaxTmemBufs];
   __shared__ uint32_t tmem_base_s;
-  __shared__ float s_scale[256];
-  __shared__ float s_shift[256];
+  __shared__ __align__(16) float s_scale[kMaxCout];
+  __shared__ __align__(16) float s_shift[kMaxCout];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -133,84 +152,114 @@ __global__ void __launch_bounds__(192) conv_gemm_kernel(const __grid_constant__ 
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(&tmem_full_bar, 1);
+    for (int b = 0; b < kMaxTmemBufs; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], 4 * (kEpiGroups / p.nbuf));
+    }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
+  // folded BatchNorm / bias of every output channel, padded so that vector reads past Cout stay in bounds
+  const int cpad = (p.Cout + 7) & ~7;
+  for (int i = threadIdx.x; i < cpad; i += blockDim.x) {
+    s_scale[i] = (p.scale != nullptr && i < p.Cout) ? p.scale[i] : 1.f;
+    s_shift[i] = (p.shift != nullptr && i < p.Cout) ? p.shift[i] : 0.f;
+  }
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_s;
 
-  const int bx = blockIdx.x;
-  const int tw = bx % p.tiles_w;
-  const int th = (bx / p.tiles_w) % p.tiles_h;
-  const int n = bx / (p.tiles_w * p.tiles_h);
-  const int w0 = tw * p.Wt, h0 = th * p.Ht;
-  const int n0 = blockIdx.y * p.BN;
+  const int tiles_m = p.tiles_w * p.tiles_h * p.n_img;
+  const int num_tiles = tiles_m * p.tiles_n;
+  const int my_tiles = ((int)blockIdx.x < num_tiles) ? (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
   if (warp == 0) {
     // ---------------- TMA producer ----------------
-    for (int it = 0; it < p.num_k; ++it) {
-      const int s = it % p.stages;
-      const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
-      mbar_wait(&empty_bar[s], ph ^ 1u);
-      if (lane == 0) {
-        const KEntry e = p.sched[it];
-        mbar_arrive_expect_tx(&full_bar[s], p.a_bytes + (uint32_t)b_stage);
-        tma_load_5d(sA + s * kAStage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
-        tma_load_2d(sB + s * b_stage, &p.b_map, &full_bar[s], it * 64, n0);
+    uint32_t it = 0;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+      const int nt = tile % p.tiles_n, mt = tile / p.tiles_n;
+      const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h, n = mt / (p.tiles_w * p.tiles_h);
+      const int w0 = tw * p.Wt, h0 = th * p.Ht, n0 = nt * p.BN;
+      for (int k = 0; k < p.num_k; ++k, ++it) {
+        const int s = (int)(it % (uint32_t)p.stages);
+        const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
+        mbar_wait(&empty_bar[s], ph ^ 1u);
+        if (lane == 0) {
+          const KEntry e = p.sched[k];
+          mbar_arrive_expect_tx(&full_bar[s], p.a_bytes + (uint32_t)b_stage);
+          tma_load_5d(sA + s * kAStage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
+          tma_load_2d(sB + s * b_stage, &p.b_map, &full_bar[s], k * 64, n0);
+        }
+        __syncwarp();
       }
-      __syncwarp();
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer ----------------
     const uint32_t idesc = umma_idesc_bf16_f32(128, p.BN, 0, 0);
-    for (int it = 0; it < p.num_k; ++it) {
-      const int s = it % p.stages;
-      const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
-      mbar_wait(&full_bar[s], ph);
+    uint32_t it = 0;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int buf = i % p.nbuf;
+      const uint32_t use = (uint32_t)(i / p.nbuf);
+      mbar_wait(&tmem_empty_bar[buf], (use & 1u) ^ 1u);   // epilogue has drained this accumulator
       tc_fence_after_sync();
-      if (lane == 0) {
-        const uint32_t a_base = smem_u32(sA + s * kAStage);
-        const uint32_t b_base = smem_u32(sB + s * b_stage);
+      const uint32_t tmem_d = tmem_base + (uint32_t)(buf * p.BN);
+      for (int k = 0; k < p.num_k; ++k, ++it) {
+        const int s = (int)(it % (uint32_t)p.stages);
+        const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after_sync();
+        if (lane == 0) {
+          const uint32_t a_base = smem_u32(sA + s * kAStage);
+          const uint32_t b_base = smem_u32(sB + s * b_stage);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint64_t adesc = umma_smem_desc_sw128(a_base + k * 32, 16, 1024);
-          const uint64_t bdesc = umma_smem_desc_sw128(b_base + k * 32, 16, 1024);
-          umma_bf16(tmem_base, adesc, bdesc, idesc, (uint32_t)((it | k) != 0));
+          for (int kk = 0; kk < 4; ++kk) {
+            const uint64_t adesc = umma_smem_desc_sw128(a_base + kk * 32, 16, 1024);
+            const uint64_t bdesc = umma_smem_desc_sw128(b_base + kk * 32, 16, 1024);
+            umma_bf16(tmem_d, adesc, bdesc, idesc, (uint32_t)((k | kk) != 0));
+          }
+          umma_commit(&empty_bar[s]);
+          if (k == p.num_k - 1) umma_commit(&tmem_full_bar[buf]);
         }
-        umma_commit(&empty_bar[s]);
-        if (it == p.num_k - 1) umma_commit(&tmem_full_bar);
+        __syncwarp();
       }
-      __syncwarp();
     }
   } else {
     // ---------------- epilogue ----------------
-    const int et = threadIdx.x - 64;
-    for (int i = et; i < p.BN; i += 128) {
-      const int c = n0 + i;
-      s_scale[i] = (p.scale != nullptr && c < p.Cout) ? p.scale[c] : 1.f;
-      s_shift[i] = (p.shift != nullptr && c < p.Cout) ? p.shift[c] : 0.f;
-    }
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-
-    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    const int q = warp & 3;             // TMEM lane quadrant this warp may read
+    // Group g serves TMEM buffer g % nbuf; when there are fewer buffers than groups (wide tiles), the groups that
+    // share a buffer split its columns.  Each mbarrier is then waited on for consecutive phases only.
+    const int grp = (warp - 2) >> 2;
+    const int slot = grp % p.nbuf;
+    const int part = grp / p.nbuf;
+    const int nparts = kEpiGroups / p.nbuf;
     const int r = q * 32 + lane;
     const int hh = r / p.Wt;
     const int ww = r - hh * p.Wt;
-    const int h = h0 + hh, w = w0 + ww;
-    const bool valid = (r < p.Wt * p.Ht) && (h < p.Hout) && (w < p.Wout);
-    const long pix = ((long)n * p.Hout + h) * p.Wout + w;
-    mbar_wait(&tmem_full_bar, 0);
-    tc_fence_after_sync();
-    const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
-    switch (p.act) {  // activation resolved once per tile: the column loop is branch-free
-      case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
-      case LY_ACT_SILU: epilogue_cols<LY_ACT_SILU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
-      case LY_ACT_HSWISH: epilogue_cols<LY_ACT_HSWISH>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
-      case LY_ACT_SIGMOID: epilogue_cols<LY_ACT_SIGMOID>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
-      default: epilogue_cols<LY_ACT_NONE>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift); break;
+    for (int i = slot; i < my_tiles; i += p.nbuf) {
+      const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+      const int nt = tile % p.tiles_n, mt = tile / p.tiles_n;
+      const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h, n = mt / (p.tiles_w * p.tiles_h);
+      const int h = th * p.Ht + hh, w = tw * p.Wt + ww, n0 = nt * p.BN;
+      const bool valid = (r < p.Wt * p.Ht) && (h < p.Hout) && (w < p.Wout);
+      const long pix = ((long)n * p.Hout + h) * p.Wout + w;
+      const int buf = i % p.nbuf;
+      const uint32_t use = (uint32_t)(i / p.nbuf);
+      mbar_wait(&tmem_full_bar[buf], use & 1u);
+      tc_fence_after_sync();
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);
+      const int cb = part * 16, cs = nparts * 16;
+      switch (p.act) {  // activation resolved once per tile: the column loop is branch-free
+        case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;
+        case LY_ACT_SILU: epilogue_cols<LY_ACT_SILU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;
+        case LY_ACT_HSWISH: epilogue_cols<LY_ACT_HSWISH>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;
+        case LY_ACT_SIGMOID: epilogue_cols<LY_ACT_SIGMOID>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;
+        default: epilogue_cols<LY_ACT_NONE>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
     }
   }
 
@@ -298,7 +347,7 @@ static int set_smem_attr_once() {
   LY_CUDA(cudaGetDevice(&dev));
   cudaError_t err = cudaSuccess;
   std::call_once(flags[dev & 63], [&] {
-    err = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024);
+    err = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   });
   if (err != cudaSuccess) return fail(LY_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(err));
   return LY_OK;
@@ -414,8 +463,11 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
   const int ny = ceil_div(cout_r, 256);
   p.BN = (ceil_div(cout_r, ny) + 15) / 16 * 16;
   p.Cout = d->Cout;
+  p.tiles_n = ny;
+  LY_REQUIRE(d->Cout <= kMaxCout, "Cout=%d exceeds %d", d->Cout, kMaxCout);
+  p.nbuf = p.BN <= 128 ? 4 : 2;   // accumulators in flight; must divide kEpiGroups
   p.tmem_cols = 32;
-  while (p.tmem_cols < p.BN) p.tmem_cols *= 2;
+  while (p.tmem_cols < p.nbuf * p.BN) p.tmem_cols *= 2;
   {
     uint64_t dims[2] = {(uint64_t)num_k * 64, (uint64_t)d->Cout};
     uint64_t str[1] = {(uint64_t)num_k * 64 * 2};
@@ -424,10 +476,9 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
     if (rc != LY_OK) return rc;
   }
   const int stage_bytes = kAStage + p.BN * 128;
-  // at most ~100 KB of shared memory per CTA: two or more CTAs per SM, so one CTA's epilogue overlaps another's
-  // TMA/MMA main loop (TMEM: 2 x 256 columns still fit)
-  p.stages = num_k < kMaxStages ? num_k : kMaxStages;
-  while (p.stages > 2 && p.stages * stage_bytes > 100 * 1024) --p.stages;
+  // one persistent CTA per SM: as deep a TMA ring as fits (<= 8 slots, <= ~190 KB)
+  p.stages = kMaxStages;
+  while (p.stages > 2 && p.stages * stage_bytes > 196 * 1024) --p.stages;
   const size_t smem_bytes = (size_t)p.stages * stage_bytes + 1024;
 
   // ---- epilogue
@@ -448,8 +499,10 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
 
   rc = set_smem_attr_once();
   if (rc != LY_OK) return rc;
-  dim3 grid((unsigned)(p.tiles_w * p.tiles_h * p.n_img), (unsigned)ny, 1);
-  conv_gemm_kernel<<<grid, 192, smem_bytes, (cudaStream_t)stream>>>(p);
+  const long num_tiles = (long)p.tiles_w * p.tiles_h * p.n_img * ny;
+  const int sms = device_sm_count();
+  dim3 grid((unsigned)(num_tiles < sms ? num_tiles : sms), 1, 1);
+  conv_gemm_kernel<<<grid, kThreads, smem_bytes, (cudaStream_t)stream>>>(p);
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
