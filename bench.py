@@ -134,12 +134,110 @@ def cpu_reference_run(steps, warmup, sample_imgs):
     return sample_imgs * steps / dt, dt / steps * 1e3, cores
 
 
+def train_bench(args, warm, rank, local, world, dev):
+    """configs[2]: training forward + backward (+ SGD step) at bs=64/GPU, DDP gradient all-reduce over NCCL.
+    The loss is a surrogate (mean square of the three raw heads, scaled by WORLD_SIZE as train.py:321-322): the
+    reference's ComputeLoss is outside the hot path."""
+    import torch.distributed as dist
+    from lead_yolo_b200 import lowlevel as ll
+    from lead_yolo_b200.model import build_lead_yolo
+    model = build_lead_yolo("lead", 1, dev, seed=0).train()
+    net = model
+    if world > 1:
+        net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], output_device=local,
+                                                        static_graph=True)
+    opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.937, nesterov=True)
+    nbuf = 3
+    host = [sar_like_batch(args.batch, IMG, 100 * rank + i).pin_memory() for i in range(nbuf)]
+    dimg = [h.to(dev, non_blocking=True) for h in host]
+
+    def step(img):
+        raw = net(img)
+        loss = sum(r.float().square().mean() for r in raw) * world
+        loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(warm):
+        step(dimg[i % nbuf])
+    torch.cuda.synchronize()
+    ll.COUNT[0] = 0
+    step(dimg[0])
+    launches_per_step = ll.COUNT[0]
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step(dimg[i % nbuf])
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = e0.elapsed_time(e1)
+    # end to end: pinned host uint8 batch in, loss scalar out, every step
+    stage = torch.empty_like(dimg[0])
+    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+    barrier()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(args.steps):
+        stage.copy_(host[i % nbuf], non_blocking=True)
+        loss_host.copy_(step(stage).detach(), non_blocking=True)
+    t1.record()
+    barrier()
+    ms_e2e = t0.elapsed_time(t1)
+    ll.PROFILE = []
+    step(dimg[0])
+    torch.cuda.synchronize()
+    prof = {}
+    for name, a, b, nbytes, flops in ll.PROFILE:
+        d = prof.setdefault(name, [0.0, 0, 0.0, 0.0])
+        d[0] += a.elapsed_time(b); d[1] += 1; d[2] += nbytes; d[3] += flops
+    ll.PROFILE = None
+    t = torch.tensor([ms_total, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = t.tolist()
+    if rank == 0:
+        imgs = args.batch * world * args.steps
+        tot_ms = sum(v[0] for v in prof.values())
+        if args.profile_kernels:
+            for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0]):
+                sys.stderr.write(f"[bench] {k:28s} {v[1]:4d} calls {v[0]:9.3f} ms {100 * v[0] / tot_ms:5.1f}%\n")
+        print(json.dumps({
+            "metric": "LEAD-YOLO images/sec @640", "value": imgs / (ms_total / 1e3), "unit": "images/s",
+            "n_gpus": world, "steps": args.steps, "warmup": warm, "ms_per_step": ms_total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "LEAD-YOLO.yaml training fwd+bwd+SGD bs=64/GPU 640x640 (configs[2]), surrogate "
+                                   "loss on the raw heads", "batch_per_gpu": args.batch,
+                       "parallelism": f"DDP dp{world} (NCCL gradient all-reduce)" if world > 1 else "single GPU",
+                       "l2": "inputs rotate over 3 batches; activations >> L2", "cuda_graph": False},
+            "clocks": clocks,
+            "e2e": {"value": imgs / (ms_e2e / 1e3), "unit": "images/s", "h2d_bytes_per_step": int(host[0].numel()),
+                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches_per_step * args.steps),
+            "kernel_ms_per_step": {k: round(v[0], 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])[:8]},
+            "train_roofline_images_per_s_per_gpu": 40600.0}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"],
+                    help="infer = BASELINE configs[1] (default, the driver's line); train = configs[2]: forward + "
+                         "backward + SGD step, DDP over NCCL when --gpus > 1")
     ap.add_argument("--batch", type=int, default=BS)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -170,6 +268,8 @@ def main():
     dev = torch.device("cuda", local)
     from lead_yolo_b200 import lowlevel as ll
     from lead_yolo_b200.model import build_lead_yolo
+    if args.mode == "train":
+        return train_bench(args, warm, rank, local, world, dev)
 
     model = build_lead_yolo("lead", 1, dev, seed=0).eval()
     nbuf = 3   # rotate 3 input batches (3 x 78.6 MB > 126 MB L2)
@@ -307,7 +407,13 @@ def main():
     else:
         roof = {"bound": "hbm", "achieved": tbytes / (tms / 1e3) / 1e9, "peak": hbm, "unit": "GB/s"}
     roof["frac"] = roof["achieved"] / roof["peak"]
-    roof.update({"traffic": None, "kernel": tname, "launches_per_step": tn, "share_of_step": tms / tot_ms,
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r01_conv_traffic.json")
+    if tname == "ly_conv_fwd" and os.path.exists(tpath) and args.batch == BS:
+        tj = json.load(open(tpath))   # DRAM bytes of all launches of this kernel in one step (ncu --set full capture)
+        if tj.get("launches_per_step") == tn:
+            traffic = tj["dram_bytes_read_per_step"] + tj["dram_bytes_write_per_step"]
+    roof.update({"traffic": traffic, "kernel": tname, "launches_per_step": tn, "share_of_step": tms / tot_ms,
                  "peak_source": which, "algorithmic_bytes_per_step": tbytes, "algorithmic_flops_per_step": tflops})
 
     line = {
