@@ -332,38 +332,27 @@ def main():
         clocks = sampler.stop()
         ms_total = e0.elapsed_time(e1)
 
-        # ---- end to end: pinned host uint8 in, decoded predictions out, through model(images)
-        stage = [torch.empty_like(dimg[0]) for _ in range(2)]
-        out_host = torch.empty((args.batch, 25200, 6), dtype=torch.float32).pin_memory()
-        copy_s = torch.cuda.Stream()
-        main_s = torch.cuda.current_stream()
+        # ---- end to end through the public serving call (lead_yolo_b200.engine.InferenceEngine): pinned host uint8
+        # batch in, decoded predictions (B,25200,6) fp32 back on the host, every step; copies overlap the replay
+        from lead_yolo_b200.engine import InferenceEngine
+        eng = InferenceEngine(model, args.batch, IMG, slots=2, device=dev)
+        out_host = eng.host_out[0]
 
         def e2e_loop(k):
-            ready = [torch.cuda.Event() for _ in range(2)]
-            done = [torch.cuda.Event() for _ in range(2)]
-            with torch.cuda.stream(copy_s):
-                stage[0].copy_(host[0], non_blocking=True)
-                ready[0].record(copy_s)
+            last = None
             for i in range(k):
-                b = i % 2
-                if i + 1 < k:   # prefetch the next batch on the copy stream while this one computes
-                    with torch.cuda.stream(copy_s):
-                        if i >= 1:
-                            copy_s.wait_event(done[(i + 1) % 2])
-                        stage[(i + 1) % 2].copy_(host[(i + 1) % nbuf], non_blocking=True)
-                        ready[(i + 1) % 2].record(copy_s)
-                main_s.wait_event(ready[b])
-                pred = model(stage[b])[0]
-                done[b].record(main_s)
-                out_host.copy_(pred, non_blocking=True)
-            main_s.synchronize()
+                s_ = eng.submit(host[i % nbuf])
+                if last is not None:
+                    eng.result(last)           # the host consumes batch i-1 while batch i is in flight
+                last = s_
+            eng.result(last)
 
         e2e_loop(3)
         barrier()
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0.record()
+        t0.record(eng.s_in)                    # all streams idle after the barrier: first H2D starts here
         e2e_loop(args.steps)
-        t1.record()
+        t1.record(eng.s_out)                   # after the last D2H
         barrier()
         ms_e2e = t0.elapsed_time(t1)
 

@@ -135,6 +135,13 @@ int ly_copy_upsample(const void* src, long lds, int N, int Hs, int Ws, int C, in
                      ly_stream_t stream);
 int ly_downsum2(const void* src, long lds, int N, int H, int W, int C, void* dst, long ldd, ly_stream_t stream);
 
+/* Detect post-processing of one level (models/yolo.py:95-125), fp32: p = conv output [N][ny][nx][na*no] (NHWC);
+ * raw [N][na][ny][nx][no] (the permuted view training consumes) and/or the decoded rows of this level inside
+ * z [N][rows_total][no] at row_off + a*ny*nx + y*nx + x: xy = (2s - 0.5 + grid)*stride, wh = (2s)^2 * anchor*stride,
+ * rest = s, s = sigmoid.  anchors: [na][2] in stride units (Detect.anchors[i]). */
+int ly_detect_decode(const float* p, int N, int ny, int nx, int na, int no, float stride, const float* anchors,
+                     float* raw, float* z, long rows_total, long row_off, ly_stream_t stream);
+
 /* rfa.SE global average pool (models/rfa.py:80,90): bf16 [N][C] <- mean over HW. */
 int ly_gap(const void* x, long ldx, int N, int HW, int C, void* out, long ldo, ly_stream_t stream);
 
@@ -143,6 +150,12 @@ int ly_gap(const void* x, long ldx, int N, int HW, int C, void* out, long ldo, l
  * row N*H + n*W + w = mean_h x[n,:,w,c].  Gates use the same row layout.
  * ------------------------------------------------------------------------------------------------------ */
 int ly_ca_pool(const void* x, long ldx, int N, int H, int W, int C, void* pooled, long ldp, ly_stream_t stream);
+/* Inference: everything between pooling and gating in one kernel (common.py:1601-1608).  pooled/gates: "HW rows"
+ * matrices with `rows` rows of which the first nh use conv_h (wh [C][mip], bh [C]) and the rest conv_w (ww, bw);
+ * w1 [mip][C] = conv1.weight; scale/shift [mip] = bn1 folded with conv1.bias; mip <= 32. */
+int ly_ca_mid_infer(const void* pooled, long ldp, long rows, long nh, int C, int mip, const float* w1,
+                    const float* scale, const float* shift, const float* wh, const float* bh, const float* ww,
+                    const float* bw, void* gates, long ldg, ly_stream_t stream);
 int ly_ca_apply(const void* x, long ldx, const void* gates, long ldg, int N, int H, int W, int C, void* out,
                 long ldo, ly_stream_t stream); /* out = x * a_h[n,h,c] * a_w[n,w,c] */
 int ly_ca_gate_grad(const void* x, long ldx, const void* dy, long lddy, const void* gates, long ldg, int N, int H,

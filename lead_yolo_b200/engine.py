@@ -1,0 +1,70 @@
+"""Pipelined inference front end: host uint8 images in, decoded predictions out.
+
+`InferenceEngine` captures the whole LEAD-YOLO forward (stem .. Detect decode) into CUDA graphs bound to static
+device buffers and overlaps, on three streams, the host->device copy of batch i+1, the graph replay of batch i and the
+device->host copy of batch i-1.  This is the call a serving user makes; the modules themselves stay ordinary
+nn.Modules (bs=1 is launch-bound without graph capture).
+"""
+from __future__ import annotations
+
+import torch
+
+
+class InferenceEngine:
+    def __init__(self, model: torch.nn.Module, batch: int, img: int = 640, slots: int = 2, device=None):
+        self.model = model.eval()
+        self.device = torch.device(device) if device is not None else next(model.parameters()).device
+        self.slots = slots
+        self.s_in, self.s_run, self.s_out = (torch.cuda.Stream(self.device) for _ in range(3))
+        self.inp = [torch.zeros((batch, 3, img, img), dtype=torch.uint8, device=self.device) for _ in range(slots)]
+        self.graphs, self.out = [], []
+        with torch.no_grad():
+            self.s_run.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self.s_run):
+                for _ in range(2):          # warm-up: fills weight-pack caches, Detect grids
+                    self.model(self.inp[0])
+            self.s_run.synchronize()
+            for s in range(slots):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self.s_run):
+                    o = self.model(self.inp[s])
+                self.graphs.append(g)
+                self.out.append(o[0])
+        self.host_out = [torch.empty(self.out[0].shape, dtype=self.out[0].dtype).pin_memory() for _ in range(slots)]
+        self.ev_in = [torch.cuda.Event() for _ in range(slots)]
+        self.ev_run = [torch.cuda.Event() for _ in range(slots)]
+        self.ev_out = [torch.cuda.Event() for _ in range(slots)]
+        self._n = 0
+
+    def submit(self, host_images: torch.Tensor) -> int:
+        """Enqueue one pinned uint8 (B,3,H,W) host batch; returns the slot whose host_out will hold the result."""
+        s = self._n % self.slots
+        first = self._n < self.slots
+        with torch.cuda.stream(self.s_in):
+            if not first:
+                self.s_in.wait_event(self.ev_run[s])       # previous replay on this slot has consumed its input
+            self.inp[s].copy_(host_images, non_blocking=True)
+            self.ev_in[s].record(self.s_in)
+        with torch.cuda.stream(self.s_run):
+            self.s_run.wait_event(self.ev_in[s])
+            if not first:
+                self.s_run.wait_event(self.ev_out[s])      # previous result of this slot has left the device
+            self.graphs[s].replay()
+            self.ev_run[s].record(self.s_run)
+        with torch.cuda.stream(self.s_out):
+            self.s_out.wait_event(self.ev_run[s])
+            self.host_out[s].copy_(self.out[s], non_blocking=True)
+            self.ev_out[s].record(self.s_out)
+        self._n += 1
+        return s
+
+    def result(self, slot: int) -> torch.Tensor:
+        """Host tensor (B, 25200, 6) of the batch submitted to `slot`; valid until the slot is reused."""
+        self.ev_out[slot].synchronize()
+        return self.host_out[slot]
+
+    def __call__(self, host_images: torch.Tensor) -> torch.Tensor:
+        return self.result(self.submit(host_images))
+
+    def drain(self):
+        self.s_out.synchronize()

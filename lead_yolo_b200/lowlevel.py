@@ -159,7 +159,9 @@ _SIGS = {
     "ly_copy_upsample": "pliiiiipl",
     "ly_downsum2": "pliiiipl",
     "ly_gap": "pliiipl",
+    "ly_detect_decode": "piiiiifpppll",
     "ly_ca_pool": "pliiiipl",
+    "ly_ca_mid_infer": "plllii" + "ppppppp" + "pl",
     "ly_ca_apply": "plpliiiipl",
     "ly_ca_gate_grad": "plplpliiiipl",
     "ly_ca_pool_bwd": "pliiiipl",

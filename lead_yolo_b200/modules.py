@@ -463,8 +463,17 @@ class CoordAtt(nn.Module):
             raise LeadYoloError("CoordAtt: oup must equal the input channels")
         fast = _fast(self)
         p = ops.CaPoolFn.apply(x)                                   # (1, c, n*h + n*w, 1)
-        y = conv_bn_act(self.conv1, self.bn1, "hswish", [p], fast)   # (1, mip, rows, 1)
         nh = n * h
+        if fast and self.conv1.out_channels <= 32:
+            f32 = lambda t, tag: ops.cached([t], tag, lambda: t.detach().float().reshape(t.shape[0], -1).contiguous())  # noqa: E731
+            scale, shift = ops.bn_fold(self.bn1, self.conv1.bias)
+            gates = ll.empty_cl(1, c, n * (h + w), 1, device=x.device)
+            ll.call("ly_ca_mid_infer", p, c, n * (h + w), nh, c, self.conv1.out_channels,
+                    f32(self.conv1.weight, "caw1"), scale, shift, f32(self.conv_h.weight, "cawh"),
+                    f32(self.conv_h.bias, "cabh"), f32(self.conv_w.weight, "caww"), f32(self.conv_w.bias, "cabw"),
+                    gates, c)
+            return ops.CaApplyFn.apply(x, gates)
+        y = conv_bn_act(self.conv1, self.bn1, "hswish", [p], fast)   # (1, mip, rows, 1)
         if fast:
             gates = ll.empty_cl(1, c, n * (h + w), 1, device=x.device)
             conv_bn_act(self.conv_h, None, "sigmoid", [y[:, :, :nh]], True, out=gates[:, :, :nh])
@@ -618,6 +627,27 @@ class Detect(nn.Module):
         z = []
         x = list(x)
         fast = _fast(self)
+        if fast and not self.export and torch.is_tensor(self.stride):
+            # inference: conv heads on the tensor cores, then one fp32 kernel per level writes both the permuted raw
+            # map and this level's decoded rows straight into the concatenated (bs, sum na*ny*nx, no) output
+            shapes = [(int(t.shape[2]), int(t.shape[3])) for t in x]
+            bs = int(x[0].shape[0])
+            rows = sum(self.na * ny * nx for ny, nx in shapes)
+            zcat = torch.empty((bs, rows, self.no), dtype=torch.float32, device=x[0].device)
+            off = 0
+            for i in range(self.nl):
+                m = self.m[i]
+                ny, nx = shapes[i]
+                wp = ops.cached([m.weight], ("wp", (m.in_channels,)), lambda: pack_conv_weight(m.weight, None))
+                b = ops.cached([m.bias], "b32", lambda: m.bias.detach().float().contiguous())
+                y = ops.conv_infer([x[i]], wp, m.out_channels, shift=b, out_fp32=True)
+                raw = torch.empty((bs, self.na, ny, nx, self.no), dtype=torch.float32, device=y.device)
+                anc = ops.cached([self.anchors], ("anc", i), lambda: self.anchors[i].detach().float().contiguous())
+                ll.call("ly_detect_decode", y, bs, ny, nx, self.na, self.no, float(self.stride[i]), anc, raw, zcat,
+                        rows, off)
+                x[i] = raw
+                off += self.na * ny * nx
+            return zcat, x
         for i in range(self.nl):
             m = self.m[i]
             if fast:
