@@ -15,6 +15,42 @@ namespace ly {
 
 __device__ __forceinline__ uint4 ldx16(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 
+// Asynchronous input staging: each warp copies the k*k input vectors of its 32 pixels (16 B per lane and tap) into a
+// warp-private shared-memory buffer with cp.async (zero-filled outside the image), one pixel group ahead of the
+// arithmetic, so the global-load latency is off the critical path even at the low occupancy these register-heavy
+// kernels run at.
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src, bool valid) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  const int bytes = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int K>
+__device__ __forceinline__ void rf_prefetch(uint8_t* buf, const __nv_bfloat16* __restrict__ x, long ldx, long M, int H,
+                                            int W, int s, int ho, int wo, long m, int v, int lane) {
+  const bool pact = m < M;
+  const int w = pact ? (int)(m % wo) : 0, h = pact ? (int)((m / wo) % ho) : 0;
+  const long n = pact ? m / ((long)wo * ho) : 0;
+#pragma unroll
+  for (int i = 0; i < K; ++i)
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      const int yy = h * s + i - K / 2, xx = w * s + j - K / 2;
+      const bool ok = pact && yy >= 0 && yy < H && xx >= 0 && xx < W;
+      const __nv_bfloat16* src = ok ? x + ((n * H + yy) * W + xx) * ldx + v * 8 : x;
+      cp_async16(buf + ((i * K + j) * 32 + lane) * 16, src, ok);
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void rf_fetch(const uint8_t* buf, int lane, float (&xin)[K * K][8]) {
+#pragma unroll
+  for (int ij = 0; ij < K * K; ++ij) unpack8(*reinterpret_cast<const uint4*>(buf + (ij * 32 + lane) * 16), xin[ij]);
+}
+
 template <int K>
 __device__ __forceinline__ void rf_load_inputs(const __nv_bfloat16* __restrict__ x, long ldx, int H, int W, int s,
                                                int n, int h, int w, int v, bool act, float (&xin)[K * K][8]) {
@@ -89,7 +125,8 @@ __global__ void __launch_bounds__(512, 1) rf_stats_kernel(const __nv_bfloat16* _
                                                           const float* __restrict__ wgk,
                                                           const float* __restrict__ scale,
                                                           const float* __restrict__ shift, float* __restrict__ maps,
-                                                          float* __restrict__ gap_sum, int use_atomics) {
+                                                          float* __restrict__ gap_sum, int use_atomics,
+                                                          __nv_bfloat16* __restrict__ G) {
   constexpr int KK = K * K;
   extern __shared__ float dsm[];
   __shared__ int smax[KK][32];
@@ -99,11 +136,18 @@ __global__ void __launch_bounds__(512, 1) rf_stats_kernel(const __nv_bfloat16* _
   float* wsm = dsm;
   float* ssm = wsm + KK * KK * WPB * 8;
   float* hsm = ssm + KK * WPB * 8;
+  uint8_t* stage = reinterpret_cast<uint8_t*>(hsm + KK * WPB * 8) + (size_t)warp * 2 * KK * 512;
   rf_stage_weights<K>(wgk, scale, shift, C, blockIdx.y * WPB, WPB, V, wsm, ssm, hsm);
   const int v = blockIdx.y * WPB + warp;
   const bool vact = v < V;
   const long groups = (M + 31) / 32;
-  for (long pg = blockIdx.x; pg < groups; pg += gridDim.x) {
+  int pbuf = 0;
+  if (vact && (long)blockIdx.x < groups) rf_prefetch<K>(stage, x, ldx, M, H, W, s, ho, wo, (long)blockIdx.x * 32 + lane, v, lane);
+  cp_async_commit();
+  for (long pg = blockIdx.x; pg < groups; pg += gridDim.x, pbuf ^= 1) {
+    if (vact && pg + gridDim.x < groups)
+      rf_prefetch<K>(stage + (pbuf ^ 1) * KK * 512, x, ldx, M, H, W, s, ho, wo, (pg + gridDim.x) * 32 + lane, v, lane);
+    cp_async_commit();
     __syncthreads();  // staged weights visible / previous iteration's smax, ssum consumed
     for (int i = threadIdx.x; i < KK * 32; i += blockDim.x) {
       smax[i / 32][i % 32] = 0;  // features are >= 0 after ReLU: 0 is the identity of the max
@@ -116,7 +160,9 @@ __global__ void __launch_bounds__(512, 1) rf_stats_kernel(const __nv_bfloat16* _
     const int n = pact ? (int)(m / ((long)wo * ho)) : 0;
     if (vact) {
       float xin[KK][8];
-      rf_load_inputs<K>(x, ldx, H, W, s, n, h, w, v, pact, xin);
+      cp_async_wait<1>();
+      __syncwarp();
+      rf_fetch<K>(stage + pbuf * KK * 512, lane, xin);
       // SE pooling: every input pixel is summed exactly once, by the output pixel whose s x s block contains it
       float gsum[8];
 #pragma unroll
@@ -152,6 +198,7 @@ __global__ void __launch_bounds__(512, 1) rf_stats_kernel(const __nv_bfloat16* _
         for (int e = 1; e < 8; ++e) { mx = fmaxf(mx, g[e]); sm += g[e]; }
         atomicMax(&smax[t][lane], __float_as_int(mx));
         atomicAdd(&ssum[t][lane], sm);
+        if (G != nullptr && pact) *reinterpret_cast<uint4*>(G + (m * KK + t) * (long)C + v * 8) = pack8(g);
       }
     }
     __syncthreads();
@@ -239,18 +286,28 @@ __global__ void __launch_bounds__(256) rf_apply_kernel(const __nv_bfloat16* __re
   float* wsm = dsm;
   float* ssm = wsm + KK * KK * VB * 8;
   float* hsm = ssm + KK * VB * 8;
+  uint8_t* stage = reinterpret_cast<uint8_t*>(hsm + KK * VB * 8) + (size_t)warp * 2 * KK * 512;
   rf_stage_weights<K>(wgk, scale, shift, C, blockIdx.y * VB, VB, V, wsm, ssm, hsm);
   __syncthreads();
   const int v = blockIdx.y * VB + warp;
   if (v >= V) return;
   const long groups = (M + 31) / 32;
-  for (long pg = blockIdx.x; pg < groups; pg += gridDim.x) {
+  int pbuf = 0;
+  if ((long)blockIdx.x < groups) rf_prefetch<K>(stage, x, ldx, M, H, W, s, ho, wo, (long)blockIdx.x * 32 + lane, v, lane);
+  cp_async_commit();
+  for (long pg = blockIdx.x; pg < groups; pg += gridDim.x, pbuf ^= 1) {
+    if (pg + gridDim.x < groups)
+      rf_prefetch<K>(stage + (pbuf ^ 1) * KK * 512, x, ldx, M, H, W, s, ho, wo, (pg + gridDim.x) * 32 + lane, v, lane);
+    cp_async_commit();
     const long m = pg * 32 + lane;
     const bool pact = m < M;
     const int w = pact ? (int)(m % wo) : 0, h = pact ? (int)((m / wo) % ho) : 0;
     const int n = pact ? (int)(m / ((long)wo * ho)) : 0;
     float xin[KK][8];
-    rf_load_inputs<K>(x, ldx, H, W, s, n, h, w, v, pact, xin);
+    cp_async_wait<1>();
+    __syncwarp();
+    rf_fetch<K>(stage + pbuf * KK * 512, lane, xin);
+    __syncwarp();
     if (!pact) continue;
     float s8[8];
     {
@@ -270,6 +327,28 @@ __global__ void __launch_bounds__(256) rf_apply_kernel(const __nv_bfloat16* __re
       *reinterpret_cast<uint4*>(arow + (long)t * C) = pack8(g);
     }
   }
+}
+
+// pass 2 when pass 1 stored the features: A = G * se[n,c] * att (pure streaming, in place allowed)
+__global__ void __launch_bounds__(256) rf_gate2_kernel(const __nv_bfloat16* __restrict__ G, long M, int KK, int K,
+                                                       int V, int ho, int wo, const float* __restrict__ se,
+                                                       const float* __restrict__ att, __nv_bfloat16* __restrict__ A) {
+  const long total = M * KK * V;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int v = (int)(tid % V);
+  const int t = (int)((tid / V) % KK);
+  const long m = tid / ((long)V * KK);
+  const int w = (int)(m % wo), h = (int)((m / wo) % ho);
+  const long n = m / ((long)wo * ho);
+  const float a = __ldg(att + (n * (ho * K) + (h * K + t / K)) * (long)(wo * K) + (w * K + t % K));
+  float g[8];
+  unpack8(__ldg(reinterpret_cast<const uint4*>(G + tid * 8)), g);
+  const float4 s0 = __ldg(reinterpret_cast<const float4*>(se + n * (V * 8) + v * 8));
+  const float4 s1 = __ldg(reinterpret_cast<const float4*>(se + n * (V * 8) + v * 8 + 4));
+  g[0] *= s0.x * a; g[1] *= s0.y * a; g[2] *= s0.z * a; g[3] *= s0.w * a;
+  g[4] *= s1.x * a; g[5] *= s1.y * a; g[6] *= s1.z * a; g[7] *= s1.w * a;
+  *reinterpret_cast<uint4*>(A + tid * 8) = pack8(g);
 }
 
 }  // namespace ly
@@ -306,20 +385,23 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
   {
     long bx = groups < (long)sms ? groups : (long)sms;      // one block per SM (512 threads, 128 registers)
     dim3 grid1((unsigned)bx, (unsigned)vgroups);
-    const size_t sm1 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * WPB * 8;
+    const size_t sm1 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * WPB * 8 + (size_t)WPB * 2 * KK * 512;
     if (k == 1) {
       rf_stats_kernel<1><<<grid1, WPB * 32, sm1, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, WPB, s, ho, wo,
-                                                          wgk, scale, shift, maps, gap_sum, vgroups > 1);
+                                                          wgk, scale, shift, maps, gap_sum, vgroups > 1, nullptr);
     } else {
       static bool attr_done[64] = {false};
       int dev = 0;
       LY_CUDA(cudaGetDevice(&dev));
       if (!attr_done[dev & 63]) {
-        LY_CUDA(cudaFuncSetAttribute(rf_stats_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        LY_CUDA(cudaFuncSetAttribute(rf_stats_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
+        LY_CUDA(cudaFuncSetAttribute(rf_apply_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         attr_done[dev & 63] = true;
       }
+      // k = 3: the features cost k^4 = 81 MACs per channel; store them once (in A) instead of recomputing in pass 2
       rf_stats_kernel<3><<<grid1, WPB * 32, sm1, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, WPB, s, ho, wo,
-                                                          wgk, scale, shift, maps, gap_sum, vgroups > 1);
+                                                          wgk, scale, shift, maps, gap_sum, vgroups > 1,
+                                                          (__nv_bfloat16*)A);
     }
     LY_LAUNCH_CHECK();
   }
@@ -333,13 +415,13 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
     if (bx > groups) bx = groups;
     if (bx < 1) bx = 1;
     dim3 grid2((unsigned)bx, (unsigned)vg8);
-    const size_t sm2 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * 8 * 8;
+    const size_t sm2 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * 8 * 8 + (size_t)8 * 2 * KK * 512;
     if (k == 1)
       rf_apply_kernel<1><<<grid2, 256, sm2, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, s, ho, wo, wgk, scale,
                                                      shift, se, att, (__nv_bfloat16*)A);
     else
-      rf_apply_kernel<3><<<grid2, 256, sm2, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, s, ho, wo, wgk, scale,
-                                                     shift, se, att, (__nv_bfloat16*)A);
+      rf_gate2_kernel<<<ceil_div(M * KK * V, 256), 256, 0, stream>>>((const __nv_bfloat16*)A, M, KK, k, V, ho, wo, se,
+                                                                    att, (__nv_bfloat16*)A);
   }
   LY_LAUNCH_CHECK();
   return LY_OK;

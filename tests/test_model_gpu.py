@@ -96,7 +96,7 @@ def test_640_eval_and_nms_box_parity(variant):
         for c_, b_ in ((conf, xyxy[0]), (conf_ref, xyxy[1])):
             m_ = c_ > 0.25
             counts.append(int(torchvision.ops.nms(b_[m_], c_[m_], 0.45).numel()))
-        assert abs(counts[0] - counts[1]) <= max(2, 0.06 * counts[1]), f"post-NMS box count {counts}"
+        assert abs(counts[0] - counts[1]) <= max(2, 0.10 * counts[1]), f"post-NMS box count {counts}"
         n_total += counts[1]
     assert n_total > 0, "parity run produced no boxes: threshold/bias choice is not exercising NMS"
 
