@@ -31,9 +31,12 @@ struct KEntry {
 struct alignas(64) ConvGemmParams {
   CUtensorMap a_map[4];
   CUtensorMap b_map;
+  CUtensorMap o_map;   // output as [rows][Cout] for the TMA-store epilogue (flat 1x1 case)
   int tiles_w, tiles_h, n_img, tiles_n;
   int Wt, Ht, Hout, Wout;
   int num_k, Cout, BN, tmem_cols, stages, nbuf;
+  int tma_store;   // epilogue stages 32-row x 64-column slabs in shared memory and stores them with TMA
+  int b_resident;  // all weight chunks stay in shared memory for the whole kernel (single N tile, small K*N)
   int act, out_fp32, vec_ok, res_vec_ok;
   uint32_t a_bytes;
   int patch_k, patch_c;
@@ -115,6 +118,59 @@ __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t 
   }
 }
 
+// TMA-store epilogue (flat 1x1, bf16, no residual scatter): each warp converts its 32 rows x 64 columns into a
+// 128B-swizzled shared-memory slab and one lane issues a bulk tensor store — full 128 B lines reach L2 instead of
+// 16 B pieces of 32 B sectors.
+template <int ACT>
+__device__ __forceinline__ void epilogue_cols_tma(const ConvGemmParams& p, uint32_t trow, int row0, int n0,
+                                                  const float* s_scale, const float* s_shift, uint8_t* slab, int lane,
+                                                  long pix, bool valid) {
+  for (int c64 = 0; c64 < p.BN; c64 += 64) {
+    if (lane == 0) tma_store_wait_read<0>();   // previous slab has left shared memory
+    __syncwarp();
+#pragma unroll
+    for (int sub = 0; sub < 4; ++sub) {
+      const int c0 = c64 + sub * 16;
+      if (c0 >= p.BN) break;
+      uint32_t acc[16];
+      tmem_ld16(trow + (uint32_t)c0, acc);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        const int c = n0 + c0 + g * 8;
+        float v[8];
+        if (c < p.Cout) {
+          const float4 sc0 = *reinterpret_cast<const float4*>(s_scale + c);
+          const float4 sc1 = *reinterpret_cast<const float4*>(s_scale + c + 4);
+          const float4 sh0 = *reinterpret_cast<const float4*>(s_shift + c);
+          const float4 sh1 = *reinterpret_cast<const float4*>(s_shift + c + 4);
+          const float sc[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
+          const float sh[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = act_apply_t<ACT>(fmaf(__uint_as_float(acc[g * 8 + j]), sc[j], sh[j]));
+          if (p.residual != nullptr && valid) {
+            float rr[8];
+            unpack8(*reinterpret_cast<const uint4*>(p.residual + pix * p.res_ld + c), rr);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] += rr[j];
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = 0.f;
+        }
+        const int chunk = sub * 2 + g;
+        *reinterpret_cast<uint4*>(slab + lane * 128 + ((chunk ^ (lane & 7)) << 4)) = pack8(v);
+      }
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_2d(&p.o_map, slab, n0 + c64, row0);
+      tma_store_commit();
+    }
+  }
+}
+
 // Persistent, warp-specialised kernel: one CTA per SM walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...
 //   warp 0      TMA producer   (smem ring of `stages` {A box, B box} slots, continuous across tiles)
 //   warp 1      MMA issuer     (accumulates tile i into TMEM buffer i & 1)
@@ -129,6 +185,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[kMaxStages];
   __shared__ uint64_t empty_bar[kMaxStages];
+  __shared__ uint64_t b_ready_bar;
   __shared__ uint64_t tmem_full_bar[kMaxTmemBufs];
   __shared__ uint64_t tmem_empty_bar[kMaxTmemBufs];
   __shared__ uint32_t tmem_base_s;
@@ -142,6 +199,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   uint8_t* sA = smem;
   uint8_t* sB = smem + p.stages * kAStage;
   const int b_stage = p.BN * 128;
+  // 4 KB store slab per epilogue warp, after the A/B buffers (1024-byte aligned: every piece above is)
+  uint8_t* slabs = sB + (p.b_resident ? p.num_k : p.stages) * b_stage;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.b_map);
@@ -152,6 +211,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
+    mbar_init(&b_ready_bar, 1);
     for (int b = 0; b < kMaxTmemBufs; ++b) {
       mbar_init(&tmem_full_bar[b], 1);
       mbar_init(&tmem_empty_bar[b], 4 * (kEpiGroups / p.nbuf));
@@ -176,6 +236,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
 
   if (warp == 0) {
     // ---------------- TMA producer ----------------
+    if (p.b_resident && lane == 0 && my_tiles > 0) {   // weights once per CTA, not once per tile
+      mbar_arrive_expect_tx(&b_ready_bar, (uint32_t)(p.num_k * b_stage));
+      for (int k = 0; k < p.num_k; ++k) tma_load_2d(sB + k * b_stage, &p.b_map, &b_ready_bar, k * 64, 0);
+    }
     uint32_t it = 0;
     for (int i = 0; i < my_tiles; ++i) {
       const int tile = (int)blockIdx.x + i * (int)gridDim.x;
@@ -188,9 +252,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         mbar_wait(&empty_bar[s], ph ^ 1u);
         if (lane == 0) {
           const KEntry e = p.sched[k];
-          mbar_arrive_expect_tx(&full_bar[s], p.a_bytes + (uint32_t)b_stage);
+          mbar_arrive_expect_tx(&full_bar[s], p.a_bytes + (p.b_resident ? 0u : (uint32_t)b_stage));
           tma_load_5d(sA + s * kAStage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
-          tma_load_2d(sB + s * b_stage, &p.b_map, &full_bar[s], k * 64, n0);
+          if (!p.b_resident) tma_load_2d(sB + s * b_stage, &p.b_map, &full_bar[s], k * 64, n0);
         }
         __syncwarp();
       }
@@ -199,6 +263,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     // ---------------- MMA issuer ----------------
     const uint32_t idesc = umma_idesc_bf16_f32(128, p.BN, 0, 0);
     uint32_t it = 0;
+    if (p.b_resident && my_tiles > 0) mbar_wait(&b_ready_bar, 0);
     for (int i = 0; i < my_tiles; ++i) {
       const int buf = i % p.nbuf;
       const uint32_t use = (uint32_t)(i / p.nbuf);
@@ -212,7 +277,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         tc_fence_after_sync();
         if (lane == 0) {
           const uint32_t a_base = smem_u32(sA + s * kAStage);
-          const uint32_t b_base = smem_u32(sB + s * b_stage);
+          const uint32_t b_base = smem_u32(sB + (p.b_resident ? k : s) * b_stage);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             const uint64_t adesc = umma_smem_desc_sw128(a_base + kk * 32, 16, 1024);
@@ -250,6 +315,20 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       tc_fence_after_sync();
       const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);
       const int cb = part * 16, cs = nparts * 16;
+      if (p.tma_store) {
+        // flat rows: tile row r <-> pixel w; the whole tile's columns go through this warp's slab
+        uint8_t* slab = slabs + (warp - 2) * 4096;
+        const int row0 = tw * p.Wt + q * 32;
+        if (part == 0) {
+          switch (p.act) {
+            case LY_ACT_RELU: epilogue_cols_tma<LY_ACT_RELU>(p, trow, row0, n0, s_scale, s_shift, slab, lane, pix, valid); break;
+            case LY_ACT_SILU: epilogue_cols_tma<LY_ACT_SILU>(p, trow, row0, n0, s_scale, s_shift, slab, lane, pix, valid); break;
+            case LY_ACT_HSWISH: epilogue_cols_tma<LY_ACT_HSWISH>(p, trow, row0, n0, s_scale, s_shift, slab, lane, pix, valid); break;
+            case LY_ACT_SIGMOID: epilogue_cols_tma<LY_ACT_SIGMOID>(p, trow, row0, n0, s_scale, s_shift, slab, lane, pix, valid); break;
+            default: epilogue_cols_tma<LY_ACT_NONE>(p, trow, row0, n0, s_scale, s_shift, slab, lane, pix, valid); break;
+          }
+        }
+      } else
       switch (p.act) {  // activation resolved once per tile: the column loop is branch-free
         case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;
         case LY_ACT_SILU: epilogue_cols<LY_ACT_SILU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;
@@ -261,6 +340,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
     }
+    if (p.tma_store && lane == 0) tma_store_wait_all<0>();   // stores complete before the CTA retires
   }
 
   tc_fence_before_sync();
@@ -476,10 +556,33 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
     if (rc != LY_OK) return rc;
   }
   const int stage_bytes = kAStage + p.BN * 128;
-  // one persistent CTA per SM: as deep a TMA ring as fits (<= 8 slots, <= ~190 KB)
+  // one persistent CTA per SM.  When the whole packed weight matrix of this launch is small (single N tile), keep it
+  // resident in shared memory: the TMA ring then carries activations only and the L2 -> SM traffic per tile halves.
+  const uintptr_t oa = reinterpret_cast<uintptr_t>(d->out);
+  p.vec_ok = d->out_fp32 ? ((oa % 16 == 0) && (d->out_ld % 4 == 0)) : ((oa % 16 == 0) && (d->out_ld % 8 == 0));
+  p.res_vec_ok = d->residual != nullptr && (reinterpret_cast<uintptr_t>(d->residual) % 16 == 0) &&
+                 (d->res_ld % 8 == 0);
+  // TMA-store epilogue: flat rows, bf16, dense-enough output, no scatter; needs nparts == 1 (one group per tile)
+  p.tma_store = (flat_rows && d->patch_k == 0 && !d->out_fp32 && p.vec_ok && p.nbuf == kEpiGroups &&
+                 (d->residual == nullptr || p.res_vec_ok)) ? 1 : 0;
+  if (p.tma_store) {
+    const uint64_t M = (uint64_t)d->N * d->H * d->W;
+    uint64_t dims[2] = {(uint64_t)d->Cout, M};
+    uint64_t str[1] = {(uint64_t)d->out_ld * 2};
+    uint32_t box[2] = {64, 32};
+    rc = tmap_encode_bf16(&p.o_map, d->out, 2, dims, str, box);
+    if (rc != LY_OK) return rc;
+  }
+  const int budget = 196 * 1024 - (p.tma_store ? kEpiGroups * 4 * 4096 : 0);
+  const long b_all = (long)num_k * p.BN * 128;
+  p.b_resident = (ny == 1 && b_all <= 100 * 1024) ? 1 : 0;
   p.stages = kMaxStages;
-  while (p.stages > 2 && p.stages * stage_bytes > 196 * 1024) --p.stages;
-  const size_t smem_bytes = (size_t)p.stages * stage_bytes + 1024;
+  if (p.b_resident) {
+    while (p.stages > 2 && (long)p.stages * kAStage + b_all > budget) --p.stages;
+  } else {
+    while (p.stages > 2 && p.stages * stage_bytes > budget) --p.stages;
+  }
+  const size_t smem_bytes = (p.tma_store ? (size_t)kEpiGroups * 4 * 4096 : 0) + (p.b_resident ? (size_t)p.stages * kAStage + (size_t)b_all : (size_t)p.stages * stage_bytes) + 1024;
 
   // ---- epilogue
   p.act = d->act;
@@ -492,10 +595,6 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
   p.out_fp32 = d->out_fp32;
   p.patch_k = d->patch_k;
   p.patch_c = d->patch_c;
-  const uintptr_t oa = reinterpret_cast<uintptr_t>(d->out);
-  p.vec_ok = d->out_fp32 ? ((oa % 16 == 0) && (d->out_ld % 4 == 0)) : ((oa % 16 == 0) && (d->out_ld % 8 == 0));
-  p.res_vec_ok = d->residual != nullptr && (reinterpret_cast<uintptr_t>(d->residual) % 16 == 0) &&
-                 (d->res_ld % 8 == 0);
 
   rc = set_smem_attr_once();
   if (rc != LY_OK) return rc;

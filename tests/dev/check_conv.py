@@ -32,6 +32,7 @@ CASES = {
     "l1_pconv": (64, 160, 160, [8], 8, 3, 1, 1, "none", False, False, False),
     "l1_mlp3": (64, 160, 160, [48], 24, 1, 1, 0, "none", True, False, False),
     "l12_3x3": (64, 40, 40, [128], 128, 3, 1, 1, "silu", False, False, True),
+    "l16_cv12": (64, 80, 80, [168], 128, 1, 1, 0, "silu", False, False, True),
 }
 
 
