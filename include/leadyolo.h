@@ -116,6 +116,15 @@ int ly_stem_fwd(const void* img, int img_is_u8, int N, int H, int W, int Cout, c
 int ly_stem_wgrad(const void* img, int img_is_u8, int N, int H, int W, int Cout, const void* dz, long ld_dz,
                   float in_scale, float* dwk, ly_stream_t stream);
 
+/* Fused FasterNet block, inference (models/common.py:1432-1437,1478-1482): y = x + W2 relu(scale*(W1 [pconv3x3(x[:,:C/4])
+ * | x[:,C/4:]]) + shift) in ONE kernel; x and y are dense NHWC bf16 [N][H][W][C], C in {24, 40}.  The partial-conv
+ * output and the 2C-wide hidden tensor stay in TMEM / shared memory.  wimg: pre-swizzled bf16 weight image with
+ * sections W1x | W2 | W1p | Wp at byte offsets 0 / off_w2 / off_w1p / off_wp (lead_yolo_b200.packing.
+ * fasternet_weight_image); scale/shift: folded mlp.1 BatchNorm [2C]. */
+int ly_fasternet_block_infer(const void* x, void* y, int N, int H, int W, int C, const void* wimg, int w_bytes,
+                             int off_w2, int off_w1p, int off_wp, const float* scale, const float* shift,
+                             ly_stream_t stream);
+
 /* FasterNet partial 3x3 convolution, inference (models/common.py:1416,1432-1437): out[p][co] = sum over the 3x3
  * taps and the first `cpp` channels of x (8-aligned slice; real width dim//4, the rest has zero weights).
  * wk: fp32 [9][cpp][cpp] (tap, ci, co); cpp in {8,16,24,32,40}.  CUDA cores, warp-uniform weights. */

@@ -321,6 +321,17 @@ class MLPBlock(nn.Module):
         cpp = (cp + 7) // 8 * 8
         w1, bn, act, w2 = self.mlp[0], self.mlp[1], _act_name(self.mlp[2]), self.mlp[3]
         c = x.shape[1]
+        if fast and c in (24, 40) and act == "relu" and ll.pixel_ld(x) == c and x.data_ptr() % 16 == 0:
+            # whole block in one kernel (csrc/fasternet_block.cu)
+            from .packing import fasternet_weight_image
+            img = ops.cached([w1.weight, w2.weight, pc.partial_conv3.weight], ("fnb", c), lambda: fasternet_weight_image(
+                w1.weight, w2.weight, pc.partial_conv3.weight))
+            scale, shift = ops.bn_fold(bn)
+            n, _, h, wd = x.shape
+            y = ll.empty_cl(n, c, h, wd, device=x.device)
+            ll.call("ly_fasternet_block_infer", x, y, n, h, wd, c, img[0], img[0].numel() * 2, img[1], img[2], img[3],
+                    scale, shift)
+            return y
         t1 = pc._t1(x, fast)
         # u = W1[:, :cp] t1 + W1[:, cp:] x[:, cp:]  ==  [W1[:, :cp] | 0] t1(8-aligned)  +  [0 | W1[:, cp:]] x
         if fast:

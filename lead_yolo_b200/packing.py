@@ -70,3 +70,57 @@ def unpack_conv_weight(wp: torch.Tensor, cout: int, src_channels, kh: int, kw: i
                 col += (cs + 63) // 64 * 64
         off += cs
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Pre-swizzled shared-memory images (csrc/fasternet_block.cu): K-major tiles exactly as tcgen05 reads them, so
+# the kernel fetches all weights of a block with ONE bulk copy.
+#   SW128 tile: rows of 64 bf16 (128 B); 16-byte chunk j of row r is stored at chunk j ^ (r & 7)
+#   SW32  tile: rows of 16 bf16 (32 B);  16-byte chunk j of row r is stored at chunk j ^ ((r >> 2) & 1)
+# ---------------------------------------------------------------------------------------------------------
+def _swizzle_rows(mat: torch.Tensor, chunks: int, fn) -> torch.Tensor:
+    rows = mat.shape[0]
+    m = mat.reshape(rows, chunks, 8)
+    r = torch.arange(rows, device=mat.device).view(-1, 1)
+    j = torch.arange(chunks, device=mat.device).view(1, -1)
+    dst = (j ^ fn(r)).expand(rows, chunks)
+    out = torch.empty_like(m)
+    out.scatter_(1, dst.unsqueeze(-1).expand(rows, chunks, 8), m)
+    return out.reshape(-1)
+
+
+def swizzle128(mat: torch.Tensor) -> torch.Tensor:
+    assert mat.shape[1] == 64 and mat.shape[0] % 8 == 0
+    return _swizzle_rows(mat, 8, lambda r: r & 7)
+
+
+def swizzle32(mat: torch.Tensor) -> torch.Tensor:
+    assert mat.shape[1] == 16 and mat.shape[0] % 8 == 0
+    return _swizzle_rows(mat, 2, lambda r: (r >> 2) & 1)
+
+
+def fasternet_weight_image(w1: torch.Tensor, w2: torch.Tensor, wp: torch.Tensor):
+    """(image bf16 1-D, off_w2, off_w1p, off_wp in bytes) for MLPBlock weights mlp.0 (2C,C,1,1), mlp.3 (C,2C,1,1) and
+    partial_conv3 (Cp,Cp,3,3).  Sections: W1x [2C][64] | W2 [chunks][N2][64] | W1p [2C][16] | Wp [9][16][16]."""
+    c2, c = w1.shape[0], w1.shape[1]
+    cp = wp.shape[0]
+    assert cp <= 16 and c <= 64
+    n2 = (c + 15) // 16 * 16
+    chunks = (c2 + 63) // 64
+    f = lambda t: t.detach().float()  # noqa: E731
+    pad = torch.nn.functional.pad
+    w1m = f(w1)[:, :, 0, 0]
+    w1x = w1m.clone()
+    w1x[:, :cp] = 0
+    parts = [swizzle128(pad(w1x, (0, 64 - c)).to(torch.bfloat16))]
+    w2m = pad(f(w2)[:, :, 0, 0], (0, chunks * 64 - c2, 0, n2 - c))
+    for kc in range(chunks):
+        parts.append(swizzle128(w2m[:, kc * 64:(kc + 1) * 64].to(torch.bfloat16).contiguous()))
+    off_w2 = parts[0].numel() * 2
+    off_w1p = off_w2 + sum(p.numel() for p in parts[1:]) * 2
+    parts.append(swizzle32(pad(w1m[:, :cp], (0, 16 - cp)).to(torch.bfloat16)))
+    off_wp = off_w1p + parts[-1].numel() * 2
+    wpf = f(wp)
+    for t in range(9):
+        parts.append(swizzle32(pad(wpf[:, :, t // 3, t % 3], (0, 16 - cp, 0, 16 - cp)).to(torch.bfloat16)))
+    return torch.cat(parts).contiguous(), off_w2, off_w1p, off_wp
