@@ -202,6 +202,21 @@ int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int W, int C, i
                           const float* wgk, const float* scale, const float* shift, const float* w1, const float* w2,
                           int R, const float* wa, float* maps, float* gap_sum, float* se, float* att, void* A,
                           ly_stream_t stream);
+/* k = 3 inference pipeline with the feature generation on the tensor cores (csrc/rf_generate_tc.cu): the depthwise
+ * 3x3 of rfa.py:101-105 runs as a grouped 3x3 convolution (16 -> 144 channels per group) with one tcgen05.mma per tap.
+ * Two passes over x, the ungated features are never stored:
+ *   ly_rf_tc_stats  maps fp32 [N][3ho][3wo][2] = (max, mean) over channels of relu(generate + shift); zeroed by the call
+ *   ly_rf_tc_apply  A bf16 [N*ho*wo][9*C], A[m][t*C+c] = relu(generate + shift) * se[n][c] * att[n][3h+t/3][3w+t%3]
+ * wc: bf16 [C/16][9 taps][9 t][16] generate weights with the BatchNorm scale folded in; shift: fp32 [C/16][9 t][16].
+ * C % 16 == 0, s in {1, 2}; A 32-byte aligned. */
+int ly_rf_tc_stats(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
+                   const float* shift, float* maps, ly_stream_t stream);
+int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
+                   const float* shift, const float* se, const float* att, void* A, ly_stream_t stream);
+/* gap_sum[n][c] = sum_hw x (zeroed by the call);  se = sigmoid(W2 relu(W1 gap_sum/HW)), att = sigmoid(conv3x3(maps)). */
+int ly_rf_gap_sum(const void* x, long ldx, int N, int HW, int C, float* gap_sum, ly_stream_t stream);
+int ly_rf_se_att(const float* gap_sum, int N, int C, int HW, const float* w1, const float* w2, int R, const float* maps,
+                 int HK, int WK, const float* wa, float* se, float* att, ly_stream_t stream);
 int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse,
                    const float* att, void* dG, float* dse, float* datt, ly_stream_t stream);
 int ly_rf_attention_bwd(const float* datt, const float* att, const float* maps, const int16_t* amax, int N, int ho,

@@ -351,6 +351,86 @@ __global__ void __launch_bounds__(256) rf_gate2_kernel(const __nv_bfloat16* __re
   *reinterpret_cast<uint4*>(A + tid * 8) = pack8(g);
 }
 
+// ---- k = 1 (generate is a per-channel scale): lean streaming kernels, one warp per pixel -------------------------
+// pass 1: g = relu(w'[c]*x + shift[c]);  max_c / mean_c via warp shuffles;  SE sums accumulated per warp
+__global__ void __launch_bounds__(256) rf1_stats_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int HW, int V,
+                                                        const float* __restrict__ wgk, const float* __restrict__ scale,
+                                                        const float* __restrict__ shift, float* __restrict__ maps,
+                                                        float* __restrict__ gap_sum) {
+  const int C = V * 8;
+  const int n = blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const long warps = (long)gridDim.x * wpb;
+  const long w0 = (long)blockIdx.x * wpb + (threadIdx.x >> 5);
+  float wv[2][8], hv[2][8], gs[2][8];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int v = lane + q * 32;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const bool ok = v < V;
+      wv[q][e] = ok ? wgk[v * 8 + e] * (scale != nullptr ? scale[v * 8 + e] : 1.f) : 0.f;
+      hv[q][e] = ok ? shift[v * 8 + e] : 0.f;
+      gs[q][e] = 0.f;
+    }
+  }
+  for (long p = w0; p < HW; p += warps) {
+    const __nv_bfloat16* px = x + ((long)n * HW + p) * ldx;
+    float mx = 0.f, sm = 0.f;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int v = lane + q * 32;
+      if (v < V) {
+        float f[8];
+        unpack8(ldx16(px + v * 8), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          gs[q][e] += f[e];
+          const float g = fmaxf(fmaf(f[e], wv[q][e], hv[q][e]), 0.f);
+          mx = fmaxf(mx, g);
+          sm += g;
+        }
+      }
+    }
+    mx = warp_max(mx);
+    sm = warp_sum(sm);
+    if (lane == 0) *reinterpret_cast<float2*>(maps + ((long)n * HW + p) * 2) = make_float2(mx, sm / (float)C);
+  }
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int v = lane + q * 32;
+    if (v < V) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) atomicAdd(&gap_sum[(long)n * C + v * 8 + e], gs[q][e]);
+    }
+  }
+}
+
+// pass 2: A = relu(w'*x + shift) * se[n,c] * att[n,pixel]   (flat, fully coalesced)
+__global__ void __launch_bounds__(256) rf1_apply_kernel(const __nv_bfloat16* __restrict__ x, long ldx, long M, int HW,
+                                                        int V, const float* __restrict__ wgk,
+                                                        const float* __restrict__ scale,
+                                                        const float* __restrict__ shift, const float* __restrict__ se,
+                                                        const float* __restrict__ att, __nv_bfloat16* __restrict__ A) {
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= M * V) return;
+  const int v = (int)(tid % V);
+  const long m = tid / V;
+  const long n = m / HW;
+  const int C = V * 8;
+  float f[8];
+  unpack8(ldx16(x + m * ldx + v * 8), f);
+  const float a = __ldg(att + m);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int c = v * 8 + e;
+    const float w = __ldg(wgk + c) * (scale != nullptr ? __ldg(scale + c) : 1.f);
+    f[e] = fmaxf(fmaf(f[e], w, __ldg(shift + c)), 0.f) * __ldg(se + n * C + c) * a;
+  }
+  *reinterpret_cast<uint4*>(A + m * (long)C + v * 8) = pack8(f);
+}
+
 }  // namespace ly
 
 using namespace ly;
@@ -378,7 +458,7 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
   const int vgroups = ceil_div(V, 16);
   const int WPB = ceil_div(V, vgroups);
   LY_CUDA(cudaMemsetAsync(gap_sum, 0, sizeof(float) * (size_t)N * C, stream));
-  if (vgroups > 1) LY_CUDA(cudaMemsetAsync(maps, 0, sizeof(float) * (size_t)N * ho * k * wo * k * 2, stream));
+  if (vgroups > 1 && k != 1) LY_CUDA(cudaMemsetAsync(maps, 0, sizeof(float) * (size_t)N * ho * k * wo * k * 2, stream));
   const int KK = k * k;
   const long groups = (M + 31) / 32;
   const int sms = device_sm_count();
@@ -387,8 +467,11 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
     dim3 grid1((unsigned)bx, (unsigned)vgroups);
     const size_t sm1 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * WPB * 8 + (size_t)WPB * 2 * KK * 512;
     if (k == 1) {
-      rf_stats_kernel<1><<<grid1, WPB * 32, sm1, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, WPB, s, ho, wo,
-                                                          wgk, scale, shift, maps, gap_sum, vgroups > 1, nullptr);
+      int bx1 = ceil_div((long)sms * 8, N);
+      if (bx1 > ceil_div(H * W, 8)) bx1 = ceil_div(H * W, 8);
+      if (bx1 < 1) bx1 = 1;
+      rf1_stats_kernel<<<dim3((unsigned)bx1, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W, V,
+                                                                            wgk, scale, shift, maps, gap_sum);
     } else {
       static bool attr_done[64] = {false};
       int dev = 0;
@@ -417,12 +500,91 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
     dim3 grid2((unsigned)bx, (unsigned)vg8);
     const size_t sm2 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * 8 * 8 + (size_t)8 * 2 * KK * 512;
     if (k == 1)
-      rf_apply_kernel<1><<<grid2, 256, sm2, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, s, ho, wo, wgk, scale,
-                                                     shift, se, att, (__nv_bfloat16*)A);
+      rf1_apply_kernel<<<ceil_div(M * V, 256), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, M, H * W, V, wgk, scale,
+                                                                shift, se, att, (__nv_bfloat16*)A);
     else
       rf_gate2_kernel<<<ceil_div(M * KK * V, 256), 256, 0, stream>>>((const __nv_bfloat16*)A, M, KK, k, V, ho, wo, se,
                                                                     att, (__nv_bfloat16*)A);
   }
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+// ---- building blocks of the k = 3 inference pipeline whose feature generation runs on the tensor cores
+// (csrc/rf_generate_tc.cu): SE channel sums, SE gate + spatial attention, gating of the stored features.
+namespace ly {
+// block = (Vp lanes over 16-byte channel vectors) x (256 / Vp pixel rows); 4 independent loads in flight per thread
+__global__ void __launch_bounds__(256) rf_gap_sum_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int HW, int V,
+                                                         int Vp, float* __restrict__ gap_sum) {
+  __shared__ float red[256 * 8];
+  const int n = blockIdx.y;
+  const int v = threadIdx.x % Vp, row = threadIdx.x / Vp, rows = 256 / Vp;
+  const long stride = (long)gridDim.x * rows;
+  float gs[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) gs[e] = 0.f;
+  if (v < V) {
+    const __nv_bfloat16* base = x + (long)n * HW * ldx + v * 8;
+    long p = (long)blockIdx.x * rows + row;
+    for (; p + 3 * stride < HW; p += 4 * stride) {
+      uint4 u[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) u[j] = ldx16(base + (p + j * stride) * ldx);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float f[8];
+        unpack8(u[j], f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) gs[e] += f[e];
+      }
+    }
+    for (; p < HW; p += stride) {
+      float f[8];
+      unpack8(ldx16(base + p * ldx), f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) gs[e] += f[e];
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[e * 256 + threadIdx.x] = gs[e];
+  __syncthreads();
+  // thread (e, v) sums the rows of its column
+  for (int i = threadIdx.x; i < V * 8; i += 256) {
+    const int e = i % 8, vv = i / 8;
+    float a = 0.f;
+    for (int r = 0; r < rows; ++r) a += red[e * 256 + r * Vp + vv];
+    atomicAdd(&gap_sum[(long)n * V * 8 + vv * 8 + e], a);
+  }
+}
+}  // namespace ly
+
+// gap_sum[n][c] = sum over the H*W pixels of x (fp32; zeroed here first)
+extern "C" int ly_rf_gap_sum(const void* x, long ldx, int N, int HW, int C, float* gap_sum, ly_stream_t st) {
+  LY_REQUIRE(x && gap_sum && C % 8 == 0 && C <= 512 && ldx % 8 == 0 && ldx >= C, "ly_rf_gap_sum: bad args");
+  cudaStream_t stream = (cudaStream_t)st;
+  LY_CUDA(cudaMemsetAsync(gap_sum, 0, sizeof(float) * (size_t)N * C, stream));
+  const int V = C / 8;
+  int Vp = 1;
+  while (Vp < V) Vp *= 2;
+  const int rows = 256 / Vp;
+  long bx = ceil_div((long)HW, (long)rows * 8);
+  const long cap = ceil_div(8L * device_sm_count(), (long)N);
+  if (bx > cap) bx = cap;
+  if (bx < 1) bx = 1;
+  rf_gap_sum_kernel<<<dim3((unsigned)bx, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, HW, V, Vp,
+                                                                        gap_sum);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+// se[n][c] = sigmoid(W2 relu(W1 gap_sum/HW));  att = sigmoid(conv3x3(maps))   (rfa.py:88-92, 106, 127)
+extern "C" int ly_rf_se_att(const float* gap_sum, int N, int C, int HW, const float* w1, const float* w2, int R,
+                            const float* maps, int HK, int WK, const float* wa, float* se, float* att,
+                            ly_stream_t st) {
+  LY_REQUIRE(gap_sum && w1 && w2 && maps && wa && se && att && R > 0 && R <= 64 && C <= 512, "ly_rf_se_att: bad args");
+  const long tot = (long)N * HK * WK;
+  rf_se_att_kernel<<<N + ceil_div(tot, 256), 256, 0, (cudaStream_t)st>>>(gap_sum, N, C, 1.f / (float)HW, w1, w2, R, se,
+                                                                        maps, HK, WK, wa, att);
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

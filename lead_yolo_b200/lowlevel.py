@@ -171,6 +171,10 @@ _SIGS = {
     "ly_rf_attention_noalloc": "piiiiippp",
     "ly_rf_gate": "piiiiiplpp",
     "ly_rfcbam_front_infer": "pliiiiiiiipppppipppppp",
+    "ly_rf_tc_stats": "pliiiiiiippp",
+    "ly_rf_tc_apply": "pliiiiiiippppp",
+    "ly_rf_gap_sum": "pliiip",
+    "ly_rf_se_att": "piiippipiippp",
     "ly_rf_gate_bwd": "ppiiiiiplpppp",
     "ly_rf_attention_bwd": "ppppiiiiipppp",
     "ly_rf_generate_bwd": "ppliiiiiiiippplp",

@@ -484,12 +484,38 @@ class RfGateAttFn(torch.autograd.Function):
         return dg, dse.to(BF16).view(n, c, 1, 1), dwa.view(1, 2, 3, 3).to(wdt), None
 
 
+def _rf_tc_weights(wg, c, gscale, gshift):
+    """Diagonal generate weights [C/16][tap][t][16] (BatchNorm scale folded in) and shift [C/16][t][16] for ly_rf_tc_*."""
+    wgk = rf_pack_generate_weight(wg, c, 3) * gscale.view(9, 1, c)          # [t][tap][c]
+    wc = wgk.view(9, 9, c // 16, 16).permute(2, 1, 0, 3).reshape(c // 16, 1296)
+    sh = gshift.view(9, c // 16, 16).permute(1, 0, 2).reshape(c // 16, 144)
+    return wc.to(BF16).contiguous(), sh.float().contiguous()
+
+
 def rfcbam_front_infer(x, wg, k, s, gscale, gshift, w1, w2, wa):
     """Inference: x -> gated GEMM operand A (N, k*k*C, ho, wo) in two passes over x (ly_rfcbam_front_infer)."""
     x = to_act(x)
     n, c, h, w = x.shape
     ho, wo = rf_out_size(h, w, k, s)
     dev = x.device
+    if k == 3 and c % 16 == 0:
+        # feature generation on the tensor cores, twice: channel statistics first, then the gated GEMM operand
+        wc, sh = cached([wg, gscale, gshift], ("rftc", c), lambda: _rf_tc_weights(wg, c, gscale, gshift))
+        w1f = cached([w1], "sew1", lambda: w1.detach().float().contiguous())
+        w2f = cached([w2], "sew2", lambda: w2.detach().float().contiguous())
+        wa32 = cached([wa], "wa32", lambda: wa.detach().float().reshape(18).contiguous())
+        nm = n * ho * 3 * wo * 3
+        nmp = (nm + 3) // 4 * 4
+        ws = torch.empty(3 * nmp + 2 * n * c, dtype=torch.float32, device=dev)
+        maps, att = ws[:2 * nm], ws[2 * nmp:2 * nmp + nm]
+        gap, se = ws[3 * nmp:3 * nmp + n * c], ws[3 * nmp + n * c:]
+        a = ll.empty_cl(n, 9 * c, ho, wo, device=dev)
+        ld = ll.pixel_ld(x)
+        ll.call("ly_rf_gap_sum", x, ld, n, h * w, c, gap)
+        ll.call("ly_rf_tc_stats", x, ld, n, h, w, c, s, ho, wo, wc, sh, maps)
+        ll.call("ly_rf_se_att", gap, n, c, h * w, w1f, w2f, int(w1.shape[0]), maps, ho * 3, wo * 3, wa32, se, att)
+        ll.call("ly_rf_tc_apply", x, ld, n, h, w, c, s, ho, wo, wc, sh, se, att, a)
+        return a
     wgk = cached([wg], ("wgk", c, k), lambda: rf_pack_generate_weight(wg, c, k))
     w1f = cached([w1], "sew1", lambda: w1.detach().float().contiguous())
     w2f = cached([w2], "sew2", lambda: w2.detach().float().contiguous())
