@@ -3,7 +3,7 @@
 // generate = depthwise 3x3 (stride s) that turns every channel into 9 features (reference models/rfa.py:101-105).
 // Per 16-channel group this is a small dense problem: a grouped 3x3 convolution 16 -> 144 channels whose weight
 // matrix is block diagonal.  Each of the 9 taps is one tcgen05.mma (M = 128 pixels, N = 144, K = 16) on a 16-channel
-// SW32 box that TMA fetches with the convolution stride as its traversal stride; 15/16 of the multiplied weights are
+// SW32 box fetched by TMA (for stride 2 from one of four parity planes of x); 15/16 of the multiplied weights are
 // zeros, which is still several times faster than the FP32 pipe, and the zeros never leave the SM: the 9 weight tiles
 // live in shared memory and only their 1296 diagonal values are rewritten when the channel group changes.
 //
@@ -24,14 +24,18 @@
 
 namespace ly {
 
-constexpr int kRtStages = 8;
+constexpr int kRtStages = 6;          // one stage = the 3 tap boxes of a kernel row, filled under ONE mbarrier phase:
+                                      // a lone producer lane pays ~250 cycles per barrier round trip but only ~128 per
+                                      // extra box (tests/dev/tma_issue.cu), and the TMA unit itself moves 1 box row / cycle
 constexpr int kRtA = 128 * 32;        // tap box: 128 pixels x 16 channels, SW32
 constexpr int kRtB = 144 * 32;        // weight tile of one tap: 144 outputs x 16 inputs, SW32
 constexpr int kRtB1 = 9 * kRtB;       // all 9 taps of one channel group
 constexpr int kRtThreads = 352;
 
 struct alignas(64) RfTcParams {
-  CUtensorMap a_map;   // x as (C, W, 1, H, N), box (16, s*Wt, 1, s*Ht, 1), element strides (1, s, 1, s, 1), SW32
+  // s = 1: a_map[0] = x as (C, W, 1, H, N).  s = 2: one map per input parity (ph, pw) = x[:, ph::2, pw::2, :], so a tap
+  // is a dense box of its parity plane (a strided TMA traversal would walk 4x the rows).  Box (16, Wt, 1, Ht, 1), SW32.
+  CUtensorMap a_map[4];
   int tiles_w, tiles_h, n_img, groups;
   int Wt, Ht, ho, wo, C, s;
   int items, per_cta;
@@ -64,12 +68,12 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
   uint8_t* sA = smem;
-  uint8_t* sB = smem + kRtStages * kRtA;   // 2 x kRtB1
+  uint8_t* sB = smem + kRtStages * 3 * kRtA;   // 2 x kRtB1
 
   // zero the weight tiles once: the off-diagonal entries stay zero for the whole kernel
   for (int i = threadIdx.x; i < 2 * kRtB1 / 16; i += kRtThreads) reinterpret_cast<uint4*>(sB)[i] = make_uint4(0, 0, 0, 0);
   fence_proxy_async_smem();
-  if (warp == 0 && lane == 0) tma_prefetch_desc(&p.a_map);
+  if (warp == 0 && lane < (p.s == 2 ? 4 : 1)) tma_prefetch_desc(&p.a_map[lane]);
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kRtStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int b = 0; b < 2; ++b) {
@@ -93,14 +97,21 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
       const int item = first + i;
       const int cg = item % p.groups, mt = item / p.groups;
       const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h, n = mt / (p.tiles_w * p.tiles_h);
-      for (int k = 0; k < 9; ++k, ++it) {
+      for (int ti = 0; ti < 3; ++ti, ++it) {
         const int s = (int)(it % kRtStages);
         const uint32_t ph = (it / kRtStages) & 1u;
         mbar_wait(&empty_bar[s], ph ^ 1u);
         if (lane == 0) {
-          mbar_arrive_expect_tx(&full_bar[s], p.a_bytes);
-          tma_load_5d(sA + s * kRtA, &p.a_map, &full_bar[s], cg * 16, tw * p.Wt * p.s + k % 3 - 1, 0,
-                      th * p.Ht * p.s + k / 3 - 1, n);
+          mbar_arrive_expect_tx(&full_bar[s], 3u * p.a_bytes);
+#pragma unroll
+          for (int tj = 0; tj < 3; ++tj) {
+            uint8_t* dst = sA + (s * 3 + tj) * kRtA;
+            if (p.s == 2)   // input row 2h + ti - 1: parity (ti + 1) & 1, plane row h - (ti == 0)
+              tma_load_5d(dst, &p.a_map[((ti + 1) & 1) * 2 + ((tj + 1) & 1)], &full_bar[s], cg * 16,
+                          tw * p.Wt - (tj == 0), 0, th * p.Ht - (ti == 0), n);
+            else
+              tma_load_5d(dst, &p.a_map[0], &full_bar[s], cg * 16, tw * p.Wt + tj - 1, 0, th * p.Ht + ti - 1, n);
+          }
         }
         __syncwarp();
       }
@@ -114,15 +125,17 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
       mbar_wait(&tempty[buf], ph ^ 1u);
       mbar_wait(&b1_full[buf], ph);
       tc_fence_after_sync();
-      for (int k = 0; k < 9; ++k, ++it) {
+      for (int ti = 0; ti < 3; ++ti, ++it) {
         const int s = (int)(it % kRtStages);
         mbar_wait(&full_bar[s], (it / kRtStages) & 1u);
         tc_fence_after_sync();
         if (lane == 0) {
-          umma_bf16(tmem + (uint32_t)(buf * 256), rt_desc_sw32(smem_u32(sA + s * kRtA)),
-                    rt_desc_sw32(smem_u32(sB + buf * kRtB1 + k * kRtB)), idesc, (uint32_t)(k != 0));
+#pragma unroll
+          for (int tj = 0; tj < 3; ++tj)
+            umma_bf16(tmem + (uint32_t)(buf * 256), rt_desc_sw32(smem_u32(sA + (s * 3 + tj) * kRtA)),
+                      rt_desc_sw32(smem_u32(sB + buf * kRtB1 + (ti * 3 + tj) * kRtB)), idesc, (uint32_t)((ti | tj) != 0));
           umma_commit(&empty_bar[s]);
-          if (k == 8) { umma_commit(&tfull[buf]); umma_commit(&b1_empty[buf]); }
+          if (ti == 2) { umma_commit(&tfull[buf]); umma_commit(&b1_empty[buf]); }
         }
         __syncwarp();
       }
@@ -132,12 +145,29 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
       const int buf = i & 1;
       const int cg = (first + i) % p.groups;
       mbar_wait(&b1_empty[buf], (((uint32_t)i >> 1) & 1u) ^ 1u);
-      const __nv_bfloat16* src = p.wc + (long)cg * 1296;
-      uint8_t* dst = sB + buf * kRtB1;
-      for (int idx = lane; idx < 1296; idx += 32) {
-        const int k = idx / 144, n = idx - k * 144, cl = n & 15;
-        const int off = k * kRtB + n * 32 + ((((cl >> 3) ^ (n >> 2)) & 1) << 4) + (cl & 7) * 2;
-        *reinterpret_cast<__nv_bfloat16*>(dst + off) = src[idx];
+      // 1296 values = 162 vectors of 8; a vector shares its tap k and covers outputs n0..n0+7 (n0 % 8 == 0)
+      const uint4* src = reinterpret_cast<const uint4*>(p.wc + (long)cg * 1296);
+      const uint32_t dst = smem_u32(sB + buf * kRtB1);
+      uint4 v[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const int vi = lane + 32 * j;
+        v[j] = vi < 162 ? __ldg(src + vi) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const int vi = lane + 32 * j;
+        if (vi < 162) {
+          const int k = vi / 18, n0 = (vi - k * 18) * 8;
+          const uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int n = n0 + e;
+            const uint32_t off = (uint32_t)(k * kRtB + n * 32 + (((((n & 15) >> 3) ^ (n >> 2)) & 1) << 4) + e * 2);
+            const uint16_t val = (uint16_t)((e & 1) ? (w[e >> 1] >> 16) : (w[e >> 1] & 0xFFFFu));
+            asm volatile("st.shared.b16 [%0], %1;" ::"r"(dst + off), "h"(val) : "memory");
+          }
+        }
       }
       fence_proxy_async_smem();
       __syncwarp();
@@ -271,7 +301,7 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   LY_REQUIRE(x && wc && shift, "ly_rf_tc: null pointer");
   LY_REQUIRE(C % 16 == 0 && C > 0 && (s == 1 || s == 2) && ldx % 8 == 0 && ldx >= C, "ly_rf_tc: bad C/s/ld");
   LY_REQUIRE(ho == (H + 2 - 3) / s + 1 && wo == (W + 2 - 3) / s + 1, "ly_rf_tc: output size mismatch");
-  LY_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(wc) % 2 == 0 &&
+  LY_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(wc) % 16 == 0 &&
                  reinterpret_cast<uintptr_t>(shift) % 16 == 0,
              "ly_rf_tc: alignment");
   RfTcParams p;
@@ -294,12 +324,16 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   p.ho = ho; p.wo = wo; p.C = C; p.s = s;
   p.a_bytes = (uint32_t)(16 * bw * bh * 2);
   p.wc = (const __nv_bfloat16*)wc; p.shift = shift; p.se = se; p.att = att; p.A = (__nv_bfloat16*)A; p.maps = maps;
-  {
-    uint64_t dims[5] = {(uint64_t)C, (uint64_t)W, 1, (uint64_t)H, (uint64_t)N};
-    uint64_t str[4] = {(uint64_t)ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)H * W * ldx * 2};
-    uint32_t box[5] = {16, (uint32_t)(bw * s), 1, (uint32_t)(bh * s), 1};
-    uint32_t es[5] = {1, (uint32_t)s, 1, (uint32_t)s, 1};
-    int rc = rt_encode(&p.a_map, x, 5, dims, str, box, es);
+  for (int par = 0; par < (s == 2 ? 4 : 1); ++par) {
+    const int ph = par >> 1, pw = par & 1;
+    const uint64_t Hp = (uint64_t)(H - ph + s - 1) / s, Wp = (uint64_t)(W - pw + s - 1) / s;
+    if (Hp == 0 || Wp == 0) { memcpy(&p.a_map[par], &p.a_map[0], sizeof(CUtensorMap)); continue; }  // 1-pixel inputs
+    uint64_t dims[5] = {(uint64_t)C, Wp, 1, Hp, (uint64_t)N};
+    uint64_t str[4] = {(uint64_t)s * ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)s * W * ldx * 2,
+                       (uint64_t)H * W * ldx * 2};
+    uint32_t box[5] = {16, (uint32_t)bw, 1, (uint32_t)bh, 1};
+    uint32_t es[5] = {1, 1, 1, 1, 1};
+    int rc = rt_encode(&p.a_map[par], (const __nv_bfloat16*)x + ((long)ph * W + pw) * ldx, 5, dims, str, box, es);
     if (rc) return rc;
   }
   const long items = (long)p.tiles_w * p.tiles_h * N * p.groups;
@@ -308,7 +342,7 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   p.items = (int)items;
   p.per_cta = (int)ceil_div(items, (long)sms);
   const unsigned grid = (unsigned)ceil_div(items, (long)p.per_cta);
-  const size_t smem = (size_t)kRtStages * kRtA + 2 * kRtB1 + 1024;
+  const size_t smem = (size_t)kRtStages * 3 * kRtA + 2 * kRtB1 + 1024;
   static bool attr_done[64] = {false};
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
