@@ -207,12 +207,12 @@ int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int W, int C, i
  * Two passes over x, the ungated features are never stored:
  *   ly_rf_tc_stats  maps fp32 [N][3ho][3wo][2] = (max, mean) over channels of relu(generate + shift); zeroed by the call
  *   ly_rf_tc_apply  A bf16 [N*ho*wo][9*C], A[m][t*C+c] = relu(generate + shift) * se[n][c] * att[n][3h+t/3][3w+t%3]
- * wc: bf16 [C/16][9 taps][9 t][16] generate weights with the BatchNorm scale folded in; shift: fp32 [C/16][9 t][16].
- * C % 16 == 0, s in {1, 2}; A 32-byte aligned. */
+ * wc: bf16 [C/16][9 taps][9 t][16] generate weights with the BatchNorm scale folded in; shift: uint32 [C/16][9 t][16],
+ * the BatchNorm shift split into two bf16 (hi | lo << 16, hi + lo = shift).  C % 16 == 0, s in {1, 2}; A 32-byte aligned. */
 int ly_rf_tc_stats(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
-                   const float* shift, float* maps, ly_stream_t stream);
+                   const void* shift, float* maps, ly_stream_t stream);
 int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
-                   const float* shift, const float* se, const float* att, void* A, ly_stream_t stream);
+                   const void* shift, const float* se, const float* att, void* A, ly_stream_t stream);
 /* gap_sum[n][c] = sum_hw x (zeroed by the call);  se = sigmoid(W2 relu(W1 gap_sum/HW)), att = sigmoid(conv3x3(maps)). */
 int ly_rf_gap_sum(const void* x, long ldx, int N, int HW, int C, float* gap_sum, ly_stream_t stream);
 int ly_rf_se_att(const float* gap_sum, int N, int C, int HW, const float* w1, const float* w2, int R, const float* maps,

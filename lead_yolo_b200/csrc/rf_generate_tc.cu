@@ -10,13 +10,14 @@
 // Work item = (pixel tile, channel group), channel group fastest; every CTA owns a contiguous range of items.
 //   warp 0      TMA producer: ring of tap boxes
 //   warp 1      MMA issuer: 9 taps -> one of two TMEM accumulators
-//   warps 2..9  epilogue: TMEM lane quadrant = warp % 4; warps 2..5 take t = 0..4, warps 6..9 take t = 5..8
-//   warp 10     rewrites the diagonal of the (double-buffered) weight tiles for the next item
+//   warps 2..17 epilogue: TMEM lane quadrant = warp % 4; four groups take t = {0,1,2}, {3,4}, {5,6}, {7,8}
+//   warp 18     rewrites the diagonal of the (double-buffered) weight tiles for the next item
 // Two passes over x, neither stores the ungated features (the reference materialises them three times):
 //   STATS  g = relu(acc + shift); max / mean over channels per (pixel, t) kept in registers across the channel groups
 //          of a pixel tile and merged into the attention input maps once per tile (features are >= 0, so an integer
 //          atomicMax on the float bits is exact)
-//   APPLY  A[m][t*C + c] = g * se[n][c] * att[n][3h + t/3][3w + t%3] -> the GEMM operand of RFCBAMConv.conv
+//   APPLY  A[m][(c/16)*144 + t*16 + c%16] = g * se[n][c] * att[n][3h + t/3][3w + t%3] -> the GEMM operand of
+//          RFCBAMConv.conv, staged in shared memory and written back by TMA (288 contiguous bytes per pixel and item)
 #include <string.h>
 
 #include "ly_common.cuh"
@@ -24,60 +25,117 @@
 
 namespace ly {
 
-constexpr int kRtStages = 6;          // one stage = the 3 tap boxes of a kernel row, filled under ONE mbarrier phase:
+// Per-role wait accounting for tests/dev/rf_tc_probe.cu; compiled out of the library.
+#ifdef RF_TC_DEBUG
+__device__ long long rf_tc_dbg[148][16];
+#define RT_WAIT(slot, bar, par)                    \
+  do {                                             \
+    const long long t__ = clock64();               \
+    mbar_wait(bar, par);                           \
+    dbg_acc[slot] += clock64() - t__;              \
+  } while (0)
+#define RT_DBG_DECL long long dbg_acc[4] = {0, 0, 0, 0}; const long long dbg_t0 = clock64();
+#define RT_DBG_FLUSH(base, nslots)                                                                        \
+  if (lane == 0 && blockIdx.x < 148) {                                                                    \
+    for (int z = 0; z < nslots; ++z) rf_tc_dbg[blockIdx.x][base + z] = dbg_acc[z];                        \
+    rf_tc_dbg[blockIdx.x][base + nslots] = clock64() - dbg_t0;                                            \
+  }
+#else
+#define RT_WAIT(slot, bar, par) mbar_wait(bar, par)
+#define RT_DBG_DECL
+#define RT_DBG_FLUSH(base, nslots)
+#endif
+
+constexpr int kRtStagesMax = 6;       // one stage = the 3 tap boxes of a kernel row, filled under ONE mbarrier phase:
                                       // a lone producer lane pays ~250 cycles per barrier round trip but only ~128 per
                                       // extra box (tests/dev/tma_issue.cu), and the TMA unit itself moves 1 box row / cycle
 constexpr int kRtA = 128 * 32;        // tap box: 128 pixels x 16 channels, SW32
 constexpr int kRtB = 144 * 32;        // weight tile of one tap: 144 outputs x 16 inputs, SW32
-constexpr int kRtB1 = 9 * kRtB;       // all 9 taps of one channel group
-constexpr int kRtThreads = 352;
+constexpr int kRtB1 = 10 * kRtB;      // 9 taps + the shift tile of one channel group
+constexpr int kRtStage = 128 * 288;   // APPLY: staged output of one item, [pixel][9 t][16] bf16, written back by TMA
+constexpr int kRtThreads = 608;
 
 struct alignas(64) RfTcParams {
   // s = 1: a_map[0] = x as (C, W, 1, H, N).  s = 2: one map per input parity (ph, pw) = x[:, ph::2, pw::2, :], so a tap
   // is a dense box of its parity plane (a strided TMA traversal would walk 4x the rows).  Box (16, Wt, 1, Ht, 1), SW32.
   CUtensorMap a_map[4];
+  CUtensorMap o_map;   // APPLY: A as (9C, wo, ho, N), box (144, Wt, Ht, 1), no swizzle
   int tiles_w, tiles_h, n_img, groups;
   int Wt, Ht, ho, wo, C, s;
   int items, per_cta;
   uint32_t a_bytes;
   const __nv_bfloat16* wc;  // [C/16][9 taps][144]: the diagonal values, BatchNorm scale folded in
-  const float* shift;       // [C/16][144]
+  const uint32_t* shift;    // [C/16][144]: BatchNorm shift as two bf16 (hi | lo << 16), hi + lo = shift to 16 bits
   const float* se;          // [N][C]                 (APPLY)
   const float* att;         // [N][ho*3][wo*3]        (APPLY)
-  __nv_bfloat16* A;         // [M][9*C]               (APPLY)
+  __nv_bfloat16* A;         // [M][9*C], column cg*144 + t*16 + c%16   (APPLY)
   float* maps;              // [N][ho*3][wo*3][2]     (STATS; zero on entry)
 };
 
-__device__ __forceinline__ uint64_t rt_desc_sw32(uint32_t addr) {
+__host__ __device__ constexpr uint64_t rt_desc_sw32(uint32_t addr) {
   return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)1 << 16) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46) |
          (6ull << 61);
 }
 
-__device__ __forceinline__ void st_global_256(void* ptr, const uint4& a, const uint4& b) {
-  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(a.x), "r"(a.y), "r"(a.z),
-               "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+__device__ __forceinline__ void st_global_256(void* ptr, const uint32_t (&w)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+               "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
                : "memory");
+}
+// packed fp32 pairs (FMUL2 / FADD2) and relu + convert + pack in one instruction: the epilogue is issue-bound
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t relu_bf16x2(uint64_t v) {   // bf16(relu(lo)) | bf16(relu(hi)) << 16
+  float lo, hi;
+  f2_unpack(v, lo, hi);
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 
 template <int MODE>  // 0 = STATS, 1 = APPLY
 __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_constant__ RfTcParams p) {
+  constexpr int kRtStages = MODE == 0 ? 6 : 4;   // APPLY trades two ring stages for the output staging buffers
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[kRtStages], empty_bar[kRtStages], tfull[2], tempty[2], b1_full[2], b1_empty[2];
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
-  uint8_t* sA = smem;
-  uint8_t* sB = smem + kRtStages * 3 * kRtA;   // 2 x kRtB1
+  uint8_t* sA = smem;                                  // ring: kRtStages x 3 tap boxes
+  uint8_t* sOnes = smem + kRtStages * 3 * kRtA;        // [128][16] with columns 0 and 1 = 1.0: A operand of the shift MMA
+  uint8_t* sB = sOnes + kRtA;                          // 2 x kRtB1
+  uint8_t* sStage = sB + 2 * kRtB1;                    // APPLY: 2 x kRtStage
 
-  // zero the weight tiles once: the off-diagonal entries stay zero for the whole kernel
-  for (int i = threadIdx.x; i < 2 * kRtB1 / 16; i += kRtThreads) reinterpret_cast<uint4*>(sB)[i] = make_uint4(0, 0, 0, 0);
+  // weight tiles: the off-diagonal entries stay zero for the whole kernel
+  for (int i = threadIdx.x; i < (kRtA + 2 * kRtB1) / 16; i += kRtThreads)
+    reinterpret_cast<uint4*>(sOnes)[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  if (threadIdx.x < 128)   // columns 0,1 live in 16-byte chunk 0, stored at chunk (r >> 2) & 1 of row r
+    *reinterpret_cast<uint32_t*>(sOnes + threadIdx.x * 32 + ((threadIdx.x >> 2) & 1) * 16) = 0x3F803F80u;
   fence_proxy_async_smem();
   if (warp == 0 && lane < (p.s == 2 ? 4 : 1)) tma_prefetch_desc(&p.a_map[lane]);
+  if (MODE == 1 && warp == 2 && lane == 0) tma_prefetch_desc(&p.o_map);
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kRtStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int b = 0; b < 2; ++b) {
-      mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 8);
+      mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 16);
       mbar_init(&b1_full[b], 1); mbar_init(&b1_empty[b], 1);
     }
     fence_mbar_init();
@@ -90,179 +148,230 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
 
   const int first = (int)blockIdx.x * p.per_cta;
   const int mine = min(p.per_cta, p.items - first);
+  const int tiles_img = p.tiles_w * p.tiles_h;
 
   if (warp == 0) {
-    uint32_t it = 0;
-    for (int i = 0; i < mine; ++i) {
-      const int item = first + i;
-      const int cg = item % p.groups, mt = item / p.groups;
-      const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h, n = mt / (p.tiles_w * p.tiles_h);
-      for (int ti = 0; ti < 3; ++ti, ++it) {
-        const int s = (int)(it % kRtStages);
-        const uint32_t ph = (it / kRtStages) & 1u;
-        mbar_wait(&empty_bar[s], ph ^ 1u);
-        if (lane == 0) {
+    if (lane == 0) {
+      RT_DBG_DECL
+      int cg = first % p.groups, mt = first / p.groups;
+      uint32_t s = 0, ph = 1;   // ring slot and the parity to wait for on its empty barrier
+      for (int i = 0; i < mine; ++i) {
+        const int n = mt / tiles_img, tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+        const int c0 = cg * 16;
+        for (int ti = 0; ti < 3; ++ti) {
+          RT_WAIT(0, &empty_bar[s], ph);
           mbar_arrive_expect_tx(&full_bar[s], 3u * p.a_bytes);
-#pragma unroll
-          for (int tj = 0; tj < 3; ++tj) {
-            uint8_t* dst = sA + (s * 3 + tj) * kRtA;
-            if (p.s == 2)   // input row 2h + ti - 1: parity (ti + 1) & 1, plane row h - (ti == 0)
-              tma_load_5d(dst, &p.a_map[((ti + 1) & 1) * 2 + ((tj + 1) & 1)], &full_bar[s], cg * 16,
-                          tw * p.Wt - (tj == 0), 0, th * p.Ht - (ti == 0), n);
-            else
-              tma_load_5d(dst, &p.a_map[0], &full_bar[s], cg * 16, tw * p.Wt + tj - 1, 0, th * p.Ht + ti - 1, n);
+          uint8_t* dst = sA + s * 3 * kRtA;
+          if (p.s == 2) {   // input row 2h + ti - 1: parity (ti + 1) & 1, plane row h - (ti == 0)
+            const int row = th * p.Ht - (ti == 0), col = tw * p.Wt;
+            const CUtensorMap* m0 = &p.a_map[((ti + 1) & 1) * 2];
+            tma_load_5d(dst, m0 + 1, &full_bar[s], c0, col - 1, 0, row, n);
+            tma_load_5d(dst + kRtA, m0, &full_bar[s], c0, col, 0, row, n);
+            tma_load_5d(dst + 2 * kRtA, m0 + 1, &full_bar[s], c0, col, 0, row, n);
+          } else {
+            const int row = th * p.Ht + ti - 1, col = tw * p.Wt;
+            tma_load_5d(dst, &p.a_map[0], &full_bar[s], c0, col - 1, 0, row, n);
+            tma_load_5d(dst + kRtA, &p.a_map[0], &full_bar[s], c0, col, 0, row, n);
+            tma_load_5d(dst + 2 * kRtA, &p.a_map[0], &full_bar[s], c0, col + 1, 0, row, n);
           }
+          if (++s == kRtStages) { s = 0; ph ^= 1u; }
         }
-        __syncwarp();
+        if (++cg == p.groups) { cg = 0; ++mt; }
       }
+      RT_DBG_FLUSH(0, 1)
     }
   } else if (warp == 1) {
-    const uint32_t idesc = umma_idesc_bf16_f32(128, 144, 0, 0);
-    uint32_t it = 0;
-    for (int i = 0; i < mine; ++i) {
-      const int buf = i & 1;
-      const uint32_t ph = ((uint32_t)i >> 1) & 1u;
-      mbar_wait(&tempty[buf], ph ^ 1u);
-      mbar_wait(&b1_full[buf], ph);
-      tc_fence_after_sync();
-      for (int ti = 0; ti < 3; ++ti, ++it) {
-        const int s = (int)(it % kRtStages);
-        mbar_wait(&full_bar[s], (it / kRtStages) & 1u);
+    if (lane == 0) {
+      RT_DBG_DECL
+      const uint32_t idesc = umma_idesc_bf16_f32(128, 144, 0, 0);
+      const uint64_t a_desc0 = rt_desc_sw32(smem_u32(sA)), b_desc0 = rt_desc_sw32(smem_u32(sB));
+      const uint64_t ones_desc = rt_desc_sw32(smem_u32(sOnes));
+      uint32_t s = 0, ph = 0;
+      for (int i = 0; i < mine; ++i) {
+        const int buf = i & 1;
+        const uint32_t bph = ((uint32_t)i >> 1) & 1u;
+        const uint32_t d_tmem = tmem + (uint32_t)(buf * 256);
+        const uint64_t b_desc = b_desc0 + (uint64_t)(buf * (kRtB1 >> 4));
+        RT_WAIT(0, &tempty[buf], bph ^ 1u);
+        RT_WAIT(1, &b1_full[buf], bph);
         tc_fence_after_sync();
-        if (lane == 0) {
+        umma_bf16(d_tmem, ones_desc, b_desc + (uint64_t)(9 * (kRtB >> 4)), idesc, 0u);   // acc = shift
+        for (int ti = 0; ti < 3; ++ti) {
+          RT_WAIT(2, &full_bar[s], ph);
+          tc_fence_after_sync();
+          const uint64_t a_desc = a_desc0 + (uint64_t)(s * (3 * kRtA >> 4));
 #pragma unroll
           for (int tj = 0; tj < 3; ++tj)
-            umma_bf16(tmem + (uint32_t)(buf * 256), rt_desc_sw32(smem_u32(sA + (s * 3 + tj) * kRtA)),
-                      rt_desc_sw32(smem_u32(sB + buf * kRtB1 + (ti * 3 + tj) * kRtB)), idesc, (uint32_t)((ti | tj) != 0));
+            umma_bf16(d_tmem, a_desc + (uint64_t)(tj * (kRtA >> 4)), b_desc + (uint64_t)((ti * 3 + tj) * (kRtB >> 4)), idesc,
+                      1u);
           umma_commit(&empty_bar[s]);
-          if (ti == 2) { umma_commit(&tfull[buf]); umma_commit(&b1_empty[buf]); }
+          if (++s == kRtStages) { s = 0; ph ^= 1u; }
         }
-        __syncwarp();
+        umma_commit(&tfull[buf]);
+        umma_commit(&b1_empty[buf]);
       }
+      RT_DBG_FLUSH(2, 3)
     }
-  } else if (warp == 10) {
+  } else if (warp == 18) {
+    RT_DBG_DECL
+    // 1296 diagonal values per channel group: value (tap k, output n) goes to row n, column n & 15 of tile k, i.e. byte
+    //   k*kRtB + n*32 + 16*(((n >> 3) ^ (n >> 2)) & 1) + 2*(n & 7).  Its shared-memory bank depends only on n % 16 (16
+    // distinct banks), so lane l takes n = l, l+32, ... of every tap: 2-way conflicts instead of the 32-way ones of a
+    // "8 consecutive n per lane" split.  Shift tile: row n, columns 0,1 = (hi, lo): 4 bytes at 9*kRtB + n*32 + 16*((n>>2)&1).
+    // The next group's values are fetched before waiting for the buffer.
+    uint32_t off[5], soff[5];
+#pragma unroll
+    for (int m = 0; m < 5; ++m) {
+      const int n = lane + 32 * m;
+      off[m] = smem_u32(sB) + (uint32_t)(n * 32 + ((((n >> 3) ^ (n >> 2)) & 1) << 4) + (n & 7) * 2);
+      soff[m] = smem_u32(sB) + (uint32_t)(9 * kRtB + n * 32 + ((n >> 2) & 1) * 16);
+    }
+    uint16_t v[9][5];
+    uint32_t sh[5];
+    auto fetch = [&](int cg) {
+      const uint16_t* src = reinterpret_cast<const uint16_t*>(p.wc) + (long)cg * 1296 + lane;
+#pragma unroll
+      for (int k = 0; k < 9; ++k)
+#pragma unroll
+        for (int m = 0; m < 5; ++m) v[k][m] = (m < 4 || lane < 16) ? __ldg(src + k * 144 + 32 * m) : (uint16_t)0;
+#pragma unroll
+      for (int m = 0; m < 5; ++m) sh[m] = (m < 4 || lane < 16) ? __ldg(p.shift + cg * 144 + lane + 32 * m) : 0u;
+    };
+    int cg = first % p.groups;
+    fetch(cg);
     for (int i = 0; i < mine; ++i) {
       const int buf = i & 1;
-      const int cg = (first + i) % p.groups;
-      mbar_wait(&b1_empty[buf], (((uint32_t)i >> 1) & 1u) ^ 1u);
-      // 1296 values = 162 vectors of 8; a vector shares its tap k and covers outputs n0..n0+7 (n0 % 8 == 0)
-      const uint4* src = reinterpret_cast<const uint4*>(p.wc + (long)cg * 1296);
-      const uint32_t dst = smem_u32(sB + buf * kRtB1);
-      uint4 v[6];
+      RT_WAIT(0, &b1_empty[buf], (((uint32_t)i >> 1) & 1u) ^ 1u);
 #pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        const int vi = lane + 32 * j;
-        v[j] = vi < 162 ? __ldg(src + vi) : make_uint4(0, 0, 0, 0);
-      }
+      for (int k = 0; k < 9; ++k)
 #pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        const int vi = lane + 32 * j;
-        if (vi < 162) {
-          const int k = vi / 18, n0 = (vi - k * 18) * 8;
-          const uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+        for (int m = 0; m < 5; ++m)
+          if (m < 4 || lane < 16)
+            asm volatile("st.shared.b16 [%0], %1;" ::"r"(off[m] + (uint32_t)(buf * kRtB1 + k * kRtB)), "h"(v[k][m]) : "memory");
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int n = n0 + e;
-            const uint32_t off = (uint32_t)(k * kRtB + n * 32 + (((((n & 15) >> 3) ^ (n >> 2)) & 1) << 4) + e * 2);
-            const uint16_t val = (uint16_t)((e & 1) ? (w[e >> 1] >> 16) : (w[e >> 1] & 0xFFFFu));
-            asm volatile("st.shared.b16 [%0], %1;" ::"r"(dst + off), "h"(val) : "memory");
-          }
-        }
-      }
+      for (int m = 0; m < 5; ++m)
+        if (m < 4 || lane < 16)
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(soff[m] + (uint32_t)(buf * kRtB1)), "r"(sh[m]) : "memory");
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&b1_full[buf]);
+      if (++cg == p.groups) cg = 0;
+      if (i + 1 < mine) fetch(cg);
     }
+    RT_DBG_FLUSH(6, 1)
   } else {
+    RT_DBG_DECL
     const int q = warp & 3;
-    const int half = (warp - 2) >> 2;
-    const int t0 = half * 5, nt = half ? 4 : 5;
+    const int eg = (warp - 2) >> 2;                 // epilogue group: t = 0..2 | 3,4 | 5,6 | 7,8
+    const int t0 = eg == 0 ? 0 : 1 + 2 * eg, nt = eg == 0 ? 3 : 2;
     const int r = q * 32 + lane;
     const int hh = r / p.Wt, ww = r - hh * p.Wt;
     const float invC = 1.f / (float)p.C;
-    float va[5], vb[5];   // STATS: running max / sum;  APPLY: va = attention values
-    int cur_mt = -1, n = 0, h = 0, w = 0;
-    bool valid = false;
+    float va[3], vb[3];   // STATS: running max / sum;  APPLY: va = attention values
+    int cg = first % p.groups, mt = first / p.groups;
+    int n = 0, h = 0, w = 0;
+    bool valid = false, fresh = true;
+    const float* se_row = nullptr;
+    int tile_w0 = 0, tile_h0 = 0;
     for (int i = 0; i < mine; ++i) {
-      const int item = first + i;
-      const int cg = item % p.groups, mt = item / p.groups;
       const int buf = i & 1;
-      if (mt != cur_mt) {
-        cur_mt = mt;
-        const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h;
-        n = mt / (p.tiles_w * p.tiles_h);
-        h = th * p.Ht + hh; w = tw * p.Wt + ww;
+      if (fresh) {
+        fresh = false;
+        n = mt / tiles_img;
+        const int tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+        tile_w0 = tw * p.Wt; tile_h0 = th * p.Ht;
+        h = tile_h0 + hh; w = tile_w0 + ww;
         valid = (r < p.Wt * p.Ht) && h < p.ho && w < p.wo;
 #pragma unroll
-        for (int tt = 0; tt < 5; ++tt) {
+        for (int tt = 0; tt < 3; ++tt) {
           va[tt] = 0.f; vb[tt] = 0.f;
           if (MODE == 1 && valid && tt < nt) {
             const int t = t0 + tt;
             va[tt] = __ldg(p.att + ((long)n * (p.ho * 3) + (h * 3 + t / 3)) * (long)(p.wo * 3) + (w * 3 + t % 3));
           }
         }
+        if (MODE == 1) se_row = p.se + (long)n * p.C;
       }
-      float sev[16];
+      uint64_t se2[8];
       if (MODE == 1) {
-        const float4* sp = reinterpret_cast<const float4*>(p.se + (long)n * p.C + cg * 16);
+        const float4* sp = reinterpret_cast<const float4*>(se_row + cg * 16);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float4 v = __ldg(sp + j);
-          sev[4 * j] = v.x; sev[4 * j + 1] = v.y; sev[4 * j + 2] = v.z; sev[4 * j + 3] = v.w;
+          const float4 e = __ldg(sp + j);
+          se2[2 * j] = f2_pack(e.x, e.y); se2[2 * j + 1] = f2_pack(e.z, e.w);
         }
       }
-      const long m = ((long)n * p.ho + h) * p.wo + w;
-      mbar_wait(&tfull[buf], ((uint32_t)i >> 1) & 1u);
+      RT_WAIT(0, &tfull[buf], ((uint32_t)i >> 1) & 1u);
       tc_fence_after_sync();
-      const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * 256);
-      const float4* sh4 = reinterpret_cast<const float4*>(p.shift + cg * 144);
-#pragma unroll
-      for (int tt = 0; tt < 5; ++tt) {
-        if (tt < nt) {
-          const int t = t0 + tt;
-          uint32_t acc[16];
-          tmem_ld16(trow + (uint32_t)(t * 16), acc);
-          tmem_ld_wait();
-          float g[16];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float4 sv = __ldg(sh4 + t * 4 + j);
-            g[4 * j] = fmaxf(__uint_as_float(acc[4 * j]) + sv.x, 0.f);
-            g[4 * j + 1] = fmaxf(__uint_as_float(acc[4 * j + 1]) + sv.y, 0.f);
-            g[4 * j + 2] = fmaxf(__uint_as_float(acc[4 * j + 2]) + sv.z, 0.f);
-            g[4 * j + 3] = fmaxf(__uint_as_float(acc[4 * j + 3]) + sv.w, 0.f);
-          }
-          if (MODE == 0) {
-            float mx = va[tt], sm = 0.f;
-#pragma unroll
-            for (int j = 0; j < 16; ++j) { mx = fmaxf(mx, g[j]); sm += g[j]; }
-            va[tt] = mx; vb[tt] += sm;
-          } else {
-            float lo[8], hi[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) { lo[j] = g[j] * sev[j] * va[tt]; hi[j] = g[8 + j] * sev[8 + j] * va[tt]; }
-            if (valid) st_global_256(p.A + m * 9L * p.C + (long)t * p.C + cg * 16, pack8(lo), pack8(hi));
-          }
-        }
-      }
+      const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * 256 + t0 * 16);
+      uint32_t acc[3][16];
+      tmem_ld16(trow, acc[0]);
+      tmem_ld16(trow + 16u, acc[1]);
+      if (nt == 3) tmem_ld16(trow + 32u, acc[2]);
+      tmem_ld_wait();
+      // the accumulator is in registers: hand the TMEM buffer back before doing the arithmetic
       tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[buf]);
-      if (MODE == 0) {
-        const bool last = (i == mine - 1) || ((item + 1) / p.groups != mt);
-        if (last && valid) {
+      uint8_t* stg = sStage + buf * kRtStage;
 #pragma unroll
-          for (int tt = 0; tt < 5; ++tt) {
-            if (tt < nt) {
-              const int t = t0 + tt;
-              const long pos = ((long)n * (p.ho * 3) + (h * 3 + t / 3)) * (long)(p.wo * 3) + (w * 3 + t % 3);
-              atomicMax(reinterpret_cast<int*>(p.maps + pos * 2), __float_as_int(va[tt]));
-              atomicAdd(p.maps + pos * 2 + 1, vb[tt] * invC);
+      for (int tt = 0; tt < 3; ++tt) {
+        if (tt < nt) {
+          if (MODE == 0) {   // acc = generate + shift; relu is implied for the max (running max starts at 0)
+            float mx = va[tt];
+            uint64_t s2 = f2_pack(0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float x0 = __uint_as_float(acc[tt][2 * j]), x1 = __uint_as_float(acc[tt][2 * j + 1]);
+              mx = fmaxf(fmaxf(mx, x0), x1);
+              s2 = f2_add(s2, f2_pack(fmaxf(x0, 0.f), fmaxf(x1, 0.f)));
             }
+            float s_lo, s_hi;
+            f2_unpack(s2, s_lo, s_hi);
+            va[tt] = mx; vb[tt] += s_lo + s_hi;
+          } else {           // relu(acc) * se * att = relu(acc * (se * att)): both gates are sigmoids (> 0)
+            const uint64_t att2 = f2_pack(va[tt], va[tt]);
+            uint32_t wds[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint64_t x2 = f2_pack(__uint_as_float(acc[tt][2 * j]), __uint_as_float(acc[tt][2 * j + 1]));
+              wds[j] = relu_bf16x2(f2_mul(x2, f2_mul(se2[j], att2)));
+            }
+            uint4* dst = reinterpret_cast<uint4*>(stg + r * 288 + (t0 + tt) * 32);
+            dst[0] = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+            dst[1] = make_uint4(wds[4], wds[5], wds[6], wds[7]);
           }
         }
       }
+      if (MODE == 1) {
+        // one barrier per item: the elected thread has seen the previous store finish reading its staging buffer (the
+        // one the next item writes) before anybody passes, then sends this item's tile; TMA clips at the image border
+        fence_proxy_async_smem();
+        const bool elected = (warp == 2 && lane == 0);
+        if (elected) tma_store_wait_read<0>();
+        asm volatile("bar.sync 1, 512;" ::: "memory");
+        if (elected) {
+          tma_store_4d(&p.o_map, stg, cg * 144, tile_w0, tile_h0, n);
+          tma_store_commit();
+        }
+      }
+      const bool last = (i == mine - 1) || (cg + 1 == p.groups);
+      if (MODE == 0 && last && valid) {
+#pragma unroll
+        for (int tt = 0; tt < 3; ++tt) {
+          if (tt < nt) {
+            const int t = t0 + tt;
+            const long pos = ((long)n * (p.ho * 3) + (h * 3 + t / 3)) * (long)(p.wo * 3) + (w * 3 + t % 3);
+            atomicMax(reinterpret_cast<int*>(p.maps + pos * 2), __float_as_int(va[tt]));
+            atomicAdd(p.maps + pos * 2 + 1, vb[tt] * invC);
+          }
+        }
+      }
+      if (++cg == p.groups) { cg = 0; ++mt; fresh = true; }
     }
+    if (MODE == 1 && warp == 2 && lane == 0) tma_store_wait_all<0>();
+    if (warp == 2) { RT_DBG_FLUSH(8, 1) }
+    if (warp == 14) { RT_DBG_FLUSH(10, 1) }
   }
   tc_fence_before_sync();
   __syncthreads();
@@ -274,7 +383,7 @@ typedef CUresult (*rt_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, 
                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 static int rt_encode(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides,
-                     const uint32_t* box, const uint32_t* estr) {
+                     const uint32_t* box, const uint32_t* estr, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_32B) {
   static rt_encode_fn fn = nullptr;
   if (!fn) {
     void* f = nullptr;
@@ -289,20 +398,20 @@ static int rt_encode(CUtensorMap* out, const void* base, int rank, const uint64_
   for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bd[i] = box[i]; es[i] = estr[i]; }
   for (int i = 0; i + 1 < rank; ++i) gs[i] = strides[i];
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bd, es,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail(LY_ECUDA, "cuTensorMapEncodeTiled(SW32) failed: %d", (int)r);
+  if (r != CUDA_SUCCESS) return fail(LY_ECUDA, "cuTensorMapEncodeTiled(rf_tc) failed: %d", (int)r);
   return LY_OK;
 }
 
 static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo,
-                        const void* wc, const float* shift, const float* se, const float* att, void* A, float* maps,
+                        const void* wc, const void* shift, const float* se, const float* att, void* A, float* maps,
                         cudaStream_t stream) {
   LY_REQUIRE(x && wc && shift, "ly_rf_tc: null pointer");
   LY_REQUIRE(C % 16 == 0 && C > 0 && (s == 1 || s == 2) && ldx % 8 == 0 && ldx >= C, "ly_rf_tc: bad C/s/ld");
   LY_REQUIRE(ho == (H + 2 - 3) / s + 1 && wo == (W + 2 - 3) / s + 1, "ly_rf_tc: output size mismatch");
   LY_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(wc) % 16 == 0 &&
-                 reinterpret_cast<uintptr_t>(shift) % 16 == 0,
+                 reinterpret_cast<uintptr_t>(shift) % 4 == 0,
              "ly_rf_tc: alignment");
   RfTcParams p;
   memset(&p, 0, sizeof(p));
@@ -323,7 +432,7 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   p.groups = C / 16;
   p.ho = ho; p.wo = wo; p.C = C; p.s = s;
   p.a_bytes = (uint32_t)(16 * bw * bh * 2);
-  p.wc = (const __nv_bfloat16*)wc; p.shift = shift; p.se = se; p.att = att; p.A = (__nv_bfloat16*)A; p.maps = maps;
+  p.wc = (const __nv_bfloat16*)wc; p.shift = (const uint32_t*)shift; p.se = se; p.att = att; p.A = (__nv_bfloat16*)A; p.maps = maps;
   for (int par = 0; par < (s == 2 ? 4 : 1); ++par) {
     const int ph = par >> 1, pw = par & 1;
     const uint64_t Hp = (uint64_t)(H - ph + s - 1) / s, Wp = (uint64_t)(W - pw + s - 1) / s;
@@ -336,26 +445,35 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
     int rc = rt_encode(&p.a_map[par], (const __nv_bfloat16*)x + ((long)ph * W + pw) * ldx, 5, dims, str, box, es);
     if (rc) return rc;
   }
+  if (mode == 1) {
+    uint64_t dims[4] = {(uint64_t)9 * C, (uint64_t)wo, (uint64_t)ho, (uint64_t)N};
+    uint64_t str[3] = {(uint64_t)9 * C * 2, (uint64_t)wo * 9 * C * 2, (uint64_t)ho * wo * 9 * C * 2};
+    uint32_t box[4] = {144, (uint32_t)bw, (uint32_t)bh, 1};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = rt_encode(&p.o_map, A, 4, dims, str, box, es, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) return rc;
+  }
   const long items = (long)p.tiles_w * p.tiles_h * N * p.groups;
   LY_REQUIRE(items < (1L << 30), "ly_rf_tc: problem too large");
   const int sms = device_sm_count();
   p.items = (int)items;
   p.per_cta = (int)ceil_div(items, (long)sms);
   const unsigned grid = (unsigned)ceil_div(items, (long)p.per_cta);
-  const size_t smem = (size_t)kRtStages * 3 * kRtA + 2 * kRtB1 + 1024;
+  const size_t smem0 = (size_t)6 * 3 * kRtA + kRtA + 2 * kRtB1 + 1024;
+  const size_t smem1 = (size_t)4 * 3 * kRtA + kRtA + 2 * kRtB1 + 2 * kRtStage + 1024;
   static bool attr_done[64] = {false};
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
   if (!attr_done[dev & 63]) {
-    LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem0));
+    LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
     attr_done[dev & 63] = true;
   }
   if (mode == 0) {
     LY_CUDA(cudaMemsetAsync(maps, 0, sizeof(float) * 2 * (size_t)N * ho * 3 * wo * 3, stream));
-    rf_tc_kernel<0><<<grid, kRtThreads, smem, stream>>>(p);
+    rf_tc_kernel<0><<<grid, kRtThreads, smem0, stream>>>(p);
   } else {
-    rf_tc_kernel<1><<<grid, kRtThreads, smem, stream>>>(p);
+    rf_tc_kernel<1><<<grid, kRtThreads, smem1, stream>>>(p);
   }
   LY_LAUNCH_CHECK();
   return LY_OK;
@@ -366,18 +484,20 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
 using namespace ly;
 
 // x: NHWC bf16 (pixel stride ldx); wc: bf16 [C/16][9 taps][9 t][16] depthwise generate weights with the BatchNorm scale
-// folded in (value for output (t, c) and tap ij at wc[c/16][ij][t][c%16]); shift: fp32 [C/16][9 t][16].
+// folded in (value for output (t, c) and tap ij at wc[c/16][ij][t][c%16]); shift: uint32 [C/16][9 t][16], the BatchNorm
+// shift as two bf16 (hi | lo << 16, hi + lo = shift): it enters the accumulator through a tenth MMA against a tile of ones.
 // Pass 1: maps fp32 [N][3*ho][3*wo][2] = (max, mean) over channels of the generated features (zeroed by the call).
 extern "C" int ly_rf_tc_stats(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
-                              const float* shift, float* maps, ly_stream_t st) {
+                              const void* shift, float* maps, ly_stream_t st) {
   LY_REQUIRE(maps, "ly_rf_tc_stats: null pointer");
   return rf_tc_launch(0, x, ldx, N, H, W, C, s, ho, wo, wc, shift, nullptr, nullptr, nullptr, maps, (cudaStream_t)st);
 }
 
-// Pass 2: A bf16 [N*ho*wo][9*C], A[m][t*C + c] = relu(generate + shift) * se[n][c] * att[n][3h + t/3][3w + t%3].
+// Pass 2: A bf16 [N*ho*wo][9*C], A[m][(c/16)*144 + t*16 + c%16] = relu(generate + shift) * se[n][c] * att[n][3h+t/3][3w+t%3]
+// (channel-group-major columns: one item's 144 values per pixel are contiguous, so TMA writes them back in 288-byte rows).
 extern "C" int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
-                              const float* shift, const float* se, const float* att, void* A, ly_stream_t st) {
-  LY_REQUIRE(se && att && A && reinterpret_cast<uintptr_t>(A) % 32 == 0 && reinterpret_cast<uintptr_t>(se) % 16 == 0,
+                              const void* shift, const float* se, const float* att, void* A, ly_stream_t st) {
+  LY_REQUIRE(se && att && A && reinterpret_cast<uintptr_t>(A) % 16 == 0 && reinterpret_cast<uintptr_t>(se) % 16 == 0,
              "ly_rf_tc_apply: null or misaligned pointer");
   return rf_tc_launch(1, x, ldx, N, H, W, C, s, ho, wo, wc, shift, se, att, A, nullptr, (cudaStream_t)st);
 }

@@ -584,8 +584,9 @@ class RFCBAMConv(nn.Module):
             gscale, gshift = ops.bn_fold(gbn, None, perm=perm)
             a = ops.rfcbam_front_infer(x, gen.weight, k, s, gscale, gshift, self.se.fc[0].weight,
                                        self.se.fc[2].weight, self.get_weight[0].weight)
-            wp = ops.cached([conv.weight], ("rfconv", c, k), lambda: pack_conv_weight(
-                conv.weight.detach().float().permute(0, 2, 3, 1).reshape(cout, k * k * c, 1, 1), None))
+            tcl = ops.rf_tc_layout(k, c)
+            wp = ops.cached([conv.weight], ("rfconv", c, k, tcl), lambda: pack_conv_weight(
+                ops.rf_conv_weight_matrix(conv.weight, k, c, tcl), None))
             scale, shift = ops.bn_fold(cbn, conv.bias)
             return ops.conv_infer([a], wp, cout, scale=scale, shift=shift, act="relu")
         se = self.se(x)

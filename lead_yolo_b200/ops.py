@@ -485,20 +485,39 @@ class RfGateAttFn(torch.autograd.Function):
 
 
 def _rf_tc_weights(wg, c, gscale, gshift):
-    """Diagonal generate weights [C/16][tap][t][16] (BatchNorm scale folded in) and shift [C/16][t][16] for ly_rf_tc_*."""
+    """Diagonal generate weights [C/16][tap][t][16] (BatchNorm scale folded in) and shift [C/16][t][16] as (bf16 hi | bf16 lo << 16) words for ly_rf_tc_*."""
     wgk = rf_pack_generate_weight(wg, c, 3) * gscale.view(9, 1, c)          # [t][tap][c]
     wc = wgk.view(9, 9, c // 16, 16).permute(2, 1, 0, 3).reshape(c // 16, 1296)
-    sh = gshift.view(9, c // 16, 16).permute(1, 0, 2).reshape(c // 16, 144)
-    return wc.to(BF16).contiguous(), sh.float().contiguous()
+    sh = gshift.float().view(9, c // 16, 16).permute(1, 0, 2).reshape(c // 16, 144)
+    hi = sh.to(BF16)
+    lo = (sh - hi.float()).to(BF16)
+    packed = (hi.view(torch.int16).to(torch.int32) & 0xFFFF) | (lo.view(torch.int16).to(torch.int32) << 16)
+    return wc.to(BF16).contiguous(), packed.contiguous()
+
+
+def rf_tc_layout(k, c):
+    """True when rfcbam_front_infer takes the tensor-core path, whose A columns are channel-group-major:
+    column (ch // 16) * 144 + t * 16 + ch % 16 instead of t * C + ch."""
+    return k == 3 and c % 16 == 0
+
+
+def rf_conv_weight_matrix(w, k, c, tc_layout):
+    """RFCBAMConv.conv weight [Cout, C, k, k] -> [Cout, k*k*C, 1, 1] in the column order of the gated operand A."""
+    cout = w.shape[0]
+    m = w.detach().float().permute(0, 2, 3, 1).reshape(cout, k * k, c)            # [cout][t][ch]
+    if tc_layout:
+        m = m.reshape(cout, k * k, c // 16, 16).permute(0, 2, 1, 3)
+    return m.reshape(cout, k * k * c, 1, 1)
 
 
 def rfcbam_front_infer(x, wg, k, s, gscale, gshift, w1, w2, wa):
-    """Inference: x -> gated GEMM operand A (N, k*k*C, ho, wo) in two passes over x (ly_rfcbam_front_infer)."""
+    """Inference: x -> gated GEMM operand A (N, k*k*C, ho, wo) in two passes over x (ly_rfcbam_front_infer, or the
+    tensor-core pair ly_rf_tc_stats / ly_rf_tc_apply when rf_tc_layout(k, C))."""
     x = to_act(x)
     n, c, h, w = x.shape
     ho, wo = rf_out_size(h, w, k, s)
     dev = x.device
-    if k == 3 and c % 16 == 0:
+    if rf_tc_layout(k, c):
         # feature generation on the tensor cores, twice: channel statistics first, then the gated GEMM operand
         wc, sh = cached([wg, gscale, gshift], ("rftc", c), lambda: _rf_tc_weights(wg, c, gscale, gshift))
         w1f = cached([w1], "sew1", lambda: w1.detach().float().contiguous())
