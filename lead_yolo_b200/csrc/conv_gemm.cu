@@ -17,6 +17,27 @@
 
 namespace ly {
 
+// Per-role wait accounting for tests/dev/conv_probe.cu; compiled out of the library.
+#ifdef CONV_GEMM_DEBUG
+__device__ long long conv_dbg[148][16];
+#define CG_WAIT(slot, bar, par)                    \
+  do {                                             \
+    const long long t__ = clock64();               \
+    mbar_wait(bar, par);                           \
+    dbg_acc[slot] += clock64() - t__;              \
+  } while (0)
+#define CG_DBG_DECL long long dbg_acc[4] = {0, 0, 0, 0}; const long long dbg_t0 = clock64();
+#define CG_DBG_FLUSH(base, nslots)                                                                      \
+  if (lane == 0 && blockIdx.x < 148) {                                                                  \
+    for (int z = 0; z < nslots; ++z) conv_dbg[blockIdx.x][base + z] = dbg_acc[z];                       \
+    conv_dbg[blockIdx.x][base + nslots] = clock64() - dbg_t0;                                           \
+  }
+#else
+#define CG_WAIT(slot, bar, par) mbar_wait(bar, par)
+#define CG_DBG_DECL
+#define CG_DBG_FLUSH(base, nslots)
+#endif
+
 constexpr int kMaxK = 96;      // K chunks of 64 per launch
 constexpr int kMaxStages = 8;
 constexpr int kMaxCout = 2560;  // scale/shift staged in shared memory
@@ -234,64 +255,71 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   const int num_tiles = tiles_m * p.tiles_n;
   const int my_tiles = ((int)blockIdx.x < num_tiles) ? (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
+  // The two single-lane roles below share their SM sub-partition with four busy epilogue warps, so every instruction of
+  // theirs costs several issue slots: indices advance incrementally (no division), descriptors are base + offset.
   if (warp == 0) {
     // ---------------- TMA producer ----------------
-    if (p.b_resident && lane == 0 && my_tiles > 0) {   // weights once per CTA, not once per tile
-      mbar_arrive_expect_tx(&b_ready_bar, (uint32_t)(p.num_k * b_stage));
-      for (int k = 0; k < p.num_k; ++k) tma_load_2d(sB + k * b_stage, &p.b_map, &b_ready_bar, k * 64, 0);
-    }
-    uint32_t it = 0;
-    for (int i = 0; i < my_tiles; ++i) {
-      const int tile = (int)blockIdx.x + i * (int)gridDim.x;
-      const int nt = tile % p.tiles_n, mt = tile / p.tiles_n;
-      const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h, n = mt / (p.tiles_w * p.tiles_h);
-      const int w0 = tw * p.Wt, h0 = th * p.Ht, n0 = nt * p.BN;
-      for (int k = 0; k < p.num_k; ++k, ++it) {
-        const int s = (int)(it % (uint32_t)p.stages);
-        const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
-        mbar_wait(&empty_bar[s], ph ^ 1u);
-        if (lane == 0) {
+    if (lane == 0 && my_tiles > 0) {
+      CG_DBG_DECL
+      if (p.b_resident) {   // weights once per CTA, not once per tile
+        mbar_arrive_expect_tx(&b_ready_bar, (uint32_t)(p.num_k * b_stage));
+        for (int k = 0; k < p.num_k; ++k) tma_load_2d(sB + k * b_stage, &p.b_map, &b_ready_bar, k * 64, 0);
+      }
+      const uint32_t tx = p.a_bytes + (p.b_resident ? 0u : (uint32_t)b_stage);
+      const int tiles_img = p.tiles_w * p.tiles_h;
+      int tile = (int)blockIdx.x;
+      int s = 0;
+      uint32_t ph = 1;   // parity to wait for on the empty barrier of slot s
+      for (int i = 0; i < my_tiles; ++i, tile += (int)gridDim.x) {
+        const int mt = tile / p.tiles_n, nt = tile - mt * p.tiles_n;
+        const int n = mt / tiles_img, tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+        const int w0 = tw * p.Wt, h0 = th * p.Ht, n0 = nt * p.BN;
+        for (int k = 0; k < p.num_k; ++k) {
           const KEntry e = p.sched[k];
-          mbar_arrive_expect_tx(&full_bar[s], p.a_bytes + (p.b_resident ? 0u : (uint32_t)b_stage));
+          CG_WAIT(0, &empty_bar[s], ph);
+          mbar_arrive_expect_tx(&full_bar[s], tx);
           tma_load_5d(sA + s * kAStage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
           if (!p.b_resident) tma_load_2d(sB + s * b_stage, &p.b_map, &full_bar[s], k * 64, n0);
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
-        __syncwarp();
       }
+      CG_DBG_FLUSH(0, 1)
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer ----------------
-    const uint32_t idesc = umma_idesc_bf16_f32(128, p.BN, 0, 0);
-    uint32_t it = 0;
-    if (p.b_resident && my_tiles > 0) mbar_wait(&b_ready_bar, 0);
-    for (int i = 0; i < my_tiles; ++i) {
-      const int buf = i % p.nbuf;
-      const uint32_t use = (uint32_t)(i / p.nbuf);
-      mbar_wait(&tmem_empty_bar[buf], (use & 1u) ^ 1u);   // epilogue has drained this accumulator
-      tc_fence_after_sync();
-      const uint32_t tmem_d = tmem_base + (uint32_t)(buf * p.BN);
-      for (int k = 0; k < p.num_k; ++k, ++it) {
-        const int s = (int)(it % (uint32_t)p.stages);
-        const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
-        mbar_wait(&full_bar[s], ph);
+    if (lane == 0 && my_tiles > 0) {
+      CG_DBG_DECL
+      const uint32_t idesc = umma_idesc_bf16_f32(128, p.BN, 0, 0);
+      const uint64_t a_desc0 = umma_smem_desc_sw128(smem_u32(sA), 16, 1024);
+      const uint64_t b_desc0 = umma_smem_desc_sw128(smem_u32(sB), 16, 1024);
+      const uint32_t a_step = (uint32_t)(kAStage >> 4), b_step = (uint32_t)(b_stage >> 4);
+      if (p.b_resident) mbar_wait(&b_ready_bar, 0);
+      int s = 0, buf = 0;
+      uint32_t ph = 0, use_par = 1;   // use_par: parity to wait for on tmem_empty_bar[buf]
+      for (int i = 0; i < my_tiles; ++i) {
+        CG_WAIT(0, &tmem_empty_bar[buf], use_par);   // epilogue has drained this accumulator
         tc_fence_after_sync();
-        if (lane == 0) {
-          const uint32_t a_base = smem_u32(sA + s * kAStage);
-          const uint32_t b_base = smem_u32(sB + (p.b_resident ? k : s) * b_stage);
-#pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const uint64_t adesc = umma_smem_desc_sw128(a_base + kk * 32, 16, 1024);
-            const uint64_t bdesc = umma_smem_desc_sw128(b_base + kk * 32, 16, 1024);
-            umma_bf16(tmem_d, adesc, bdesc, idesc, (uint32_t)((k | kk) != 0));
-          }
+        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * p.BN);
+        for (int k = 0; k < p.num_k; ++k) {
+          CG_WAIT(1, &full_bar[s], ph);
+          tc_fence_after_sync();
+          const uint64_t adesc = a_desc0 + (uint64_t)((uint32_t)s * a_step);
+          const uint64_t bdesc = b_desc0 + (uint64_t)((uint32_t)(p.b_resident ? k : s) * b_step);
+          umma_bf16(tmem_d, adesc, bdesc, idesc, (uint32_t)(k != 0));
+          umma_bf16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);   // + 32 bytes = next 16 K elements inside the swizzle atom
+          umma_bf16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+          umma_bf16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
           umma_commit(&empty_bar[s]);
-          if (k == p.num_k - 1) umma_commit(&tmem_full_bar[buf]);
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
-        __syncwarp();
+        umma_commit(&tmem_full_bar[buf]);
+        if (++buf == p.nbuf) { buf = 0; use_par ^= 1u; }
       }
+      CG_DBG_FLUSH(2, 2)
     }
   } else {
     // ---------------- epilogue ----------------
+    CG_DBG_DECL
     const int q = warp & 3;             // TMEM lane quadrant this warp may read
     // Group g serves TMEM buffer g % nbuf; when there are fewer buffers than groups (wide tiles), the groups that
     // share a buffer split its columns.  Each mbarrier is then waited on for consecutive phases only.
@@ -311,7 +339,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       const long pix = ((long)n * p.Hout + h) * p.Wout + w;
       const int buf = i % p.nbuf;
       const uint32_t use = (uint32_t)(i / p.nbuf);
-      mbar_wait(&tmem_full_bar[buf], use & 1u);
+      CG_WAIT(0, &tmem_full_bar[buf], use & 1u);
       tc_fence_after_sync();
       const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);
       const int cb = part * 16, cs = nparts * 16;
@@ -341,6 +369,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
     }
     if (p.tma_store && lane == 0) tma_store_wait_all<0>();   // stores complete before the CTA retires
+    if (warp == 2) { CG_DBG_FLUSH(5, 1) }
+    if (warp == 6) { CG_DBG_FLUSH(7, 1) }
   }
 
   tc_fence_before_sync();
