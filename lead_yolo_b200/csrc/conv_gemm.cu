@@ -7,6 +7,7 @@
 //                                is double-buffered in TMEM so tile i drains while tile i+1 is being multiplied
 //   A and B tiles live in 128B-swizzled shared memory, accumulators (128 x BN fp32) in TMEM.
 //   Zero padding of a 3x3 convolution and ragged channel counts are TMA out-of-bounds zero fill.
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -56,6 +57,8 @@ struct alignas(64) ConvGemmParams {
   int tiles_w, tiles_h, n_img, tiles_n;
   int Wt, Ht, Hout, Wout;
   int num_k, Cout, BN, tmem_cols, stages, nbuf;
+  int kgroup;      // K chunks per ring stage: one mbarrier phase and ONE tcgen05.commit (~340 cycles of the issuing lane,
+                   // tests/dev/mma_issue.cu) cover kgroup x 4 MMAs
   int tma_store;   // epilogue stages 32-row x 64-column slabs in shared memory and stores them with TMA
   int b_resident;  // all weight chunks stay in shared memory for the whole kernel (single N tile, small K*N)
   int act, out_fp32, vec_ok, res_vec_ok;
@@ -218,10 +221,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
   uint8_t* sA = smem;
-  uint8_t* sB = smem + p.stages * kAStage;
+  uint8_t* sB = smem + p.stages * p.kgroup * kAStage;
   const int b_stage = p.BN * 128;
   // 4 KB store slab per epilogue warp, after the A/B buffers (1024-byte aligned: every piece above is)
-  uint8_t* slabs = sB + (p.b_resident ? p.num_k : p.stages) * b_stage;
+  uint8_t* slabs = sB + (p.b_resident ? p.num_k : p.stages * p.kgroup) * b_stage;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.b_map);
@@ -265,7 +268,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         mbar_arrive_expect_tx(&b_ready_bar, (uint32_t)(p.num_k * b_stage));
         for (int k = 0; k < p.num_k; ++k) tma_load_2d(sB + k * b_stage, &p.b_map, &b_ready_bar, k * 64, 0);
       }
-      const uint32_t tx = p.a_bytes + (p.b_resident ? 0u : (uint32_t)b_stage);
+      const int kg = p.kgroup;
+      const uint32_t tx = (uint32_t)kg * (p.a_bytes + (p.b_resident ? 0u : (uint32_t)b_stage));
       const int tiles_img = p.tiles_w * p.tiles_h;
       int tile = (int)blockIdx.x;
       int s = 0;
@@ -274,12 +278,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         const int mt = tile / p.tiles_n, nt = tile - mt * p.tiles_n;
         const int n = mt / tiles_img, tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
         const int w0 = tw * p.Wt, h0 = th * p.Ht, n0 = nt * p.BN;
-        for (int k = 0; k < p.num_k; ++k) {
-          const KEntry e = p.sched[k];
+        for (int k = 0; k < p.num_k; k += kg) {
           CG_WAIT(0, &empty_bar[s], ph);
           mbar_arrive_expect_tx(&full_bar[s], tx);
-          tma_load_5d(sA + s * kAStage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
-          if (!p.b_resident) tma_load_2d(sB + s * b_stage, &p.b_map, &full_bar[s], k * 64, n0);
+          for (int j = 0; j < kg; ++j) {
+            const KEntry e = p.sched[k + j];
+            tma_load_5d(sA + (s * kg + j) * kAStage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
+            if (!p.b_resident) tma_load_2d(sB + (s * kg + j) * b_stage, &p.b_map, &full_bar[s], (k + j) * 64, n0);
+          }
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
       }
@@ -294,21 +300,24 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       const uint64_t b_desc0 = umma_smem_desc_sw128(smem_u32(sB), 16, 1024);
       const uint32_t a_step = (uint32_t)(kAStage >> 4), b_step = (uint32_t)(b_stage >> 4);
       if (p.b_resident) mbar_wait(&b_ready_bar, 0);
+      const int kg = p.kgroup;
       int s = 0, buf = 0;
       uint32_t ph = 0, use_par = 1;   // use_par: parity to wait for on tmem_empty_bar[buf]
       for (int i = 0; i < my_tiles; ++i) {
         CG_WAIT(0, &tmem_empty_bar[buf], use_par);   // epilogue has drained this accumulator
         tc_fence_after_sync();
         const uint32_t tmem_d = tmem_base + (uint32_t)(buf * p.BN);
-        for (int k = 0; k < p.num_k; ++k) {
+        for (int k = 0; k < p.num_k; k += kg) {
           CG_WAIT(1, &full_bar[s], ph);
           tc_fence_after_sync();
-          const uint64_t adesc = a_desc0 + (uint64_t)((uint32_t)s * a_step);
-          const uint64_t bdesc = b_desc0 + (uint64_t)((uint32_t)(p.b_resident ? k : s) * b_step);
-          umma_bf16(tmem_d, adesc, bdesc, idesc, (uint32_t)(k != 0));
-          umma_bf16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);   // + 32 bytes = next 16 K elements inside the swizzle atom
-          umma_bf16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
-          umma_bf16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+          for (int j = 0; j < kg; ++j) {
+            const uint64_t adesc = a_desc0 + (uint64_t)((uint32_t)(s * kg + j) * a_step);
+            const uint64_t bdesc = b_desc0 + (uint64_t)((uint32_t)(p.b_resident ? k + j : s * kg + j) * b_step);
+            umma_bf16(tmem_d, adesc, bdesc, idesc, (uint32_t)((k | j) != 0));
+            umma_bf16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);   // + 32 bytes = next 16 K elements inside the swizzle atom
+            umma_bf16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+            umma_bf16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+          }
           umma_commit(&empty_bar[s]);
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
@@ -585,7 +594,6 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
     rc = tmap_encode_bf16(&p.b_map, d->w_packed, 2, dims, str, box);
     if (rc != LY_OK) return rc;
   }
-  const int stage_bytes = kAStage + p.BN * 128;
   // one persistent CTA per SM.  When the whole packed weight matrix of this launch is small (single N tile), keep it
   // resident in shared memory: the TMA ring then carries activations only and the L2 -> SM traffic per tile halves.
   const uintptr_t oa = reinterpret_cast<uintptr_t>(d->out);
@@ -606,13 +614,21 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
   const int budget = 196 * 1024 - (p.tma_store ? kEpiGroups * 4 * 4096 : 0);
   const long b_all = (long)num_k * p.BN * 128;
   p.b_resident = (ny == 1 && b_all <= 100 * 1024) ? 1 : 0;
-  p.stages = kMaxStages;
-  if (p.b_resident) {
-    while (p.stages > 2 && (long)p.stages * kAStage + b_all > budget) --p.stages;
-  } else {
-    while (p.stages > 2 && p.stages * stage_bytes > budget) --p.stages;
+  // K chunks per ring stage: the largest divisor of num_k (<= 4) that still leaves a ring of >= 3 stages (>= 2 when
+  // one chunk alone is big).  Fewer, larger stages amortise the commit / mbarrier round trips of the single-lane roles.
+  const long chunk_bytes = kAStage + (p.b_resident ? 0 : p.BN * 128);
+  const long ring_budget = budget - (p.b_resident ? b_all : 0);
+  p.kgroup = 1;
+  static const int g_max = getenv("LY_CONV_KGROUP_MAX") ? atoi(getenv("LY_CONV_KGROUP_MAX")) : 4;     // dev knobs
+  static const int min_stages = getenv("LY_CONV_MIN_STAGES") ? atoi(getenv("LY_CONV_MIN_STAGES")) : 2;
+  for (int g = g_max; g >= 2; --g) {
+    if (num_k % g == 0 && ring_budget / (g * chunk_bytes) >= min_stages) { p.kgroup = g; break; }
   }
-  const size_t smem_bytes = (p.tma_store ? (size_t)kEpiGroups * 4 * 4096 : 0) + (p.b_resident ? (size_t)p.stages * kAStage + (size_t)b_all : (size_t)p.stages * stage_bytes) + 1024;
+  p.stages = (int)(ring_budget / (p.kgroup * chunk_bytes));
+  if (p.stages > kMaxStages) p.stages = kMaxStages;
+  LY_REQUIRE(p.stages >= 2, "shared-memory ring too small (BN=%d)", p.BN);
+  const size_t smem_bytes = (p.tma_store ? (size_t)kEpiGroups * 4 * 4096 : 0) + (p.b_resident ? (size_t)b_all : 0) +
+                            (size_t)p.stages * p.kgroup * chunk_bytes + 1024;
 
   // ---- epilogue
   p.act = d->act;
