@@ -351,8 +351,10 @@ __global__ void __launch_bounds__(256) rf_gate2_kernel(const __nv_bfloat16* __re
   *reinterpret_cast<uint4*>(A + tid * 8) = pack8(g);
 }
 
-// ---- k = 1 (generate is a per-channel scale): lean streaming kernels, one warp per pixel -------------------------
-// pass 1: g = relu(w'[c]*x + shift[c]);  max_c / mean_c via warp shuffles;  SE sums accumulated per warp
+// ---- k = 1 (generate is a per-channel scale): lean streaming kernels --------------------------------------------
+// pass 1: g = relu(w'[c]*x + shift[c]);  max_c / mean_c via warp shuffles;  SE sums accumulated per warp.
+// One warp per pixel, four pixels in flight per warp (four independent 16-byte loads per lane before any arithmetic).
+template <bool TWO>   // TWO: a second channel vector per lane (C > 256)
 __global__ void __launch_bounds__(256) rf1_stats_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int HW, int V,
                                                         const float* __restrict__ wgk, const float* __restrict__ scale,
                                                         const float* __restrict__ shift, float* __restrict__ maps,
@@ -363,9 +365,11 @@ __global__ void __launch_bounds__(256) rf1_stats_kernel(const __nv_bfloat16* __r
   const int wpb = blockDim.x >> 5;
   const long warps = (long)gridDim.x * wpb;
   const long w0 = (long)blockIdx.x * wpb + (threadIdx.x >> 5);
-  float wv[2][8], hv[2][8], gs[2][8];
+  constexpr int NQ = TWO ? 2 : 1;
+  constexpr bool two = TWO;
+  float wv[NQ][8], hv[NQ][8], gs[NQ][8];
 #pragma unroll
-  for (int q = 0; q < 2; ++q) {
+  for (int q = 0; q < NQ; ++q) {
     const int v = lane + q * 32;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -375,30 +379,50 @@ __global__ void __launch_bounds__(256) rf1_stats_kernel(const __nv_bfloat16* __r
       gs[q][e] = 0.f;
     }
   }
-  for (long p = w0; p < HW; p += warps) {
-    const __nv_bfloat16* px = x + ((long)n * HW + p) * ldx;
-    float mx = 0.f, sm = 0.f;
+  const float invC = 1.f / (float)C;
+  const __nv_bfloat16* img = x + (long)n * HW * ldx;
+  for (long p0 = w0; p0 < HW; p0 += 4 * warps) {
+    uint4 u[4][NQ];
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const int v = lane + q * 32;
-      if (v < V) {
+    for (int j = 0; j < 4; ++j) {
+      const long p = p0 + j * warps;
+      u[j][0] = (p < HW && lane < V) ? ldx16(img + p * ldx + lane * 8) : make_uint4(0, 0, 0, 0);
+      if (two) u[j][NQ - 1] = (p < HW && lane + 32 < V) ? ldx16(img + p * ldx + (lane + 32) * 8) : make_uint4(0, 0, 0, 0);
+    }
+    float mx[4], sm[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      mx[j] = 0.f; sm[j] = 0.f;
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
         float f[8];
-        unpack8(ldx16(px + v * 8), f);
+        unpack8(u[j][q], f);
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          gs[q][e] += f[e];
+          gs[q][e] += f[e];                       // zero vectors (inactive lanes / pixels) add nothing
           const float g = fmaxf(fmaf(f[e], wv[q][e], hv[q][e]), 0.f);
-          mx = fmaxf(mx, g);
-          sm += g;
+          mx[j] = fmaxf(mx[j], g);
+          sm[j] += g;
         }
       }
+      if (lane >= V) { mx[j] = 0.f; sm[j] = 0.f; }   // inactive lanes would contribute relu(shift)
     }
-    mx = warp_max(mx);
-    sm = warp_sum(sm);
-    if (lane == 0) *reinterpret_cast<float2*>(maps + ((long)n * HW + p) * 2) = make_float2(mx, sm / (float)C);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], o));
+        sm[j] += __shfl_xor_sync(0xffffffffu, sm[j], o);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long p = p0 + j * warps;
+      if (lane == j && p < HW) *reinterpret_cast<float2*>(maps + ((long)n * HW + p) * 2) = make_float2(mx[j], sm[j] * invC);
+    }
   }
 #pragma unroll
-  for (int q = 0; q < 2; ++q) {
+  for (int q = 0; q < NQ; ++q) {
     const int v = lane + q * 32;
     if (v < V) {
 #pragma unroll
@@ -407,28 +431,53 @@ __global__ void __launch_bounds__(256) rf1_stats_kernel(const __nv_bfloat16* __r
   }
 }
 
-// pass 2: A = relu(w'*x + shift) * se[n,c] * att[n,pixel]   (flat, fully coalesced)
-__global__ void __launch_bounds__(256) rf1_apply_kernel(const __nv_bfloat16* __restrict__ x, long ldx, long M, int HW,
-                                                        int V, const float* __restrict__ wgk,
-                                                        const float* __restrict__ scale,
+// pass 2: A = relu(w'*x + shift) * se[n,c] * att[n,pixel] = relu(x * (w'*se) + shift*se) * att   (se > 0).
+// A thread keeps ONE 8-channel vector for its whole life, so the per-channel coefficients are registers and the loop
+// body is one 16-byte load, one broadcast attention load, 16 FMAs/MAXs and one 16-byte store; block = rows x V threads.
+__global__ void __launch_bounds__(256) rf1_apply_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int HW, int V,
+                                                        const float* __restrict__ wgk, const float* __restrict__ scale,
                                                         const float* __restrict__ shift, const float* __restrict__ se,
                                                         const float* __restrict__ att, __nv_bfloat16* __restrict__ A) {
-  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (tid >= M * V) return;
-  const int v = (int)(tid % V);
-  const long m = tid / V;
-  const long n = m / HW;
+  const int n = blockIdx.y;
+  const int rows = 256 / V;
+  const int v = threadIdx.x % V, row = threadIdx.x / V;
+  if (row >= rows) return;
   const int C = V * 8;
-  float f[8];
-  unpack8(ldx16(x + m * ldx + v * 8), f);
-  const float a = __ldg(att + m);
+  float wse[8], hse[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
     const int c = v * 8 + e;
-    const float w = __ldg(wgk + c) * (scale != nullptr ? __ldg(scale + c) : 1.f);
-    f[e] = fmaxf(fmaf(f[e], w, __ldg(shift + c)), 0.f) * __ldg(se + n * C + c) * a;
+    const float g = __ldg(se + (long)n * C + c);
+    wse[e] = __ldg(wgk + c) * (scale != nullptr ? __ldg(scale + c) : 1.f) * g;
+    hse[e] = __ldg(shift + c) * g;
   }
-  *reinterpret_cast<uint4*>(A + m * (long)C + v * 8) = pack8(f);
+  const __nv_bfloat16* xin = x + (long)n * HW * ldx + v * 8;
+  __nv_bfloat16* out = A + (long)n * HW * C + v * 8;
+  const float* at = att + (long)n * HW;
+  const long stride = (long)gridDim.x * rows;
+  long p = (long)blockIdx.x * rows + row;
+  for (; p + 3 * stride < HW; p += 4 * stride) {
+    uint4 u[4];
+    float a[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { u[j] = ldx16(xin + (p + j * stride) * ldx); a[j] = __ldg(at + p + j * stride); }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float f[8];
+      unpack8(u[j], f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = fmaxf(fmaf(f[e], wse[e], hse[e]), 0.f) * a[j];
+      *reinterpret_cast<uint4*>(out + (p + j * stride) * C) = pack8(f);
+    }
+  }
+  for (; p < HW; p += stride) {
+    float f[8];
+    unpack8(ldx16(xin + p * ldx), f);
+    const float a = __ldg(at + p);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = fmaxf(fmaf(f[e], wse[e], hse[e]), 0.f) * a;
+    *reinterpret_cast<uint4*>(out + p * C) = pack8(f);
+  }
 }
 
 }  // namespace ly
@@ -468,10 +517,14 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
     const size_t sm1 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * WPB * 8 + (size_t)WPB * 2 * KK * 512;
     if (k == 1) {
       int bx1 = ceil_div((long)sms * 8, N);
-      if (bx1 > ceil_div(H * W, 8)) bx1 = ceil_div(H * W, 8);
+      if (bx1 > ceil_div(H * W, 32)) bx1 = ceil_div(H * W, 32);
       if (bx1 < 1) bx1 = 1;
-      rf1_stats_kernel<<<dim3((unsigned)bx1, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W, V,
-                                                                            wgk, scale, shift, maps, gap_sum);
+      if (V > 32)
+        rf1_stats_kernel<true><<<dim3((unsigned)bx1, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W,
+                                                                                    V, wgk, scale, shift, maps, gap_sum);
+      else
+        rf1_stats_kernel<false><<<dim3((unsigned)bx1, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W,
+                                                                                     V, wgk, scale, shift, maps, gap_sum);
     } else {
       static bool attr_done[64] = {false};
       int dev = 0;
@@ -500,8 +553,15 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
     dim3 grid2((unsigned)bx, (unsigned)vg8);
     const size_t sm2 = sizeof(float) * (size_t)(KK * KK + 2 * KK) * 8 * 8 + (size_t)8 * 2 * KK * 512;
     if (k == 1)
-      rf1_apply_kernel<<<ceil_div(M * V, 256), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, M, H * W, V, wgk, scale,
-                                                                shift, se, att, (__nv_bfloat16*)A);
+    {
+      const int rows = 256 / V;
+      long bxa = ceil_div((long)H * W, (long)rows * 8);     // ~8 pixels per thread
+      const long cap = ceil_div((long)sms * 16, (long)N);
+      if (bxa > cap) bxa = cap;
+      if (bxa < 1) bxa = 1;
+      rf1_apply_kernel<<<dim3((unsigned)bxa, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W, V, wgk,
+                                                                            scale, shift, se, att, (__nv_bfloat16*)A);
+    }
     else
       rf_gate2_kernel<<<ceil_div(M * KK * V, 256), 256, 0, stream>>>((const __nv_bfloat16*)A, M, KK, k, V, ho, wo, se,
                                                                     att, (__nv_bfloat16*)A);
