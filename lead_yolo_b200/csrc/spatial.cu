@@ -323,6 +323,10 @@ static int stem_wgrad_dispatch(const Tin* img, int N, int H, int W, int Cout, co
 
 }  // namespace ly
 
+namespace ly {
+int stem_tc_u8(const uint8_t* img, int N, int H, int W, int Cout, const float* wk, const float* scale, const float* shift,
+               float in_scale, __nv_bfloat16* out, long ld_out, cudaStream_t st);   // stem_tc.cu
+}
 using namespace ly;
 
 extern "C" int ly_stem_fwd(const void* img, int img_is_u8, int N, int H, int W, int Cout, const float* wk,
@@ -333,9 +337,14 @@ extern "C" int ly_stem_fwd(const void* img, int img_is_u8, int N, int H, int W, 
   LY_REQUIRE(reinterpret_cast<uintptr_t>(img) % 16 == 0, "ly_stem_fwd: image not 16-byte aligned");
   int rc = chk(out, ld_out, Cout, "ly_stem_fwd(out)");
   if (rc) return rc;
-  if (img_is_u8)
+  if (img_is_u8) {
+    // uint8 pixels are exact in bf16: the tensor-core kernel (stem_tc.cu) replaces 48*Cout FP32 FMAs per pixel
+    if (Cout % 8 == 0 && Cout <= 64 && W % 16 == 0)
+      return stem_tc_u8((const uint8_t*)img, N, H, W, Cout, wk, scale, shift, in_scale, (__nv_bfloat16*)out, ld_out,
+                        (cudaStream_t)st);
     return stem_dispatch<uint8_t>((const uint8_t*)img, N, H, W, Cout, wk, scale, shift, in_scale,
                                   (__nv_bfloat16*)out, ld_out, (cudaStream_t)st);
+  }
   return stem_dispatch<float>((const float*)img, N, H, W, Cout, wk, scale, shift, in_scale, (__nv_bfloat16*)out,
                               ld_out, (cudaStream_t)st);
 }
