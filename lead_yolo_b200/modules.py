@@ -243,6 +243,12 @@ class Upsample(nn.Module):
 # ------------------------------------------------------------------------------------------------------------
 # FasterNet — reference models/common.py:1411-1561
 # ------------------------------------------------------------------------------------------------------------
+# The partial conv runs on the implicit-GEMM kernel (tensor cores, 8-aligned channel slice, zero weight rows for the
+# untouched channels inside the slice); LY_PCONV_KERNEL=1 selects the FP32 CUDA-core kernel instead (A/B knob: it is
+# ~2.5x slower at C=80 since the GEMM kernel became persistent).
+_PCONV_KERNEL = bool(__import__('os').environ.get('LY_PCONV_KERNEL'))
+
+
 class Partial_conv3(nn.Module):
     """3x3 convolution over the first dim//n_div channels, rest untouched — reference common.py:1411-1437.
     Inside MLPBlock the partial conv is folded into the block's kernels; this standalone forward exists for
@@ -267,7 +273,7 @@ class Partial_conv3(nn.Module):
         w = self.partial_conv3.weight
         if x.shape[1] < cpp:
             raise LeadYoloError("Partial_conv3: channel count too small for the 8-aligned slice")
-        if fast and cpp in (8, 16, 24, 32, 40):
+        if fast and cpp in (8, 16, 24, 32, 40) and _PCONV_KERNEL:
             wk = ops.cached([w], ("pconvk", cpp), lambda: nn.functional.pad(
                 w.detach().float(), (0, 0, 0, 0, 0, cpp - cp, 0, cpp - cp)).permute(2, 3, 1, 0).reshape(
                     9, cpp, cpp).contiguous())
