@@ -42,6 +42,81 @@ __global__ void __launch_bounds__(256) ca_mid_kernel(const __nv_bfloat16* __rest
   }
 }
 
+// Fast path for mip == 8 and C == 32 * CPL: one WARP per pooled row, no block barrier inside the row loop.  The block
+// stages W1 [8][C] and Wx transposed to [8][C] in shared memory with coalesced loads (per-lane scalar loads of the
+// weights made the first version L1-request-bound); lane l owns channels [l*CPL, (l+1)*CPL) and reads its slices as
+// contiguous vectors.  The 8 hidden values come out of xor-shuffle reductions in every lane.
+// Blocks [0, gh) take the "h" rows (conv_h), the rest the "w" rows.
+template <int CPL>
+__global__ void __launch_bounds__(256) ca_mid_warp_kernel(const __nv_bfloat16* __restrict__ P, long ldp, long rows, long nh,
+                                                          int gh, const float* __restrict__ w1,
+                                                          const float* __restrict__ scale, const float* __restrict__ shift,
+                                                          const float* __restrict__ wh, const float* __restrict__ bh,
+                                                          const float* __restrict__ ww, const float* __restrict__ bw,
+                                                          __nv_bfloat16* __restrict__ gates, long ldg) {
+  constexpr int C = 32 * CPL;
+  __shared__ __align__(16) float s_w1[8 * C], s_wx[8 * C], s_b[C], s_sc[8], s_sh[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool is_h = (int)blockIdx.x < gh;
+  const float* wx = is_h ? wh : ww;
+  const float* bx = is_h ? bh : bw;
+  for (int i = threadIdx.x; i < 8 * C; i += 256) {
+    s_w1[i] = __ldg(w1 + i);
+    const int c = i >> 3, m = i & 7;        // wx is [C][8]: coalesced read, transposed write
+    s_wx[m * C + c] = __ldg(wx + i);
+  }
+  for (int i = threadIdx.x; i < C; i += 256) s_b[i] = __ldg(bx + i);
+  if (threadIdx.x < 8) { s_sc[threadIdx.x] = __ldg(scale + threadIdx.x); s_sh[threadIdx.x] = __ldg(shift + threadIdx.x); }
+  __syncthreads();
+  const long first = is_h ? 0 : nh, count = is_h ? nh : rows - nh;
+  const long wid = (long)(is_h ? blockIdx.x : blockIdx.x - gh) * 8 + warp;
+  const long nw = (long)(is_h ? gh : (int)gridDim.x - gh) * 8;
+  const int c0 = lane * CPL;
+  for (long i = wid; i < count; i += nw) {
+    const long r = first + i;
+    float f[CPL];
+    const __nv_bfloat16* src = P + r * ldp + c0;
+    if constexpr (CPL == 8) {
+      unpack8(__ldg(reinterpret_cast<const uint4*>(src)), f);
+    } else {
+#pragma unroll
+      for (int e = 0; e < CPL; e += 2) {
+        const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(src + e);
+        f[e] = __low2float(v); f[e + 1] = __high2float(v);
+      }
+    }
+    float y[8];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      float a = 0.f;
+#pragma unroll
+      for (int e = 0; e < CPL; ++e) a = fmaf(f[e], s_w1[m * C + c0 + e], a);
+      y[m] = a;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int m = 0; m < 8; ++m) y[m] += __shfl_xor_sync(0xffffffffu, y[m], o);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) y[m] = act_apply_t<LY_ACT_HSWISH>(fmaf(y[m], s_sc[m], s_sh[m]));
+    float g[CPL];
+#pragma unroll
+    for (int e = 0; e < CPL; ++e) {
+      float a = s_b[c0 + e];
+#pragma unroll
+      for (int m = 0; m < 8; ++m) a = fmaf(s_wx[m * C + c0 + e], y[m], a);
+      g[e] = 1.f / (1.f + __expf(-a));
+    }
+    __nv_bfloat16* dst = gates + r * ldg + c0;
+    if constexpr (CPL == 8) {
+      *reinterpret_cast<uint4*>(dst) = pack8(g);
+    } else {
+#pragma unroll
+      for (int e = 0; e < CPL; e += 2) *reinterpret_cast<__nv_bfloat162*>(dst + e) = __floats2bfloat162_rn(g[e], g[e + 1]);
+    }
+  }
+}
+
 }  // namespace ly
 
 using namespace ly;
@@ -55,6 +130,20 @@ extern "C" int ly_ca_mid_infer(const void* pooled, long ldp, long rows, long nh,
   LY_REQUIRE(ldp % 8 == 0 && ldp >= C && ldg >= C && reinterpret_cast<uintptr_t>(pooled) % 16 == 0 &&
                  reinterpret_cast<uintptr_t>(w1) % 16 == 0,
              "ly_ca_mid_infer: alignment / ld");
+  if (mip == 8 && (C == 64 || C == 128 || C == 256) && ldg % 8 == 0 && reinterpret_cast<uintptr_t>(gates) % 16 == 0) {
+    const long per = 32;  // rows per block: four per warp, so the staged weights are reused
+    const int gh = (int)ceil_div(nh, per), gwb = (int)ceil_div(rows - nh, per);
+    cudaStream_t s_ = (cudaStream_t)st;
+#define LY_CAMID(CPL)                                                                                                   \
+  ca_mid_warp_kernel<CPL><<<gh + gwb, 256, 0, s_>>>((const __nv_bfloat16*)pooled, ldp, rows, nh, gh, w1, scale, shift, wh, \
+                                                    bh, ww, bw, (__nv_bfloat16*)gates, ldg)
+    if (C == 64) LY_CAMID(2);
+    else if (C == 128) LY_CAMID(4);
+    else LY_CAMID(8);
+#undef LY_CAMID
+    LY_LAUNCH_CHECK();
+    return LY_OK;
+  }
   ca_mid_kernel<<<(unsigned)rows, 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)pooled, ldp, rows, nh, C, mip, w1,
                                                              scale, shift, wh, bh, ww, bw, (__nv_bfloat16*)gates, ldg);
   LY_LAUNCH_CHECK();
