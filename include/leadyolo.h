@@ -150,6 +150,13 @@ int ly_downsum2(const void* src, long lds, int N, int H, int W, int C, void* dst
  * rest = s, s = sigmoid.  anchors: [na][2] in stride units (Detect.anchors[i]). */
 int ly_detect_decode(const float* p, int N, int ny, int nx, int na, int no, float stride, const float* anchors,
                      float* raw, float* z, long rows_total, long row_off, ly_stream_t stream);
+/* The same with the 1x1 head convolution in front (models/yolo.py:79,90): ONE tensor-core kernel per level whose epilogue
+ * adds the bias and writes raw (may be NULL) and the decoded rows — the head's output never exists in its conv layout.
+ * x: NHWC bf16; w_packed as for ly_conv_fwd ([na*no][Kp]); bias fp32 [na*no]; anchors fp32 [na][2] in stride units.
+ * na*no <= 32, na <= 4. */
+int ly_detect_head_infer(const void* x, long ldx, int N, int H, int W, int Cin, const void* w_packed, const float* bias,
+                         int na, int no, float stride, const float* anchors, float* raw, float* z, long rows_total,
+                         long row_off, ly_stream_t stream);
 
 /* rfa.SE global average pool (models/rfa.py:80,90): bf16 [N][C] <- mean over HW. */
 int ly_gap(const void* x, long ldx, int N, int HW, int C, void* out, long ldo, ly_stream_t stream);

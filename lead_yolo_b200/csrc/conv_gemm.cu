@@ -70,6 +70,13 @@ struct alignas(64) ConvGemmParams {
   long res_ld;
   void* out;
   long out_ld;
+  // Detect head (ly_detect_head_infer): the epilogue decodes boxes instead of storing the raw GEMM output
+  float* det_z;          // [N][rows_total][no] decoded rows, or NULL (= ordinary convolution)
+  float* det_raw;        // [N][na][ny][nx][no] raw logits, or NULL
+  long det_rows_total, det_row_off;
+  int det_na, det_no, det_ny, det_nx;
+  float det_stride;
+  const float* det_anchors;   // device, [na][2] (w, h) in stride units
   KEntry sched[kMaxK];
 };
 
@@ -138,6 +145,49 @@ __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t 
           for (int j = 0; j < nv; ++j) o[j] = __float2bfloat16(v[j]);
         }
       }
+    }
+  }
+}
+
+// Detect epilogue (reference models/yolo.py:95-125): the 1x1 head's na*no <= 32 outputs of one pixel sit in one thread;
+// it adds the bias and writes the raw logits in the (bs, na, ny, nx, no) layout the loss consumes and the decoded row
+// (xy = (2s - 0.5 + grid) * stride, wh = (2s)^2 * anchor, rest = s, s = sigmoid) of the concatenated output, both fp32.
+// Consecutive lanes are consecutive x, so each store instruction covers a contiguous run of the output.
+__device__ __forceinline__ void epilogue_detect(const ConvGemmParams& p, uint32_t trow, bool valid, long pix,
+                                                const float* s_shift) {
+  uint32_t acc[32];
+  {
+    uint32_t lo[16], hi[16];
+    tmem_ld16(trow, lo);
+    tmem_ld16(trow + 16u, hi);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { acc[j] = lo[j]; acc[16 + j] = hi[j]; }
+  }
+  if (!valid) return;
+  const int ny = p.det_ny, nx = p.det_nx, no = p.det_no;
+  const long plane = (long)ny * nx;
+  const long n = pix / plane;
+  const int rem = (int)(pix - n * plane);
+  const int y = rem / nx, x = rem - y * nx;
+  const long a_step = plane * no;
+  float* raw = p.det_raw != nullptr ? p.det_raw + ((n * p.det_na * ny + y) * nx + x) * (long)no : nullptr;
+  float* z = p.det_z + (n * p.det_rows_total + p.det_row_off + (long)y * nx + x) * (long)no;
+  int a = 0, j = 0;
+#pragma unroll
+  for (int c = 0; c < 32; ++c) {
+    if (c < p.Cout) {      // warp-uniform
+      const float v = __uint_as_float(acc[c]) + s_shift[c];
+      if (raw != nullptr) raw[a * a_step + j] = v;
+      const float sg = 1.f / (1.f + expf(-v));
+      float o;
+      if (j == 0) o = (sg * 2.f + ((float)x - 0.5f)) * p.det_stride;
+      else if (j == 1) o = (sg * 2.f + ((float)y - 0.5f)) * p.det_stride;
+      else if (j == 2) o = (sg * 2.f) * (sg * 2.f) * (__ldg(p.det_anchors + a * 2) * p.det_stride);
+      else if (j == 3) o = (sg * 2.f) * (sg * 2.f) * (__ldg(p.det_anchors + a * 2 + 1) * p.det_stride);
+      else o = sg;
+      z[a * a_step + j] = o;
+      if (++j == no) { j = 0; ++a; }
     }
   }
 }
@@ -365,6 +415,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
             default: epilogue_cols_tma<LY_ACT_NONE>(p, trow, row0, n0, s_scale, s_shift, slab, lane, pix, valid); break;
           }
         }
+      } else if (p.det_z != nullptr) {
+        if (part == 0) epilogue_detect(p, trow, valid, pix, s_shift);
       } else
       switch (p.act) {  // activation resolved once per tile: the column loop is branch-free
         case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;
@@ -483,7 +535,18 @@ extern "C" int ly_conv_num_chunks(const ly_conv_desc* d) {
   return conv_chunks(d, g);
 }
 
-extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
+namespace ly {
+struct DetectArgs {
+  int na, no;
+  float stride;
+  const float* anchors;        // device, na x (w, h) in stride units
+  float* raw;
+  float* z;
+  long rows_total, row_off;
+};
+}  // namespace ly
+
+static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stream_t stream) {
   ConvGeom g;
   int rc = conv_geometry(d, &g);
   if (rc != LY_OK) return rc;
@@ -641,6 +704,17 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
   p.out_fp32 = d->out_fp32;
   p.patch_k = d->patch_k;
   p.patch_c = d->patch_c;
+  if (det != nullptr) {
+    LY_REQUIRE(flat_rows && d->patch_k == 0 && p.tiles_n == 1 && d->Cout == det->na * det->no && d->Cout <= 32 &&
+                   det->na <= 4 && d->residual == nullptr,
+               "detect head: needs a 1x1 convolution with na*no <= 32 outputs (got %d)", d->Cout);
+    p.det_z = det->z; p.det_raw = det->raw;
+    p.det_rows_total = det->rows_total; p.det_row_off = det->row_off;
+    p.det_na = det->na; p.det_no = det->no; p.det_ny = d->H; p.det_nx = d->W;
+    p.det_stride = det->stride;
+    p.det_anchors = det->anchors;
+    p.tma_store = 0;
+  }
 
   rc = set_smem_attr_once();
   if (rc != LY_OK) return rc;
@@ -650,4 +724,25 @@ extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) {
   conv_gemm_kernel<<<grid, kThreads, smem_bytes, (cudaStream_t)stream>>>(p);
   LY_LAUNCH_CHECK();
   return LY_OK;
+}
+
+extern "C" int ly_conv_fwd(const ly_conv_desc* d, ly_stream_t stream) { return conv_launch(d, nullptr, stream); }
+
+// Detect head of one level at inference (reference models/yolo.py:79,90,95-125): 1x1 convolution Cin -> na*no with bias
+// on the tensor cores whose epilogue writes raw [N][na][H][W][no] (may be NULL) and the decoded rows
+// z[N][rows_total][no] at row_off + a*H*W + y*W + x, both fp32.  x: NHWC bf16 (pixel stride ldx), w_packed as for
+// ly_conv_fwd, bias fp32 [na*no], anchors fp32 [na][2] in stride units (device).  na*no <= 32, na <= 4.
+extern "C" int ly_detect_head_infer(const void* x, long ldx, int N, int H, int W, int Cin, const void* w_packed,
+                                    const float* bias, int na, int no, float stride, const float* anchors, float* raw,
+                                    float* z, long rows_total, long row_off, ly_stream_t stream) {
+  LY_REQUIRE(x && w_packed && bias && anchors && z && na > 0 && no >= 5, "ly_detect_head_infer: bad args");
+  LY_REQUIRE(row_off >= 0 && row_off + (long)na * H * W <= rows_total, "ly_detect_head_infer: rows out of range");
+  ly_conv_desc d;
+  memset(&d, 0, sizeof(d));
+  d.n_src = 1; d.src[0] = x; d.src_c[0] = Cin; d.src_ld[0] = ldx;
+  d.N = N; d.H = H; d.W = W; d.kh = d.kw = 1; d.stride = 1; d.pad = 0;
+  d.Cout = na * no; d.w_packed = w_packed; d.shift = bias; d.act = LY_ACT_NONE;
+  d.out = z; d.out_ld = na * no; d.out_fp32 = 1;   // `out` is not written in detect mode
+  ly::DetectArgs det = {na, no, stride, anchors, raw, z, rows_total, row_off};
+  return conv_launch(&d, &det, stream);
 }

@@ -421,13 +421,18 @@ __global__ void __launch_bounds__(256) rf1_stats_kernel(const __nv_bfloat16* __r
       if (lane == j && p < HW) *reinterpret_cast<float2*>(maps + ((long)n * HW + p) * 2) = make_float2(mx[j], sm[j] * invC);
     }
   }
+  // SE sums: the block's warps are reduced in shared memory first (8x fewer same-address atomics)
+  __shared__ float red[8][NQ * 256];
+  const int wib = threadIdx.x >> 5;
 #pragma unroll
-  for (int q = 0; q < NQ; ++q) {
-    const int v = lane + q * 32;
-    if (v < V) {
+  for (int q = 0; q < NQ; ++q)
 #pragma unroll
-      for (int e = 0; e < 8; ++e) atomicAdd(&gap_sum[(long)n * C + v * 8 + e], gs[q][e]);
-    }
+    for (int e = 0; e < 8; ++e) red[wib][(q * 32 + lane) * 8 + e] = gs[q][e];
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f;
+    for (int w = 0; w < wpb; ++w) a += red[w][c];
+    atomicAdd(&gap_sum[(long)n * C + c], a);
   }
 }
 

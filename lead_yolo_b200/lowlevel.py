@@ -161,6 +161,7 @@ _SIGS = {
     "ly_downsum2": "pliiiipl",
     "ly_gap": "pliiipl",
     "ly_detect_decode": "piiiiifpppll",
+    "ly_detect_head_infer": "pliiiippiifpppll",
     "ly_ca_pool": "pliiiipl",
     "ly_ca_mid_infer": "plllii" + "ppppppp" + "pl",
     "ly_ca_apply": "plpliiiipl",

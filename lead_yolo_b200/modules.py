@@ -646,8 +646,8 @@ class Detect(nn.Module):
         x = list(x)
         fast = _fast(self)
         if fast and not self.export and torch.is_tensor(self.stride):
-            # inference: conv heads on the tensor cores, then one fp32 kernel per level writes both the permuted raw
-            # map and this level's decoded rows straight into the concatenated (bs, sum na*ny*nx, no) output
+            # inference: one tensor-core kernel per level: 1x1 head conv + bias, and its epilogue writes both the permuted
+            # raw map and this level's decoded rows straight into the concatenated (bs, sum na*ny*nx, no) output
             shapes = [(int(t.shape[2]), int(t.shape[3])) for t in x]
             bs = int(x[0].shape[0])
             rows = sum(self.na * ny * nx for ny, nx in shapes)
@@ -658,11 +658,18 @@ class Detect(nn.Module):
                 ny, nx = shapes[i]
                 wp = ops.cached([m.weight], ("wp", (m.in_channels,)), lambda: pack_conv_weight(m.weight, None))
                 b = ops.cached([m.bias], "b32", lambda: m.bias.detach().float().contiguous())
-                y = ops.conv_infer([x[i]], wp, m.out_channels, shift=b, out_fp32=True)
-                raw = torch.empty((bs, self.na, ny, nx, self.no), dtype=torch.float32, device=y.device)
+                raw = torch.empty((bs, self.na, ny, nx, self.no), dtype=torch.float32, device=x[i].device)
                 anc = ops.cached([self.anchors], ("anc", i), lambda: self.anchors[i].detach().float().contiguous())
-                ll.call("ly_detect_decode", y, bs, ny, nx, self.na, self.no, float(self.stride[i]), anc, raw, zcat,
-                        rows, off)
+                xi = ops.to_act(x[i])
+                if self.na * self.no <= 32 and self.na <= 4:
+                    # head conv + bias + decode in one kernel (ly_detect_head_infer)
+                    xi, ldx = ll.as_nhwc(xi)
+                    ll.call("ly_detect_head_infer", xi, ldx, bs, ny, nx, m.in_channels, wp, b, self.na, self.no,
+                            float(self.stride[i]), anc, raw, zcat, rows, off)
+                else:
+                    y = ops.conv_infer([xi], wp, m.out_channels, shift=b, out_fp32=True)
+                    ll.call("ly_detect_decode", y, bs, ny, nx, self.na, self.no, float(self.stride[i]), anc, raw, zcat,
+                            rows, off)
                 x[i] = raw
                 off += self.na * ny * nx
             return zcat, x
