@@ -154,7 +154,7 @@ _SIGS = {
     "ly_stem_fwd": "piiiiipppfpl",
     "ly_stem_wgrad": "piiiiiplfp",
     "ly_pconv3x3_fwd": "pliiiippl",
-    "ly_fasternet_block_infer": "ppiiiipiiiipp",
+    "ly_fasternet_block_infer": "ppiiiipiiipp",
     "ly_maxpool5_fwd": "pliiiiplp",
     "ly_maxpool5_bwd": "plpiiiipli",
     "ly_copy_upsample": "pliiiiipl",

@@ -335,8 +335,8 @@ class MLPBlock(nn.Module):
             scale, shift = ops.bn_fold(bn)
             n, _, h, wd = x.shape
             y = ll.empty_cl(n, c, h, wd, device=x.device)
-            ll.call("ly_fasternet_block_infer", x, y, n, h, wd, c, img[0], img[0].numel() * 2, img[1], img[2], img[3],
-                    scale, shift)
+            ll.call("ly_fasternet_block_infer", x, y, n, h, wd, c, img[0], img[0].numel() * 2, img[1], img[2], scale,
+                    shift)
             return y
         t1 = pc._t1(x, fast)
         # u = W1[:, :cp] t1 + W1[:, cp:] x[:, cp:]  ==  [W1[:, :cp] | 0] t1(8-aligned)  +  [0 | W1[:, cp:]] x

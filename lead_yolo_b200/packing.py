@@ -100,11 +100,12 @@ def swizzle32(mat: torch.Tensor) -> torch.Tensor:
 
 
 def fasternet_weight_image(w1: torch.Tensor, w2: torch.Tensor, wp: torch.Tensor):
-    """(image bf16 1-D, off_w2, off_w1p, off_wp in bytes) for MLPBlock weights mlp.0 (2C,C,1,1), mlp.3 (C,2C,1,1) and
-    partial_conv3 (Cp,Cp,3,3).  Sections: W1x [2C][64] | W2 [chunks][N2][64] | W1p [2C][16] | Wp [9][16][16]."""
+    """(image bf16 1-D, off_w2, off_wc in bytes) for MLPBlock weights mlp.0 (2C,C,1,1), mlp.3 (C,2C,1,1) and
+    partial_conv3 (Cp,Cp,3,3).  Sections: W1x [2C][64] | W2 [chunks][N2][64] | Wc [9][2C][16] with the partial conv folded
+    into the first GEMM: Wc_tap = W1[:, :Cp] @ Wp[:, :, tap] (fp32 product, rounded to bf16 once)."""
     c2, c = w1.shape[0], w1.shape[1]
     cp = wp.shape[0]
-    assert cp <= 16 and c <= 64
+    assert cp <= 16 and c <= 64 and c2 % 8 == 0
     n2 = (c + 15) // 16 * 16
     chunks = (c2 + 63) // 64
     f = lambda t: t.detach().float()  # noqa: E731
@@ -117,10 +118,9 @@ def fasternet_weight_image(w1: torch.Tensor, w2: torch.Tensor, wp: torch.Tensor)
     for kc in range(chunks):
         parts.append(swizzle128(w2m[:, kc * 64:(kc + 1) * 64].to(torch.bfloat16).contiguous()))
     off_w2 = parts[0].numel() * 2
-    off_w1p = off_w2 + sum(p.numel() for p in parts[1:]) * 2
-    parts.append(swizzle32(pad(w1m[:, :cp], (0, 16 - cp)).to(torch.bfloat16)))
-    off_wp = off_w1p + parts[-1].numel() * 2
+    off_wc = off_w2 + sum(p.numel() for p in parts[1:]) * 2
     wpf = f(wp)
     for t in range(9):
-        parts.append(swizzle32(pad(wpf[:, :, t // 3, t % 3], (0, 16 - cp, 0, 16 - cp)).to(torch.bfloat16)))
-    return torch.cat(parts).contiguous(), off_w2, off_w1p, off_wp
+        wc = w1m[:, :cp] @ wpf[:, :, t // 3, t % 3]                      # [2C][Cp]
+        parts.append(swizzle32(pad(wc, (0, 16 - cp)).to(torch.bfloat16)))
+    return torch.cat(parts).contiguous(), off_w2, off_wc
