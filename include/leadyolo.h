@@ -134,6 +134,10 @@ int ly_pconv3x3_fwd(const void* x, long ldx, int N, int H, int W, int cpp, const
  * idx (optional, uint8 [pixels][C]) records the arg-max tap for ly_maxpool5_bwd. */
 int ly_maxpool5_fwd(const void* x, long ldx, int N, int H, int W, int C, void* y, long ldy, uint8_t* idx,
                     ly_stream_t stream);
+/* SPPF at inference (models/common.py:364-367): the three cascaded 5x5 pools in one launch; y_k (k = 1, 2, 3 pools deep) is
+ * written at y + (k-1)*ystep elements, i.e. into three channel slices of the concat buffer.  H*W <= 1600. */
+int ly_sppf_pool3(const void* x, long ldx, int N, int H, int W, int C, void* y, long ldy, long ystep,
+                  ly_stream_t stream);
 int ly_maxpool5_bwd(const void* dy, long lddy, const uint8_t* idx, int N, int H, int W, int C, void* dx, long lddx,
                     int accumulate, ly_stream_t stream);
 

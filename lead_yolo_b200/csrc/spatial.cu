@@ -158,6 +158,74 @@ __global__ void __launch_bounds__(256) maxpool5_kernel(const __nv_bfloat16* __re
   }
 }
 
+// SPPF's three cascaded 5x5 pools in one launch (inference): y1 = mp5(x), y2 = mp5(y1) = mp9(x), y3 = mp5(y2) = mp13(x).
+// One block per (image, 8-channel vector): the H x W plane of that vector sits in shared memory; a separable pass
+// (rows, then columns) produces the 5 / 9 / 13 windows with packed bf16 maxima.  Out-of-image taps are skipped, which
+// equals MaxPool2d's -inf padding.
+__device__ __forceinline__ uint4 max8(const uint4& a, const uint4& b) {
+  uint4 r;
+  __nv_bfloat162 t;
+  t = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a.x), *reinterpret_cast<const __nv_bfloat162*>(&b.x));
+  r.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a.y), *reinterpret_cast<const __nv_bfloat162*>(&b.y));
+  r.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a.z), *reinterpret_cast<const __nv_bfloat162*>(&b.z));
+  r.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a.w), *reinterpret_cast<const __nv_bfloat162*>(&b.w));
+  r.w = *reinterpret_cast<uint32_t*>(&t);
+  return r;
+}
+
+__global__ void __launch_bounds__(256) sppf_pool3_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int H, int W,
+                                                         int V, __nv_bfloat16* __restrict__ y, long ldy, long ystep) {
+  extern __shared__ uint4 sp[];                 // [4][H*W]: input, row-max 5, 9, 13
+  const int HW = H * W;
+  uint4* sIn = sp;
+  uint4* s5 = sp + HW;
+  uint4* s9 = sp + 2 * HW;
+  uint4* s13 = sp + 3 * HW;
+  const int n = blockIdx.x / V, v = blockIdx.x - n * V;
+  const __nv_bfloat16* src = x + (long)n * HW * ldx + v * 8;
+  for (int p = threadIdx.x; p < HW; p += blockDim.x) sIn[p] = ldv(src + (long)p * ldx);
+  __syncthreads();
+  for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+    const int h = p / W, w = p - h * W;
+    const uint4* row = sIn + h * W;
+    uint4 m = row[w];
+#pragma unroll
+    for (int d = 1; d <= 6; ++d) {
+      if (w - d >= 0) m = max8(m, row[w - d]);
+      if (w + d < W) m = max8(m, row[w + d]);
+      if (d == 2) s5[p] = m;
+      if (d == 4) s9[p] = m;
+    }
+    s13[p] = m;
+  }
+  __syncthreads();
+  __nv_bfloat16* dst = y + (long)n * HW * ldy + v * 8;
+  for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+    const int h = p / W, w = p - h * W;
+    uint4 m5 = s5[p], m9 = s9[p], m13 = s13[p];
+#pragma unroll
+    for (int d = 1; d <= 6; ++d) {
+#pragma unroll
+      for (int sgn = -1; sgn <= 1; sgn += 2) {
+        const int hh = h + sgn * d;
+        if (hh >= 0 && hh < H) {
+          const int q = hh * W + w;
+          if (d <= 2) m5 = max8(m5, s5[q]);
+          if (d <= 4) m9 = max8(m9, s9[q]);
+          m13 = max8(m13, s13[q]);
+        }
+      }
+    }
+    __nv_bfloat16* o = dst + (long)p * ldy;
+    *reinterpret_cast<uint4*>(o) = m5;
+    *reinterpret_cast<uint4*>(o + ystep) = m9;
+    *reinterpret_cast<uint4*>(o + 2 * ystep) = m13;
+  }
+}
+
 // dx[i] (+)= Σ_{outputs o whose recorded arg-max is i} dy[o]   (gather form: no atomics)
 __global__ void __launch_bounds__(256) maxpool5_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long lddy,
                                                            const uint8_t* __restrict__ idx, int N, int H, int W,
@@ -370,6 +438,30 @@ extern "C" int ly_maxpool5_fwd(const void* x, long ldx, int N, int H, int W, int
   const long total = (long)N * H * W * V;
   maxpool5_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)x, ldx, N, H, W, V,
                                                                       (__nv_bfloat16*)y, ldy, idx);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+// y_k = k-fold 5x5 max pool of x for k = 1, 2, 3, written at y + (k-1)*ystep elements (three channel slices of one concat
+// buffer with pixel stride ldy).  H*W <= 1600.
+extern "C" int ly_sppf_pool3(const void* x, long ldx, int N, int H, int W, int C, void* y, long ldy, long ystep,
+                             ly_stream_t st) {
+  int rc = chk(x, ldx, C, "ly_sppf_pool3(x)");
+  if (rc) return rc;
+  rc = chk(y, ldy, C, "ly_sppf_pool3(y)");
+  if (rc) return rc;
+  LY_REQUIRE(ystep % 8 == 0 && ystep >= C && 3 * ystep <= ldy, "ly_sppf_pool3: ystep=%ld invalid", ystep);
+  LY_REQUIRE((long)H * W <= 1600, "ly_sppf_pool3: H*W=%ld exceeds 1600", (long)H * W);
+  const size_t smem = (size_t)4 * H * W * sizeof(uint4);
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  LY_CUDA(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    LY_CUDA(cudaFuncSetAttribute(sppf_pool3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 1600 * 16));
+    attr_done[dev & 63] = true;
+  }
+  sppf_pool3_kernel<<<(unsigned)(N * (C / 8)), 256, smem, (cudaStream_t)st>>>((const __nv_bfloat16*)x, ldx, H, W, C / 8,
+                                                                             (__nv_bfloat16*)y, ldy, ystep);
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

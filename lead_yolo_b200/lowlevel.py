@@ -157,6 +157,7 @@ _SIGS = {
     "ly_fasternet_block_infer": "ppiiiipiiipp",
     "ly_maxpool5_fwd": "pliiiiplp",
     "ly_maxpool5_bwd": "plpiiiipli",
+    "ly_sppf_pool3": "pliiiipll",
     "ly_copy_upsample": "pliiiiipl",
     "ly_downsum2": "pliiiipl",
     "ly_gap": "pliiipl",

@@ -203,8 +203,12 @@ class SPPF(nn.Module):
             c_ = self.cv1.conv.out_channels
             buf = ll.empty_cl(n, 4 * c_, h, w, device=x.device)
             self.cv1.run([x], out=buf[:, :c_])
-            for i in range(3):
-                ops.maxpool5_into(buf[:, i * c_:(i + 1) * c_], buf[:, (i + 1) * c_:(i + 2) * c_])
+            if h * w <= 1600:
+                # the three cascaded pools in one launch, straight into their concat slices
+                ll.call("ly_sppf_pool3", buf[:, :c_], 4 * c_, n, h, w, c_, buf[:, c_:2 * c_], 4 * c_, c_)
+            else:
+                for i in range(3):
+                    ops.maxpool5_into(buf[:, i * c_:(i + 1) * c_], buf[:, (i + 1) * c_:(i + 2) * c_])
             return self.cv2.run([buf])
         a = self.cv1(x)
         y1 = ops.MaxPool5Fn.apply(a)
