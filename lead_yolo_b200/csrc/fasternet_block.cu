@@ -23,6 +23,27 @@
 
 namespace ly {
 
+// Per-role wait accounting for tests/dev/fnb_probe.cu; compiled out of the library.
+#ifdef FNB_DEBUG
+__device__ long long fnb_dbg[296][16];
+#define FB_WAIT(slot, bar, par)                    \
+  do {                                             \
+    const long long t__ = clock64();               \
+    mbar_wait(bar, par);                           \
+    dbg_acc[slot] += clock64() - t__;              \
+  } while (0)
+#define FB_DBG_DECL long long dbg_acc[6] = {0, 0, 0, 0, 0, 0}; const long long dbg_t0 = clock64();
+#define FB_DBG_FLUSH(base, nslots)                                                                     \
+  if (blockIdx.x < 296) {                                                                              \
+    for (int z = 0; z < nslots; ++z) fnb_dbg[blockIdx.x][base + z] = dbg_acc[z];                       \
+    fnb_dbg[blockIdx.x][base + nslots] = clock64() - dbg_t0;                                           \
+  }
+#else
+#define FB_WAIT(slot, bar, par) mbar_wait(bar, par)
+#define FB_DBG_DECL
+#define FB_DBG_FLUSH(base, nslots)
+#endif
+
 struct alignas(64) FnbParams {
   CUtensorMap x_map;    // (C, W, 1, H, N) box (64, Wt, 1, Ht, 1)  SW128
   CUtensorMap tap_map;  // (16, W, 1, H, N) box (16, Wt, 1, Ht, 1) SW32
@@ -37,6 +58,7 @@ struct alignas(64) FnbParams {
   int off_w2, off_wc;    // byte offsets inside the image (W1x at 0)
   int v_chunks;          // 64-wide K chunks of the hidden tile
   int xbufs;             // 1 or 2 x buffers
+  int tmem_cols;
 };
 
 __device__ __forceinline__ uint64_t desc_sw32(uint32_t addr) {
@@ -55,7 +77,7 @@ constexpr int kTapBytes = 128 * 32;     // one tap box, SW32
 
 __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_constant__ FnbParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t w_bar, x_full[2], x_free[2], taps_full, u_full, v_ready, y_full, y_free;
+  __shared__ uint64_t w_bar, x_full[2], x_free[2], taps_full, u_full[2], v_ready, y_full, y_free;
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -70,24 +92,27 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
     mbar_init(&w_bar, 1);
     for (int b = 0; b < 2; ++b) { mbar_init(&x_full[b], 1); mbar_init(&x_free[b], 128); }
     mbar_init(&taps_full, 1);
-    mbar_init(&u_full, 1);
+    mbar_init(&u_full[0], 1);
+    mbar_init(&u_full[1], 1);
     mbar_init(&v_ready, 128);
     mbar_init(&y_full, 1);
     mbar_init(&y_free, 128);
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc(&tmem_base_s, 128);
+  if (warp == 2) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem = tmem_base_s;
-  const uint32_t tm_u = tmem, tm_y = tmem + (uint32_t)p.C2;
+  // u is double buffered: phase A of tile i+1 runs while tile i is in its hidden epilogue / phase B / output epilogue
+  const uint32_t tm_y = tmem + 2u * (uint32_t)p.C2;
 
   const int mine = ((int)blockIdx.x < p.tiles) ? (p.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   const int tiles_img = p.tiles_w * p.tiles_h;
 
   if (warp == 0) {
     if (lane == 0 && mine > 0) {
+      FB_DBG_DECL
       tma_prefetch_desc(&p.x_map);
       tma_prefetch_desc(&p.tap_map);
       mbar_arrive_expect_tx(&w_bar, (uint32_t)p.w_bytes);
@@ -100,19 +125,21 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
         const int b = p.xbufs == 2 ? (i & 1) : 0;
         const uint32_t use = p.xbufs == 2 ? ((uint32_t)i >> 1) : (uint32_t)i;
         // x buffer b: free once the output epilogue of its previous tile has read the residual
-        mbar_wait(&x_free[b], (use & 1u) ^ 1u);
+        FB_WAIT(0, &x_free[b], (use & 1u) ^ 1u);
         mbar_arrive_expect_tx(&x_full[b], box_x);
         tma_load_5d(sX + b * kXBytes, &p.x_map, &x_full[b], 0, w0, 0, h0, n);
         // tap boxes: free once the phase-A MMAs of the previous tile have completed
-        if (i > 0) mbar_wait(&u_full, (uint32_t)(i - 1) & 1u);
+        if (i > 0) FB_WAIT(1, &u_full[(i - 1) & 1], ((uint32_t)(i - 1) >> 1) & 1u);
         mbar_arrive_expect_tx(&taps_full, 9 * box_t);
 #pragma unroll
         for (int k = 0; k < 9; ++k)
           tma_load_5d(sTap + k * kTapBytes, &p.tap_map, &taps_full, 0, w0 + k % 3 - 1, 0, h0 + k / 3 - 1, n);
       }
+      FB_DBG_FLUSH(0, 2)
     }
   } else if (warp == 1) {
     if (lane == 0 && mine > 0) {
+      FB_DBG_DECL
       const uint32_t id1 = umma_idesc_bf16_f32(128, p.C2, 0, 0);
       const uint32_t id2 = umma_idesc_bf16_f32(128, p.N2, 0, 0);
       const uint64_t w1x_d = umma_smem_desc_sw128(smem_u32(sW), 16, 1024);
@@ -123,24 +150,31 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       const uint32_t wc_step = (uint32_t)(p.C2 * 32) >> 4;
       const int kx = (p.C + 15) / 16, kv = (p.C2 + 15) / 16;
       mbar_wait(&w_bar, 0);
-      for (int i = 0; i < mine; ++i) {
-        const uint32_t ph = (uint32_t)i & 1u;
+      // ---- phase A of tile i: u[i & 1][128 x 2C] = x * W1x^T + sum_taps tap * Wc_tap^T
+      auto phase_a = [&](int i) {
         const int b = p.xbufs == 2 ? (i & 1) : 0;
         const uint32_t use = p.xbufs == 2 ? ((uint32_t)i >> 1) : (uint32_t)i;
-        // ---- phase A: u[128 x 2C] = x * W1x^T + sum_taps tap * Wc_tap^T
-        mbar_wait(&x_full[b], use & 1u);
+        const uint32_t tm_u = tmem + (uint32_t)((i & 1) * p.C2);
+        FB_WAIT(0, &x_full[b], use & 1u);
         tc_fence_after_sync();
         const uint64_t x_d = umma_smem_desc_sw128(smem_u32(sX + b * kXBytes), 16, 1024);
         for (int k = 0; k < kx; ++k) umma_bf16(tm_u, x_d + (uint64_t)(k * 2), w1x_d + (uint64_t)(k * 2), id1, (uint32_t)(k != 0));
-        mbar_wait(&taps_full, ph);
+        FB_WAIT(1, &taps_full, (uint32_t)i & 1u);
         tc_fence_after_sync();
 #pragma unroll
         for (int k = 0; k < 9; ++k)
           umma_bf16(tm_u, tap_d + (uint64_t)(k * (kTapBytes >> 4)), wc_d + (uint64_t)((uint32_t)k * wc_step), id1, 1u);
-        umma_commit(&u_full);
+        umma_commit(&u_full[i & 1]);
+      };
+      phase_a(0);
+      for (int i = 0; i < mine; ++i) {
+        const uint32_t ph = (uint32_t)i & 1u;
+        // u[(i+1) & 1] was last read by the hidden epilogue of tile i-1, whose v_ready this lane has already seen; the
+        // x buffer is handed back at the start of the hidden epilogue, so the look-ahead works with one buffer too.
+        if (i + 1 < mine) phase_a(i + 1);
         // ---- phase B: y[128 x N2] = v[128 x 2C] * W2^T
-        mbar_wait(&v_ready, ph);
-        mbar_wait(&y_free, ph ^ 1u);     // the previous tile's output epilogue has drained y
+        FB_WAIT(2, &v_ready, ph);
+        FB_WAIT(3, &y_free, ph ^ 1u);     // the previous tile's output epilogue has drained y
         tc_fence_after_sync();
         for (int k = 0; k < kv; ++k) {
           const int kc = k >> 2, kk = k & 3;
@@ -149,20 +183,33 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
         }
         umma_commit(&y_full);
       }
+      FB_DBG_FLUSH(3, 4)
     }
   } else {
     const int q = warp & 3;
     const int r = q * 32 + lane;                 // tile row = TMEM lane
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const int hh = r / p.Wt, ww = r - hh * p.Wt;
+    FB_DBG_DECL
     for (int i = 0; i < mine; ++i) {
       const uint32_t ph = (uint32_t)i & 1u;
       const int b = p.xbufs == 2 ? (i & 1) : 0;
       const int t = (int)blockIdx.x + i * (int)gridDim.x;
       const int n = t / tiles_img, tr = t - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
       // ---- hidden: v = relu(scale*u + shift) -> bf16 -> SW128 A operand (zero padded to the 64-wide K chunks)
-      mbar_wait(&u_full, ph);
+      FB_WAIT(0, &u_full[i & 1], ((uint32_t)i >> 1) & 1u);
       tc_fence_after_sync();
+      // the phase-A MMAs are done with the x box; keep this row's residual in registers and hand the buffer back now, so
+      // the x box two tiles ahead is requested a whole tile earlier than "after the output epilogue"
+      uint4 xres[8];
+      {
+        const uint8_t* xrow = sX + b * kXBytes + r * 128;
+#pragma unroll
+        for (int cc = 0; cc < 8; ++cc)
+          if (cc * 8 < p.C) xres[cc] = *reinterpret_cast<const uint4*>(xrow + ((cc ^ (r & 7)) << 4));
+      }
+      mbar_arrive(&x_free[b]);
+      const uint32_t tm_u = tmem + (uint32_t)((i & 1) * p.C2);
       for (int c0 = 0; c0 < p.v_chunks * 64; c0 += 16) {
         uint32_t acc[16];
         if (c0 < p.C2) {
@@ -194,13 +241,17 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       fence_proxy_async_smem();
       mbar_arrive(&v_ready);
       // ---- output: y = x + W2 v
-      mbar_wait(&y_full, ph);
+#ifdef FNB_DEBUG
+      dbg_acc[2] += clock64();   // slot 2: time stamp sum at the end of the hidden epilogue (see probe)
+#endif
+      FB_WAIT(1, &y_full, ph);
       tc_fence_after_sync();
       const int h = th * p.Ht + hh, w = tw * p.Wt + ww;
       const bool valid = (r < p.Wt * p.Ht) && h < p.H && w < p.W;
       const long pix = ((long)n * p.H + h) * p.W + w;
-      const uint8_t* xrow = sX + b * kXBytes + r * 128;
-      for (int c0 = 0; c0 < p.N2; c0 += 16) {
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        if (c0 >= p.N2) break;
         uint32_t acc[16];
         __syncwarp();
         tmem_ld16(tm_y + lane_addr + (uint32_t)c0, acc);
@@ -211,7 +262,7 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
           const int c = c0 + g * 8;
           if (c >= p.C) break;
           float xr[8], v[8];
-          unpack8(*reinterpret_cast<const uint4*>(xrow + (((c >> 3) ^ (r & 7)) << 4)), xr);
+          unpack8(xres[(c0 >> 3) + g], xr);
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[g * 8 + j]) + xr[j];
           *reinterpret_cast<uint4*>(p.y + pix * p.C + c) = pack8(v);
@@ -219,12 +270,12 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       }
       tc_fence_before_sync();
       mbar_arrive(&y_free);
-      mbar_arrive(&x_free[b]);
     }
+    if (threadIdx.x == 64) { FB_DBG_FLUSH(8, 2) }
   }
   tc_fence_before_sync();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem, 128);
+  if (warp == 2) tmem_dealloc(tmem, (uint32_t)p.tmem_cols);
 }
 
 // TMA encode with a chosen swizzle (capi.cu offers SW128 only)
@@ -284,7 +335,9 @@ extern "C" int ly_fasternet_block_infer(const void* x, void* y, int N, int H, in
   p.off_w2 = off_w2;
   p.off_wc = off_wc;
   p.v_chunks = (p.C2 + 63) / 64;
-  LY_REQUIRE(p.C2 + p.N2 <= 128, "ly_fasternet_block_infer: accumulators do not fit 128 TMEM columns");
+  p.tmem_cols = 32;
+  while (p.tmem_cols < 2 * p.C2 + p.N2) p.tmem_cols *= 2;
+  LY_REQUIRE(p.tmem_cols <= 256, "ly_fasternet_block_infer: accumulators do not fit 256 TMEM columns");
   LY_REQUIRE(off_w2 % 1024 == 0 && off_wc % 256 == 0, "ly_fasternet_block_infer: weight image sections misaligned");
   // spatial tile of 128 pixels
   int best_wt = 16, best_ht = 8;
