@@ -7,9 +7,12 @@
 // (Wc_tap = W1[:, :Cp] * Wp_tap, packing.py), so a tile is two MMA phases instead of three:
 //     u = x * W1x^T + sum_taps tap * Wc_tap^T      (K = 64-chunk of x with its first Cp columns zeroed in W1x, 9 x K=16)
 //     y = relu(scale*u + shift) * W2^T + x
-//   warp 0   TMA (one lane): weight image once; per tile the x box (64-channel SW128, double buffered) and nine
-//            16-channel SW32 tap boxes (zero padding = TMA OOB fill); the next tile's boxes are requested as soon as
-//            the MMAs of the current one have consumed theirs
+// Tile rows use the pitch P = Wt + 2 of the tile's halo: accumulator row m = y*P + x (rows with x >= Wt are dead), so
+// the nine taps are ONE 16-channel halo box (Ht+2 x P pixels, zero padding = TMA OOB fill) read through descriptors that
+// start (dy+1)*P + (dx+1) rows further in (tests/dev/desc_shift.cu: the swizzle is a function of the absolute address).
+// That is 160-256 TMA box rows per tile instead of 9 x 128 — the TMA unit moves one 32-byte row per cycle.
+//   warp 0   TMA (one lane): weight image once; per tile the x box (64-channel SW128) and the halo box (SW32), both
+//            double buffered and requested as soon as the MMAs two tiles back have consumed theirs
 //   warp 1   tcgen05 issuer (one lane): phase A -> u in TMEM, commit; phase B -> y in TMEM, commit
 //   warps 2-5  TMEM -> registers -> shared: hidden v (bf16, SW128 A operand); final epilogue adds the residual from the
 //            x tile still in shared memory and stores y
@@ -45,15 +48,15 @@ __device__ long long fnb_dbg[296][16];
 #endif
 
 struct alignas(64) FnbParams {
-  CUtensorMap x_map;    // (C, W, 1, H, N) box (64, Wt, 1, Ht, 1)  SW128
-  CUtensorMap tap_map;  // (16, W, 1, H, N) box (16, Wt, 1, Ht, 1) SW32
+  CUtensorMap x_map;    // (C, W, 1, H, N) box (64, P, 1, Ht, 1)  SW128
+  CUtensorMap tap_map;  // (16, W, 1, H, N) box (16, P, 1, Ht+2, 1) SW32
   const __nv_bfloat16* x;
   __nv_bfloat16* y;
   const uint8_t* wimg;   // pre-swizzled weight image (see lead_yolo_b200/packing.py:fasternet_weight_image)
   const float* scale;    // [2C] folded BN
   const float* shift;
   int C, C2, N2;         // channels, hidden = 2C, GEMM2 N (C rounded up to 16)
-  int H, W, Wt, Ht, tiles_w, tiles_h, tiles;
+  int H, W, Wt, Ht, P, tiles_w, tiles_h, tiles;
   int w_bytes;           // size of the weight image
   int off_w2, off_wc;    // byte offsets inside the image (W1x at 0)
   int v_chunks;          // 64-wide K chunks of the hidden tile
@@ -73,25 +76,26 @@ __device__ __forceinline__ void bulk_copy_g2s(void* smem, const void* gmem, uint
 }
 
 constexpr int kXBytes = 128 * 128;      // x tile, SW128
-constexpr int kTapBytes = 128 * 32;     // one tap box, SW32
+constexpr int kHaloBytes = 288 * 32;    // halo box (<= 256 rows) + the rows a shifted 128-row read may run past it
 
 __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_constant__ FnbParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t w_bar, x_full[2], x_free[2], taps_full, u_full[2], v_ready, y_full, y_free;
+  __shared__ uint64_t w_bar, x_full[2], x_free[2], taps_full[2], u_full[2], v_ready, y_full, y_free;
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
   uint8_t* sX = smem;                                   // xbufs x 16 KB
-  uint8_t* sTap = sX + p.xbufs * kXBytes;               // 9 x 4 KB
-  uint8_t* sV = sTap + 9 * kTapBytes;                   // v_chunks x 16 KB
+  uint8_t* sTap = sX + p.xbufs * kXBytes;               // 2 halo buffers
+  uint8_t* sV = sTap + 2 * kHaloBytes;                  // v_chunks x 16 KB
   uint8_t* sW = sV + p.v_chunks * kXBytes;              // weight image
 
   if (warp == 1 && lane == 0) {
     mbar_init(&w_bar, 1);
     for (int b = 0; b < 2; ++b) { mbar_init(&x_full[b], 1); mbar_init(&x_free[b], 128); }
-    mbar_init(&taps_full, 1);
+    mbar_init(&taps_full[0], 1);
+    mbar_init(&taps_full[1], 1);
     mbar_init(&u_full[0], 1);
     mbar_init(&u_full[1], 1);
     mbar_init(&v_ready, 128);
@@ -117,7 +121,7 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       tma_prefetch_desc(&p.tap_map);
       mbar_arrive_expect_tx(&w_bar, (uint32_t)p.w_bytes);
       bulk_copy_g2s(sW, p.wimg, (uint32_t)p.w_bytes, &w_bar);
-      const uint32_t box_x = (uint32_t)(64 * p.Wt * p.Ht * 2), box_t = (uint32_t)(16 * p.Wt * p.Ht * 2);
+      const uint32_t box_x = (uint32_t)(64 * p.P * p.Ht * 2), box_t = (uint32_t)(16 * p.P * (p.Ht + 2) * 2);
       for (int i = 0; i < mine; ++i) {
         const int t = (int)blockIdx.x + i * (int)gridDim.x;
         const int n = t / tiles_img, tr = t - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
@@ -128,12 +132,10 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
         FB_WAIT(0, &x_free[b], (use & 1u) ^ 1u);
         mbar_arrive_expect_tx(&x_full[b], box_x);
         tma_load_5d(sX + b * kXBytes, &p.x_map, &x_full[b], 0, w0, 0, h0, n);
-        // tap boxes: free once the phase-A MMAs of the previous tile have completed
-        if (i > 0) FB_WAIT(1, &u_full[(i - 1) & 1], ((uint32_t)(i - 1) >> 1) & 1u);
-        mbar_arrive_expect_tx(&taps_full, 9 * box_t);
-#pragma unroll
-        for (int k = 0; k < 9; ++k)
-          tma_load_5d(sTap + k * kTapBytes, &p.tap_map, &taps_full, 0, w0 + k % 3 - 1, 0, h0 + k / 3 - 1, n);
+        // halo buffer i & 1: free once the phase-A MMAs of tile i-2 have completed
+        if (i > 1) FB_WAIT(1, &u_full[i & 1], (((uint32_t)i >> 1) - 1u) & 1u);
+        mbar_arrive_expect_tx(&taps_full[i & 1], box_t);
+        tma_load_5d(sTap + (i & 1) * kHaloBytes, &p.tap_map, &taps_full[i & 1], 0, w0 - 1, 0, h0 - 1, n);
       }
       FB_DBG_FLUSH(0, 2)
     }
@@ -146,6 +148,7 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       const uint64_t w2_d = umma_smem_desc_sw128(smem_u32(sW + p.off_w2), 16, 1024);
       const uint64_t wc_d = desc_sw32(smem_u32(sW + p.off_wc));
       const uint64_t tap_d = desc_sw32(smem_u32(sTap));
+      const uint32_t P2 = (uint32_t)(p.P * 2);     // one halo row = 32 bytes = 2 descriptor address units
       const uint64_t v_d = umma_smem_desc_sw128(smem_u32(sV), 16, 1024);
       const uint32_t wc_step = (uint32_t)(p.C2 * 32) >> 4;
       const int kx = (p.C + 15) / 16, kv = (p.C2 + 15) / 16;
@@ -159,11 +162,13 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
         tc_fence_after_sync();
         const uint64_t x_d = umma_smem_desc_sw128(smem_u32(sX + b * kXBytes), 16, 1024);
         for (int k = 0; k < kx; ++k) umma_bf16(tm_u, x_d + (uint64_t)(k * 2), w1x_d + (uint64_t)(k * 2), id1, (uint32_t)(k != 0));
-        FB_WAIT(1, &taps_full, (uint32_t)i & 1u);
+        FB_WAIT(1, &taps_full[i & 1], ((uint32_t)i >> 1) & 1u);
         tc_fence_after_sync();
+        const uint64_t halo_d = tap_d + (uint64_t)((i & 1) * (kHaloBytes >> 4));
 #pragma unroll
-        for (int k = 0; k < 9; ++k)
-          umma_bf16(tm_u, tap_d + (uint64_t)(k * (kTapBytes >> 4)), wc_d + (uint64_t)((uint32_t)k * wc_step), id1, 1u);
+        for (int k = 0; k < 9; ++k)   // tap (dy, dx) = the halo tile read (dy+1)*P + (dx+1) rows further in
+          umma_bf16(tm_u, halo_d + (uint64_t)((uint32_t)(k / 3) * P2 + (uint32_t)(k % 3) * 2u),
+                    wc_d + (uint64_t)((uint32_t)k * wc_step), id1, 1u);
         umma_commit(&u_full[i & 1]);
       };
       phase_a(0);
@@ -189,7 +194,7 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
     const int q = warp & 3;
     const int r = q * 32 + lane;                 // tile row = TMEM lane
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    const int hh = r / p.Wt, ww = r - hh * p.Wt;
+    const int hh = r / p.P, ww = r - hh * p.P;   // rows with ww >= Wt or hh >= Ht are dead
     FB_DBG_DECL
     for (int i = 0; i < mine; ++i) {
       const uint32_t ph = (uint32_t)i & 1u;
@@ -247,7 +252,7 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       FB_WAIT(1, &y_full, ph);
       tc_fence_after_sync();
       const int h = th * p.Ht + hh, w = tw * p.Wt + ww;
-      const bool valid = (r < p.Wt * p.Ht) && h < p.H && w < p.W;
+      const bool valid = ww < p.Wt && hh < p.Ht && h < p.H && w < p.W;
       const long pix = ((long)n * p.H + h) * p.W + w;
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 16) {
@@ -339,35 +344,33 @@ extern "C" int ly_fasternet_block_infer(const void* x, void* y, int N, int H, in
   while (p.tmem_cols < 2 * p.C2 + p.N2) p.tmem_cols *= 2;
   LY_REQUIRE(p.tmem_cols <= 256, "ly_fasternet_block_infer: accumulators do not fit 256 TMEM columns");
   LY_REQUIRE(off_w2 % 1024 == 0 && off_wc % 256 == 0, "ly_fasternet_block_infer: weight image sections misaligned");
-  // spatial tile of 128 pixels
-  int best_wt = 16, best_ht = 8;
+  // spatial tile: Ht rows of pitch P = Wt + 2 inside the 128 accumulator rows
+  int best_wt = 14, best_ht = 8;
   double best = -1;
-  const int cand[6] = {8, 16, 32, 64, 128, W <= 128 ? W : 128};
-  for (int i = 0; i < 6; ++i) {
-    const int wt = cand[i];
-    if (wt <= 0 || wt > 128) continue;
-    int ht = 128 / wt;
-    if (ht > H) ht = H;
+  const int pitches[3] = {16, 32, 64};
+  for (int i = 0; i < 3; ++i) {
+    const int wt = pitches[i] - 2, ht = 128 / pitches[i];
     const double eff = (double)H * W / ((double)ceil_div(W, wt) * ceil_div(H, ht) * 128.0);
     if (eff > best + 1e-9) { best = eff; best_wt = wt; best_ht = ht; }
   }
   p.Wt = best_wt;
   p.Ht = best_ht;
+  p.P = best_wt + 2;
   p.tiles_w = ceil_div(W, p.Wt);
   p.tiles_h = ceil_div(H, p.Ht);
   {
     uint64_t dims[5] = {(uint64_t)C, (uint64_t)W, 1, (uint64_t)H, (uint64_t)N};
     uint64_t str[4] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
-    uint32_t box[5] = {64, (uint32_t)p.Wt, 1, (uint32_t)p.Ht, 1};
+    uint32_t box[5] = {64, (uint32_t)p.P, 1, (uint32_t)p.Ht, 1};
     int rc = tmap_encode_bf16(&p.x_map, x, 5, dims, str, box);
     if (rc) return rc;
     uint64_t dims2[5] = {16, (uint64_t)W, 1, (uint64_t)H, (uint64_t)N};
-    uint32_t box2[5] = {16, (uint32_t)p.Wt, 1, (uint32_t)p.Ht, 1};
+    uint32_t box2[5] = {16, (uint32_t)p.P, 1, (uint32_t)(p.Ht + 2), 1};
     rc = encode_sw32(&p.tap_map, x, dims2, str, box2);
     if (rc) return rc;
   }
   // two x buffers (prefetch across tiles) when two CTAs still fit an SM with them
-  const size_t fixed = (size_t)9 * kTapBytes + (size_t)p.v_chunks * kXBytes + (size_t)w_bytes + 1024;
+  const size_t fixed = (size_t)2 * kHaloBytes + (size_t)p.v_chunks * kXBytes + (size_t)w_bytes + 1024;
   p.xbufs = (fixed + 2 * kXBytes <= 112 * 1024) ? 2 : 1;
   const size_t smem = fixed + (size_t)p.xbufs * kXBytes;
   static bool attr_done[64] = {false};
