@@ -14,8 +14,9 @@
 //   warp 0   TMA (one lane): weight image once; per tile the x box (64-channel SW128) and the halo box (SW32), both
 //            double buffered and requested as soon as the MMAs two tiles back have consumed theirs
 //   warp 1   tcgen05 issuer (one lane): phase A -> u in TMEM, commit; phase B -> y in TMEM, commit
-//   warps 2-5  TMEM -> registers -> shared: hidden v (bf16, SW128 A operand); final epilogue adds the residual from the
-//            x tile still in shared memory and stores y
+//   warps 2-5  hidden group: u (TMEM) -> relu(scale*u+shift) -> bf16 SW128 A operand of phase B in shared memory
+//   warps 6-9  output group: copies its row of the x box to registers (the box is then released), adds it to y (TMEM)
+//            and stores; the two groups work on different phases of consecutive tiles at the same time
 // Two CTAs per SM when the buffers fit (C = 24), so one CTA's epilogues overlap the other's MMAs.
 // Supported: C in {24, 40} (the HBM-bound FasterNet stages of LEAD-YOLO); other widths use the per-layer kernels.
 #include <string.h>
@@ -78,7 +79,7 @@ __device__ __forceinline__ void bulk_copy_g2s(void* smem, const void* gmem, uint
 constexpr int kXBytes = 128 * 128;      // x tile, SW128
 constexpr int kHaloBytes = 288 * 32;    // halo box (<= 256 rows) + the rows a shifted 128-row read may run past it
 
-__global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_constant__ FnbParams p) {
+__global__ void __launch_bounds__(320) fasternet_block_kernel(const __grid_constant__ FnbParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t w_bar, x_full[2], x_free[2], taps_full[2], u_full[2], v_ready, y_full, y_free;
   __shared__ uint32_t tmem_base_s;
@@ -103,6 +104,9 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
     mbar_init(&y_free, 128);
     fence_mbar_init();
   }
+  // the hidden tile's K padding (columns >= 2C of its last 64-wide chunk) is zeroed once and never written again
+  for (int i = threadIdx.x; i < p.v_chunks * kXBytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(sV)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
   if (warp == 2) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
   tc_fence_before_sync();
   __syncthreads();
@@ -190,9 +194,54 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       }
       FB_DBG_FLUSH(3, 4)
     }
-  } else {
+  } else if (warp < 6) {
+    // ---------------- hidden group (warps 2..5): v = relu(scale*u + shift) -> bf16 -> SW128 A operand ----------------
     const int q = warp & 3;
     const int r = q * 32 + lane;                 // tile row = TMEM lane
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    FB_DBG_DECL
+    for (int i = 0; i < mine; ++i) {
+      FB_WAIT(0, &u_full[i & 1], ((uint32_t)i >> 1) & 1u);
+      tc_fence_after_sync();
+      // sV is also read by phase B of the previous tile: its completion (y_full) is implied by v_ready ordering — the
+      // MMA lane issues phase B(i-1) before phase A(i+1)... but not before A(i); wait for y_full(i-1) explicitly.
+      if (i > 0) FB_WAIT(1, &y_full, (uint32_t)(i - 1) & 1u);
+      const uint32_t tm_u = tmem + (uint32_t)((i & 1) * p.C2);
+      for (int c0 = 0; c0 < p.C2; c0 += 16) {      // columns >= C2 of the last K chunk were zeroed once at start
+        uint32_t acc[16];
+        tmem_ld16(tm_u + lane_addr + (uint32_t)c0, acc);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          const int c = c0 + g * 8;
+          if (c < p.C2) {
+            const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + c));
+            const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + c + 4));
+            const float4 h0 = __ldg(reinterpret_cast<const float4*>(p.shift + c));
+            const float4 h1 = __ldg(reinterpret_cast<const float4*>(p.shift + c + 4));
+            const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+            const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {   // relu + convert + pack in one instruction
+              const float lo = fmaf(__uint_as_float(acc[g * 8 + 2 * j]), sc[2 * j], sh[2 * j]);
+              const float hi = fmaf(__uint_as_float(acc[g * 8 + 2 * j + 1]), sc[2 * j + 1], sh[2 * j + 1]);
+              asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(w[j]) : "f"(hi), "f"(lo));
+            }
+            const int kc = c >> 6, ch = (c >> 3) & 7;
+            *reinterpret_cast<uint4*>(sV + kc * kXBytes + r * 128 + ((ch ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+      }
+      tc_fence_before_sync();
+      fence_proxy_async_smem();
+      mbar_arrive(&v_ready);
+    }
+    if (threadIdx.x == 64) { FB_DBG_FLUSH(8, 2) }
+  } else {
+    // ---------------- output group (warps 6..9): y = x + W2 v ----------------
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const int hh = r / p.P, ww = r - hh * p.P;   // rows with ww >= Wt or hh >= Ht are dead
     FB_DBG_DECL
@@ -201,11 +250,9 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       const int b = p.xbufs == 2 ? (i & 1) : 0;
       const int t = (int)blockIdx.x + i * (int)gridDim.x;
       const int n = t / tiles_img, tr = t - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
-      // ---- hidden: v = relu(scale*u + shift) -> bf16 -> SW128 A operand (zero padded to the 64-wide K chunks)
+      // once the phase-A MMAs are done with the x box, keep this row's residual in registers and hand the buffer back:
+      // the x box two tiles ahead is then requested a whole tile earlier than "after the output epilogue"
       FB_WAIT(0, &u_full[i & 1], ((uint32_t)i >> 1) & 1u);
-      tc_fence_after_sync();
-      // the phase-A MMAs are done with the x box; keep this row's residual in registers and hand the buffer back now, so
-      // the x box two tiles ahead is requested a whole tile earlier than "after the output epilogue"
       uint4 xres[8];
       {
         const uint8_t* xrow = sX + b * kXBytes + r * 128;
@@ -214,41 +261,6 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
           if (cc * 8 < p.C) xres[cc] = *reinterpret_cast<const uint4*>(xrow + ((cc ^ (r & 7)) << 4));
       }
       mbar_arrive(&x_free[b]);
-      const uint32_t tm_u = tmem + (uint32_t)((i & 1) * p.C2);
-      for (int c0 = 0; c0 < p.v_chunks * 64; c0 += 16) {
-        uint32_t acc[16];
-        if (c0 < p.C2) {
-          tmem_ld16(tm_u + lane_addr + (uint32_t)c0, acc);
-          tmem_ld_wait();
-        }
-#pragma unroll
-        for (int g = 0; g < 2; ++g) {
-          const int c = c0 + g * 8;
-          float v[8];
-          if (c < p.C2) {
-            const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + c));
-            const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + c + 4));
-            const float4 h0 = __ldg(reinterpret_cast<const float4*>(p.shift + c));
-            const float4 h1 = __ldg(reinterpret_cast<const float4*>(p.shift + c + 4));
-            const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-            const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaxf(fmaf(__uint_as_float(acc[g * 8 + j]), sc[j], sh[j]), 0.f);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = 0.f;
-          }
-          const int kc = c >> 6, ch = (c >> 3) & 7;
-          *reinterpret_cast<uint4*>(sV + kc * kXBytes + r * 128 + ((ch ^ (r & 7)) << 4)) = pack8(v);
-        }
-      }
-      tc_fence_before_sync();
-      fence_proxy_async_smem();
-      mbar_arrive(&v_ready);
-      // ---- output: y = x + W2 v
-#ifdef FNB_DEBUG
-      dbg_acc[2] += clock64();   // slot 2: time stamp sum at the end of the hidden epilogue (see probe)
-#endif
       FB_WAIT(1, &y_full, ph);
       tc_fence_after_sync();
       const int h = th * p.Ht + hh, w = tw * p.Wt + ww;
@@ -276,7 +288,7 @@ __global__ void __launch_bounds__(192) fasternet_block_kernel(const __grid_const
       tc_fence_before_sync();
       mbar_arrive(&y_free);
     }
-    if (threadIdx.x == 64) { FB_DBG_FLUSH(8, 2) }
+    if (threadIdx.x == 192) { FB_DBG_FLUSH(11, 2) }
   }
   tc_fence_before_sync();
   __syncthreads();
@@ -385,7 +397,7 @@ extern "C" int ly_fasternet_block_infer(const void* x, void* y, int N, int H, in
   const int per_sm = smem <= 112 * 1024 ? 2 : 1;
   const long cap = (long)per_sm * device_sm_count();
   const unsigned grid = (unsigned)(p.tiles < cap ? p.tiles : cap);
-  fasternet_block_kernel<<<grid, 192, smem, (cudaStream_t)st>>>(p);
+  fasternet_block_kernel<<<grid, 320, smem, (cudaStream_t)st>>>(p);
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

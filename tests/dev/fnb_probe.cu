@@ -25,13 +25,14 @@ int main(int argc, char** argv) {
   float ms; cudaEventElapsedTime(&ms, e0, e1);
   static long long h[296][16];
   cudaMemcpyFromSymbol(h, ly::fnb_dbg, sizeof(h));
-  const char* names[11] = {"producer wait x_free", "producer wait u_full(taps)", "producer total", "mma wait x_full", "mma wait taps_full",
-                           "mma wait v_ready", "mma wait y_free", "mma total", "epi wait u_full", "epi wait y_full", "epi total"};
-  const int idx[11] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10};
+  const char* names[14] = {"producer wait x_free", "producer wait u_full(halo)", "producer total", "mma wait x_full", "mma wait taps_full",
+                           "mma wait v_ready", "mma wait y_free", "mma total", "hidden wait u_full", "hidden wait y_full(prev)", "hidden total",
+                           "output wait u_full", "output wait y_full", "output total"};
+  const int idx[14] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13};
   int nb = 0; for (int b = 0; b < 296; ++b) if (h[b][7]) ++nb;
-  const double tiles = (double)N * ((HW + 15) / 16) * ((HW + 7) / 8) / nb;   // approx
+  const double tiles = (double)N * ((HW + 13) / 14) * ((HW + 7) / 8) / nb;   // pitch-16 tiles (14 x 8)
   printf("C=%d %dx%d: %.1f us, %d CTAs, ~%.1f tiles each\n", C, HW, HW, ms * 1e3, nb, tiles);
-  for (int z = 0; z < 11; ++z) {
+  for (int z = 0; z < 14; ++z) {
     double a = 0;
     for (int b = 0; b < 296; ++b) a += (double)h[b][idx[z]];
     printf("  %-28s %9.0f clk (%6.0f / tile)\n", names[z], a / nb, a / nb / tiles);
