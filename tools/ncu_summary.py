@@ -11,7 +11,7 @@ import re
 import sys
 
 
-def launches(path, anchor="stem_kernel"):
+def launches(path, anchor="stem_"):
     rows = []
     with open(path) as f:
         lines = [l for l in f if not l.startswith("==")]
