@@ -48,6 +48,7 @@ struct KEntry {
   int16_t src;  // which A tensor map
   int16_t c0;   // channel coordinate of the chunk
   int8_t dw, dh, tz, pad_;
+  int16_t kb, kstep;  // halo mode: weight chunk of tap 0 and the chunk distance between taps
 };
 
 struct alignas(64) ConvGemmParams {
@@ -57,6 +58,10 @@ struct alignas(64) ConvGemmParams {
   int tiles_w, tiles_h, n_img, tiles_n;
   int Wt, Ht, Hout, Wout;
   int num_k, Cout, BN, tmem_cols, stages, nbuf;
+  int halo;        // 3x3 with resident weights: pitch P = Wt + 2 of the halo tile ONE box per 64-channel chunk serves all
+                   // nine taps through row-shifted descriptors (tests/dev/desc_shift.cu); 0 = one box per tap
+  int a_stage;     // bytes of one activation slot of the ring
+  int num_kb;      // 64-wide weight chunks (= num_k unless halo)
   int kgroup;      // K chunks per ring stage: one mbarrier phase and ONE tcgen05.commit (~340 cycles of the issuing lane,
                    // tests/dev/mma_issue.cu) cover kgroup x 4 MMAs
   int tma_store;   // epilogue stages 32-row x 64-column slabs in shared memory and stores them with TMA
@@ -271,10 +276,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
   uint8_t* sA = smem;
-  uint8_t* sB = smem + p.stages * p.kgroup * kAStage;
+  uint8_t* sB = smem + p.stages * p.kgroup * p.a_stage;
   const int b_stage = p.BN * 128;
   // 4 KB store slab per epilogue warp, after the A/B buffers (1024-byte aligned: every piece above is)
-  uint8_t* slabs = sB + (p.b_resident ? p.num_k : p.stages * p.kgroup) * b_stage;
+  uint8_t* slabs = sB + (p.b_resident ? p.num_kb : p.stages * p.kgroup) * b_stage;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.b_map);
@@ -315,8 +320,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     if (lane == 0 && my_tiles > 0) {
       CG_DBG_DECL
       if (p.b_resident) {   // weights once per CTA, not once per tile
-        mbar_arrive_expect_tx(&b_ready_bar, (uint32_t)(p.num_k * b_stage));
-        for (int k = 0; k < p.num_k; ++k) tma_load_2d(sB + k * b_stage, &p.b_map, &b_ready_bar, k * 64, 0);
+        mbar_arrive_expect_tx(&b_ready_bar, (uint32_t)(p.num_kb * b_stage));
+        for (int k = 0; k < p.num_kb; ++k) tma_load_2d(sB + k * b_stage, &p.b_map, &b_ready_bar, k * 64, 0);
       }
       const int kg = p.kgroup;
       const uint32_t tx = (uint32_t)kg * (p.a_bytes + (p.b_resident ? 0u : (uint32_t)b_stage));
@@ -333,7 +338,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
           mbar_arrive_expect_tx(&full_bar[s], tx);
           for (int j = 0; j < kg; ++j) {
             const KEntry e = p.sched[k + j];
-            tma_load_5d(sA + (s * kg + j) * kAStage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
+            tma_load_5d(sA + (s * kg + j) * p.a_stage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
             if (!p.b_resident) tma_load_2d(sB + (s * kg + j) * b_stage, &p.b_map, &full_bar[s], (k + j) * 64, n0);
           }
           if (++s == p.stages) { s = 0; ph ^= 1u; }
@@ -348,7 +353,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       const uint32_t idesc = umma_idesc_bf16_f32(128, p.BN, 0, 0);
       const uint64_t a_desc0 = umma_smem_desc_sw128(smem_u32(sA), 16, 1024);
       const uint64_t b_desc0 = umma_smem_desc_sw128(smem_u32(sB), 16, 1024);
-      const uint32_t a_step = (uint32_t)(kAStage >> 4), b_step = (uint32_t)(b_stage >> 4);
+      const uint32_t a_step = (uint32_t)(p.a_stage >> 4), b_step = (uint32_t)(b_stage >> 4);
       if (p.b_resident) mbar_wait(&b_ready_bar, 0);
       const int kg = p.kgroup;
       int s = 0, buf = 0;
@@ -360,6 +365,20 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         for (int k = 0; k < p.num_k; k += kg) {
           CG_WAIT(1, &full_bar[s], ph);
           tc_fence_after_sync();
+          if (p.halo) {
+            // nine taps from the one halo tile of this chunk: tap (dy, dx) starts (dy+1)*P + (dx+1) rows further in
+            const KEntry e = p.sched[k];
+            const uint64_t ahalo = a_desc0 + (uint64_t)((uint32_t)s * a_step);
+            for (int t = 0; t < 9; ++t) {
+              const int ty = t / 3, tx_ = t - ty * 3;
+              const uint64_t adesc = ahalo + (uint64_t)((uint32_t)(ty * p.halo + tx_) * 8u);   // 128-byte rows
+              const uint64_t bdesc = b_desc0 + (uint64_t)((uint32_t)(e.kb + t * e.kstep) * b_step);
+              umma_bf16(tmem_d, adesc, bdesc, idesc, (uint32_t)((k | t) != 0));
+              umma_bf16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
+              umma_bf16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+              umma_bf16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+            }
+          } else
           for (int j = 0; j < kg; ++j) {
             const uint64_t adesc = a_desc0 + (uint64_t)((uint32_t)(s * kg + j) * a_step);
             const uint64_t bdesc = b_desc0 + (uint64_t)((uint32_t)(p.b_resident ? k + j : s * kg + j) * b_step);
@@ -387,14 +406,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     const int part = grp / p.nbuf;
     const int nparts = kEpiGroups / p.nbuf;
     const int r = q * 32 + lane;
-    const int hh = r / p.Wt;
-    const int ww = r - hh * p.Wt;
+    const int pitch = p.halo ? p.halo : p.Wt;   // halo tiles keep the halo's pitch; columns >= Wt of a row are dead
+    const int hh = r / pitch;
+    const int ww = r - hh * pitch;
     for (int i = slot; i < my_tiles; i += p.nbuf) {
       const int tile = (int)blockIdx.x + i * (int)gridDim.x;
       const int nt = tile % p.tiles_n, mt = tile / p.tiles_n;
       const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h, n = mt / (p.tiles_w * p.tiles_h);
       const int h = th * p.Ht + hh, w = tw * p.Wt + ww, n0 = nt * p.BN;
-      const bool valid = (r < p.Wt * p.Ht) && (h < p.Hout) && (w < p.Wout);
+      const bool valid = (ww < p.Wt) && (hh < p.Ht) && (h < p.Hout) && (w < p.Wout);
       const long pix = ((long)n * p.Hout + h) * p.Wout + w;
       const int buf = i % p.nbuf;
       const uint32_t use = (uint32_t)(i / p.nbuf);
@@ -587,16 +607,36 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
     p.Wout = g.Wout;
     pick_tile(p.Hout, p.Wout, &p.Wt, &p.Ht);
   }
+  // 3x3 with weights that stay resident in shared memory: ONE halo box per 64-channel chunk feeds all nine taps
+  // (row-shifted descriptors), which cuts the L2 -> SM activation traffic ~6x.  The tile keeps the halo's pitch.
+  p.a_stage = kAStage;
+  p.num_kb = num_k;
+  {
+    static const int no_halo = getenv("LY_CONV_NO_HALO") ? 1 : 0;   // dev knob
+    const int cr = (d->Cout + 15) / 16 * 16;
+    if (!no_halo && g.taps == 9 && !g.patch && cr <= 256 && (long)num_k * cr * 128 <= 100 * 1024) {
+      double best = -1;
+      const int pitches[3] = {16, 32, 64};
+      for (int i = 0; i < 3; ++i) {
+        const int wt = pitches[i] - 2, ht = 128 / pitches[i];
+        const double eff = (double)p.Hout * p.Wout / ((double)ceil_div(p.Wout, wt) * ceil_div(p.Hout, ht) * 128.0);
+        if (eff > best + 1e-9) { best = eff; p.halo = pitches[i]; }
+      }
+      p.Wt = p.halo - 2;
+      p.Ht = 128 / p.halo;
+      p.a_stage = ((130 + 2 * p.halo) * 128 + 1023) / 1024 * 1024;   // box rows + what a shifted 128-row read runs past
+    }
+  }
   p.tiles_w = ceil_div(p.Wout, p.Wt);
   p.tiles_h = ceil_div(p.Hout, p.Ht);
-  p.a_bytes = (uint32_t)(64 * p.Wt * p.Ht * 2);
+  p.a_bytes = p.halo ? (uint32_t)(64 * p.halo * (p.Ht + 2) * 2) : (uint32_t)(64 * p.Wt * p.Ht * 2);
 
   // ---- A tensor maps + K schedule
-  int it = 0;
+  int it = 0, kb_base = 0;
   for (int s = 0; s < d->n_src; ++s) {
     const long ld = d->src_ld[s];
     uint64_t dims[5], str[4];
-    uint32_t box[5] = {64, (uint32_t)p.Wt, 1, (uint32_t)p.Ht, 1};
+    uint32_t box[5] = {64, (uint32_t)(p.halo ? p.halo : p.Wt), 1, (uint32_t)(p.halo ? p.Ht + 2 : p.Ht), 1};
     int ceff = d->src_c[s];
     if (flat_rows && d->patch_k == 0) {
       const uint64_t M = (uint64_t)d->N * d->H * d->W;
@@ -621,12 +661,24 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
     }
     rc = tmap_encode_bf16(&p.a_map[s], d->src[s], 5, dims, str, box);
     if (rc != LY_OK) return rc;
+    if (p.halo) {   // one entry per chunk; its nine weight chunks sit kstep apart in the packed K order (tap-major)
+      const int nch = ceil_div(ceff, 64);
+      for (int c = 0; c < nch; ++c) {
+        KEntry e;
+        e.src = (int16_t)s; e.c0 = (int16_t)(c * 64); e.dw = -1; e.dh = -1; e.tz = 0; e.pad_ = 0;
+        e.kb = (int16_t)(kb_base + c); e.kstep = (int16_t)nch;
+        p.sched[it++] = e;
+      }
+      kb_base += 9 * nch;
+      continue;
+    }
     for (int t = 0; t < g.taps; ++t) {
       for (int c0 = 0; c0 < ceff; c0 += 64) {
         KEntry e;
         e.src = (int16_t)s;
         e.c0 = (int16_t)c0;
         e.pad_ = 0;
+        e.kb = 0; e.kstep = 0;
         if (g.patch) {
           e.dw = 0; e.dh = 0; e.tz = (int8_t)t;
         } else {
@@ -679,12 +731,13 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   p.b_resident = (ny == 1 && b_all <= 100 * 1024) ? 1 : 0;
   // K chunks per ring stage: the largest divisor of num_k (<= 4) that still leaves a ring of >= 3 stages (>= 2 when
   // one chunk alone is big).  Fewer, larger stages amortise the commit / mbarrier round trips of the single-lane roles.
-  const long chunk_bytes = kAStage + (p.b_resident ? 0 : p.BN * 128);
+  LY_REQUIRE(!p.halo || p.b_resident, "halo tiles need resident weights");
+  const long chunk_bytes = p.a_stage + (p.b_resident ? 0 : p.BN * 128);
   const long ring_budget = budget - (p.b_resident ? b_all : 0);
   p.kgroup = 1;
   static const int g_max = getenv("LY_CONV_KGROUP_MAX") ? atoi(getenv("LY_CONV_KGROUP_MAX")) : 4;     // dev knobs
   static const int min_stages = getenv("LY_CONV_MIN_STAGES") ? atoi(getenv("LY_CONV_MIN_STAGES")) : 2;
-  for (int g = g_max; g >= 2; --g) {
+  for (int g = g_max; g >= 2 && !p.halo; --g) {
     if (num_k % g == 0 && ring_budget / (g * chunk_bytes) >= min_stages) { p.kgroup = g; break; }
   }
   p.stages = (int)(ring_budget / (p.kgroup * chunk_bytes));
