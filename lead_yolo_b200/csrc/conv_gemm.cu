@@ -85,6 +85,19 @@ struct alignas(64) ConvGemmParams {
   KEntry sched[kMaxK];
 };
 
+// act(scale*acc + shift).  For SiLU the kernel stages scale/2 and shift/2, so h = x/2 comes out of the one FFMA and
+// silu(x) = x * sigmoid(x) = h + h * tanh(h): FFMA, MUFU, FFMA instead of five instructions per element.
+template <int ACT>
+__device__ __forceinline__ float ssa(uint32_t acc, float sc, float sh) {
+  const float h = fmaf(__uint_as_float(acc), sc, sh);
+  if (ACT == LY_ACT_SILU) {
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+    return fmaf(h, t, h);
+  }
+  return act_apply_t<ACT>(h);
+}
+
 // One epilogue thread = one output pixel (TMEM lane).  Columns [c_begin, BN) are drained 16 at a time, stride c_step.
 template <int ACT>
 __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t trow, bool valid, int n, int h, int w,
@@ -123,7 +136,7 @@ __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t 
       float v[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j)
-        v[j] = act_apply_t<ACT>(fmaf(__uint_as_float(acc[g * 8 + j]), sc[j], sh[j]));
+        v[j] = ssa<ACT>(acc[g * 8 + j], sc[j], sh[j]);
       if (p.residual != nullptr) {
         if (p.res_vec_ok && nv == 8) {
           float rr[8];
@@ -226,7 +239,7 @@ __device__ __forceinline__ void epilogue_cols_tma(const ConvGemmParams& p, uint3
           const float sc[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
           const float sh[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
 #pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = act_apply_t<ACT>(fmaf(__uint_as_float(acc[g * 8 + j]), sc[j], sh[j]));
+          for (int j = 0; j < 8; ++j) v[j] = ssa<ACT>(acc[g * 8 + j], sc[j], sh[j]);
           if (p.residual != nullptr && valid) {
             float rr[8];
             unpack8(*reinterpret_cast<const uint4*>(p.residual + pix * p.res_ld + c), rr);
@@ -301,8 +314,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   // folded BatchNorm / bias of every output channel, padded so that vector reads past Cout stay in bounds
   const int cpad = (p.Cout + 7) & ~7;
   for (int i = threadIdx.x; i < cpad; i += blockDim.x) {
-    s_scale[i] = (p.scale != nullptr && i < p.Cout) ? p.scale[i] : 1.f;
-    s_shift[i] = (p.shift != nullptr && i < p.Cout) ? p.shift[i] : 0.f;
+    const float half = p.act == LY_ACT_SILU ? 0.5f : 1.f;   // see ssa<>
+    s_scale[i] = half * ((p.scale != nullptr && i < p.Cout) ? p.scale[i] : 1.f);
+    s_shift[i] = half * ((p.shift != nullptr && i < p.Cout) ? p.shift[i] : 0.f);
   }
   tc_fence_before_sync();
   __syncthreads();
