@@ -284,6 +284,37 @@ __global__ void __launch_bounds__(256) copy_up_kernel(const __nv_bfloat16* __res
   *reinterpret_cast<uint4*>(dst + pix * ldd + v * 8) = ldv(src + sp * lds + v * 8);
 }
 
+// up == 2: one thread per SOURCE vector, two of them in flight: one load feeds four stores
+__global__ void __launch_bounds__(256) copy_up2_kernel(const __nv_bfloat16* __restrict__ src, long lds, int N, int Hs,
+                                                       int Ws, int V, __nv_bfloat16* __restrict__ dst, long ldd) {
+  const long total = (long)N * Hs * Ws * V;
+  const long t0 = ((long)blockIdx.x * blockDim.x + threadIdx.x);
+  const long stride = (long)gridDim.x * blockDim.x;
+  const int W = Ws * 2;
+  uint4 u[2];
+  long sp[2];
+  int vv[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const long t = t0 + k * stride;
+    vv[k] = (int)(t % V);
+    sp[k] = t / V;
+    if (t < total) u[k] = ldv(src + sp[k] * lds + vv[k] * 8);
+  }
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    if (t0 + k * stride < total) {
+      const int w = (int)(sp[k] % Ws);
+      const long nh = sp[k] / Ws;               // n * Hs + h
+      __nv_bfloat16* o = dst + ((nh * 2) * W + 2 * w) * ldd + vv[k] * 8;
+      *reinterpret_cast<uint4*>(o) = u[k];
+      *reinterpret_cast<uint4*>(o + ldd) = u[k];
+      *reinterpret_cast<uint4*>(o + (long)W * ldd) = u[k];
+      *reinterpret_cast<uint4*>(o + (long)W * ldd + ldd) = u[k];
+    }
+  }
+}
+
 // Backward of the 2x nearest upsample: dst[n,h,w] = Σ_{a,b<2} src[n,2h+a,2w+b]
 __global__ void __launch_bounds__(256) downsum2_kernel(const __nv_bfloat16* __restrict__ src, long lds, int N, int H,
                                                        int W, int V, __nv_bfloat16* __restrict__ dst, long ldd) {
@@ -490,6 +521,13 @@ extern "C" int ly_copy_upsample(const void* src, long lds, int N, int Hs, int Ws
   LY_REQUIRE(up == 1 || up == 2, "ly_copy_upsample: up must be 1 or 2");
   const int V = C / 8;
   const long total = (long)N * Hs * up * Ws * up * V;
+  if (up == 2) {
+    const long src_total = (long)N * Hs * Ws * V;
+    copy_up2_kernel<<<ceil_div(src_total, 512), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)src, lds, N, Hs, Ws, V,
+                                                                           (__nv_bfloat16*)dst, ldd);
+    LY_LAUNCH_CHECK();
+    return LY_OK;
+  }
   copy_up_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)src, lds, N, Hs, Ws, V,
                                                                      up, (__nv_bfloat16*)dst, ldd);
   LY_LAUNCH_CHECK();
