@@ -171,6 +171,9 @@ __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t 
 // it adds the bias and writes the raw logits in the (bs, na, ny, nx, no) layout the loss consumes and the decoded row
 // (xy = (2s - 0.5 + grid) * stride, wh = (2s)^2 * anchor, rest = s, s = sigmoid) of the concatenated output, both fp32.
 // Consecutive lanes are consecutive x, so each store instruction covers a contiguous run of the output.
+// NO > 0: `no` known at compile time, so (anchor, field) of every unrolled column and the decode branch are static —
+// the runtime version is ~170 instructions per output value and made this epilogue the bottleneck of the head.
+template <int NO>
 __device__ __forceinline__ void epilogue_detect(const ConvGemmParams& p, uint32_t trow, bool valid, long pix,
                                                 const float* s_shift) {
   uint32_t acc[32];
@@ -183,7 +186,7 @@ __device__ __forceinline__ void epilogue_detect(const ConvGemmParams& p, uint32_
     for (int j = 0; j < 16; ++j) { acc[j] = lo[j]; acc[16 + j] = hi[j]; }
   }
   if (!valid) return;
-  const int ny = p.det_ny, nx = p.det_nx, no = p.det_no;
+  const int ny = p.det_ny, nx = p.det_nx, no = NO > 0 ? NO : p.det_no;
   const long plane = (long)ny * nx;
   const long n = pix / plane;
   const int rem = (int)(pix - n * plane);
@@ -191,21 +194,23 @@ __device__ __forceinline__ void epilogue_detect(const ConvGemmParams& p, uint32_
   const long a_step = plane * no;
   float* raw = p.det_raw != nullptr ? p.det_raw + ((n * p.det_na * ny + y) * nx + x) * (long)no : nullptr;
   float* z = p.det_z + (n * p.det_rows_total + p.det_row_off + (long)y * nx + x) * (long)no;
-  int a = 0, j = 0;
+  const float gx = ((float)x - 0.5f) * p.det_stride, gy = ((float)y - 0.5f) * p.det_stride, s2 = 2.f * p.det_stride;
+  int ar = 0, jr = 0;
 #pragma unroll
   for (int c = 0; c < 32; ++c) {
     if (c < p.Cout) {      // warp-uniform
+      const int a = NO > 0 ? c / NO : ar, j = NO > 0 ? c % NO : jr;
       const float v = __uint_as_float(acc[c]) + s_shift[c];
       if (raw != nullptr) raw[a * a_step + j] = v;
-      const float sg = 1.f / (1.f + expf(-v));
+      const float sg = __frcp_rn(1.f + __expf(-v));
       float o;
-      if (j == 0) o = (sg * 2.f + ((float)x - 0.5f)) * p.det_stride;
-      else if (j == 1) o = (sg * 2.f + ((float)y - 0.5f)) * p.det_stride;
+      if (j == 0) o = fmaf(sg, s2, gx);
+      else if (j == 1) o = fmaf(sg, s2, gy);
       else if (j == 2) o = (sg * 2.f) * (sg * 2.f) * (__ldg(p.det_anchors + a * 2) * p.det_stride);
       else if (j == 3) o = (sg * 2.f) * (sg * 2.f) * (__ldg(p.det_anchors + a * 2 + 1) * p.det_stride);
       else o = sg;
       z[a * a_step + j] = o;
-      if (++j == no) { j = 0; ++a; }
+      if (NO == 0 && ++jr == no) { jr = 0; ++ar; }
     }
   }
 }
@@ -450,7 +455,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
           }
         }
       } else if (p.det_z != nullptr) {
-        if (part == 0) epilogue_detect(p, trow, valid, pix, s_shift);
+        if (part == 0) {
+          if (p.det_no == 6) epilogue_detect<6>(p, trow, valid, pix, s_shift);
+          else epilogue_detect<0>(p, trow, valid, pix, s_shift);
+        }
       } else
       switch (p.act) {  // activation resolved once per tile: the column loop is branch-free
         case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, n0, s_scale, s_shift, cb, cs); break;

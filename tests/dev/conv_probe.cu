@@ -40,7 +40,16 @@ int main(int argc, char** argv) {
   for (int rep = 0; rep < 6; ++rep) {
     cudaMemsetAsync(scrub, rep, 256 << 20);
     cudaEventRecord(e0);
-    if (ly_conv_fwd(&d, nullptr)) { printf("error: %s\n", ly_last_error()); return 1; }
+    int rc_;
+    if (getenv("PROBE_DETECT")) {   // Detect head: na = 3, no = Cout / 3, outputs raw + z
+      static float *raw_ = nullptr, *z_ = nullptr, *anc_ = nullptr;
+      if (!raw_) { cudaMalloc(&raw_, opix * d.Cout * 4); cudaMalloc(&z_, opix * d.Cout * 4); cudaMalloc(&anc_, 64); cudaMemset(anc_, 0, 64); }
+      rc_ = ly_detect_head_infer(d.src[0], d.src_ld[0], d.N, d.H, d.W, d.src_c[0], d.w_packed, sc, 3, d.Cout / 3, 8.f, anc_, getenv("PROBE_NORAW") ? nullptr : raw_, z_,
+                                 (long)3 * d.H * d.W, 0, nullptr);
+    } else {
+      rc_ = ly_conv_fwd(&d, nullptr);
+    }
+    if (rc_) { printf("error: %s\n", ly_last_error()); return 1; }
     cudaEventRecord(e1);
     if (cudaDeviceSynchronize() != cudaSuccess) { printf("kernel failed\n"); return 1; }
     if (rep > 0) cudaEventElapsedTime(&times[rep - 1], e0, e1);
