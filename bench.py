@@ -211,7 +211,7 @@ def train_bench(args, warm, rank, local, world, dev):
         if args.profile_kernels:
             for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0]):
                 sys.stderr.write(f"[bench] {k:28s} {v[1]:4d} calls {v[0]:9.3f} ms {100 * v[0] / tot_ms:5.1f}%\n")
-        print(json.dumps({
+        _emit(json.dumps({
             "metric": "LEAD-YOLO images/sec @640", "value": imgs / (ms_total / 1e3), "unit": "images/s",
             "n_gpus": world, "steps": args.steps, "warmup": warm, "ms_per_step": ms_total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -230,6 +230,9 @@ def train_bench(args, warm, rank, local, world, dev):
 
 
 def main():
+    global _REAL_STDOUT
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -251,7 +254,7 @@ def main():
             return
         sample = 4
         ips, ms, cores = cpu_reference_run(args.steps, min(warm, 3), sample)
-        print(json.dumps({
+        _emit(json.dumps({
             "impl": "reference", "metric": "LEAD-YOLO images/sec @640", "value": ips, "unit": "images/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": min(warm, 3), "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -434,10 +437,24 @@ def main():
         except Exception as e:  # noqa: BLE001
             line["cpu_baseline"] = {"value": None, "unit": "images/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": f"failed: {e}"}
-    print(json.dumps(line))
+    _emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
+
+def _emit(*a, **k):
+    """print() onto the ORIGINAL stdout: everything else a rank writes to fd 1 (NCCL prints its version there) goes to
+    stderr, so stdout carries exactly the one JSON line the contract asks for."""
+    sys.stdout.flush()
+    if _REAL_STDOUT != 1:
+        os.dup2(_REAL_STDOUT, 1)
+    print(*a, **k)
+    sys.stdout.flush()
+    if _REAL_STDOUT != 1:
+        os.dup2(2, 1)
+
+
+_REAL_STDOUT = 1
 
 if __name__ == "__main__":
     main()
