@@ -338,7 +338,7 @@ def main():
         # ---- end to end through the public serving call (lead_yolo_b200.engine.InferenceEngine): pinned host uint8
         # batch in, decoded predictions (B,25200,6) fp32 back on the host, every step; copies overlap the replay
         from lead_yolo_b200.engine import InferenceEngine
-        eng = InferenceEngine(model, args.batch, IMG, slots=2, device=dev)
+        eng = InferenceEngine(model, args.batch, IMG, slots=int(os.environ.get("LY_ENGINE_SLOTS", "2")), device=dev)
         out_host = eng.host_out[0]
 
         def e2e_loop(k):
