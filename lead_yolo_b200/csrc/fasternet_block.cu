@@ -83,6 +83,7 @@ __global__ void __launch_bounds__(320) fasternet_block_kernel(const __grid_const
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t w_bar, x_full[2], x_free[2], taps_full[2], u_full[2], v_ready, y_full, y_free;
   __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float s_sc[128], s_sh[128];   // folded BN of the hidden layer (2C <= 128 values)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t raw = smem_u32(smem_raw);
@@ -106,6 +107,10 @@ __global__ void __launch_bounds__(320) fasternet_block_kernel(const __grid_const
   }
   // the hidden tile's K padding (columns >= 2C of its last 64-wide chunk) is zeroed once and never written again
   for (int i = threadIdx.x; i < p.v_chunks * kXBytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(sV)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < 128; i += blockDim.x) {
+    s_sc[i] = i < p.C2 ? p.scale[i] : 0.f;
+    s_sh[i] = i < p.C2 ? p.shift[i] : 0.f;
+  }
   fence_proxy_async_smem();
   if (warp == 2) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
   tc_fence_before_sync();
@@ -207,25 +212,27 @@ __global__ void __launch_bounds__(320) fasternet_block_kernel(const __grid_const
       // MMA lane issues phase B(i-1) before phase A(i+1)... but not before A(i); wait for y_full(i-1) explicitly.
       if (i > 0) FB_WAIT(1, &y_full, (uint32_t)(i - 1) & 1u);
       const uint32_t tm_u = tmem + (uint32_t)((i & 1) * p.C2);
-      for (int c0 = 0; c0 < p.C2; c0 += 16) {      // columns >= C2 of the last K chunk were zeroed once at start
-        uint32_t acc[16];
-        tmem_ld16(tm_u + lane_addr + (uint32_t)c0, acc);
+      // columns >= C2 of the last K chunk were zeroed once at start.  Up to three 16-column loads per TMEM round trip;
+      // scale / shift come from shared memory (staged once per CTA)
+      for (int cb = 0; cb < p.C2; cb += 48) {
+        uint32_t acc[3][16];
+        tmem_ld16(tm_u + lane_addr + (uint32_t)cb, acc[0]);
+        if (cb + 16 < p.C2) tmem_ld16(tm_u + lane_addr + (uint32_t)(cb + 16), acc[1]);
+        if (cb + 32 < p.C2) tmem_ld16(tm_u + lane_addr + (uint32_t)(cb + 32), acc[2]);
         tmem_ld_wait();
 #pragma unroll
-        for (int g = 0; g < 2; ++g) {
-          const int c = c0 + g * 8;
+        for (int g = 0; g < 6; ++g) {
+          const int c = cb + g * 8;
           if (c < p.C2) {
-            const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + c));
-            const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + c + 4));
-            const float4 h0 = __ldg(reinterpret_cast<const float4*>(p.shift + c));
-            const float4 h1 = __ldg(reinterpret_cast<const float4*>(p.shift + c + 4));
+            const float4 s0 = *reinterpret_cast<const float4*>(s_sc + c), s1 = *reinterpret_cast<const float4*>(s_sc + c + 4);
+            const float4 h0 = *reinterpret_cast<const float4*>(s_sh + c), h1 = *reinterpret_cast<const float4*>(s_sh + c + 4);
             const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
             const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
             uint32_t w[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {   // relu + convert + pack in one instruction
-              const float lo = fmaf(__uint_as_float(acc[g * 8 + 2 * j]), sc[2 * j], sh[2 * j]);
-              const float hi = fmaf(__uint_as_float(acc[g * 8 + 2 * j + 1]), sc[2 * j + 1], sh[2 * j + 1]);
+              const float lo = fmaf(__uint_as_float(acc[g >> 1][(g & 1) * 8 + 2 * j]), sc[2 * j], sh[2 * j]);
+              const float hi = fmaf(__uint_as_float(acc[g >> 1][(g & 1) * 8 + 2 * j + 1]), sc[2 * j + 1], sh[2 * j + 1]);
               asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(w[j]) : "f"(hi), "f"(lo));
             }
             const int kc = c >> 6, ch = (c >> 3) & 7;
