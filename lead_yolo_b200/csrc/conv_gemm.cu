@@ -47,7 +47,8 @@ constexpr int kAStage = 128 * 128;  // 128 rows x 128 B
 struct KEntry {
   int16_t src;  // which A tensor map
   int16_t c0;   // channel coordinate of the chunk
-  int8_t dw, dh, tz, pad_;
+  int8_t dw, dh, tz;
+  int8_t nk16;  // K = 16 slices of this chunk that hold channels (the rest of the 64-wide box is zero fill: not multiplied)
   int16_t kb, kstep;  // halo mode: weight chunk of tap 0 and the chunk distance between taps
 };
 
@@ -393,9 +394,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
               const uint64_t adesc = ahalo + (uint64_t)((uint32_t)(ty * p.halo + tx_) * 8u);   // 128-byte rows
               const uint64_t bdesc = b_desc0 + (uint64_t)((uint32_t)(e.kb + t * e.kstep) * b_step);
               umma_bf16(tmem_d, adesc, bdesc, idesc, (uint32_t)((k | t) != 0));
-              umma_bf16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
-              umma_bf16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
-              umma_bf16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+              if (e.nk16 > 1) umma_bf16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
+              if (e.nk16 > 2) umma_bf16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+              if (e.nk16 > 3) umma_bf16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
             }
           } else
           for (int j = 0; j < kg; ++j) {
@@ -687,7 +688,8 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
       const int nch = ceil_div(ceff, 64);
       for (int c = 0; c < nch; ++c) {
         KEntry e;
-        e.src = (int16_t)s; e.c0 = (int16_t)(c * 64); e.dw = -1; e.dh = -1; e.tz = 0; e.pad_ = 0;
+        e.src = (int16_t)s; e.c0 = (int16_t)(c * 64); e.dw = -1; e.dh = -1; e.tz = 0;
+        e.nk16 = (int8_t)ceil_div(ceff - c * 64 < 64 ? ceff - c * 64 : 64, 16);
         e.kb = (int16_t)(kb_base + c); e.kstep = (int16_t)nch;
         p.sched[it++] = e;
       }
@@ -699,7 +701,7 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
         KEntry e;
         e.src = (int16_t)s;
         e.c0 = (int16_t)c0;
-        e.pad_ = 0;
+        e.nk16 = 4;
         e.kb = 0; e.kstep = 0;
         if (g.patch) {
           e.dw = 0; e.dh = 0; e.tz = (int8_t)t;
