@@ -1,11 +1,12 @@
 // Implicit-GEMM convolution on tcgen05 tensor cores (sm_100a).
 //
-//   persistent grid (one CTA per SM, static tile striding);  block = 320 threads:
-//     warp 0      TMA producer   (A box: 64 channels x Wt x Ht pixels of one tap; B box: 64 x BN weights)
-//     warp 1      MMA issuer     (one lane issues 4 x tcgen05.mma K=16 per 64-wide K chunk)
-//     warps 2..9  epilogue       (TMEM -> registers -> scale/shift/activation/residual -> global); the accumulator
-//                                is double-buffered in TMEM so tile i drains while tile i+1 is being multiplied
-//   A and B tiles live in 128B-swizzled shared memory, accumulators (128 x BN fp32) in TMEM.
+//   persistent grid (one CTA per SM, static tile striding);  block = 576 threads:
+//     warp 0       TMA producer, one lane (A boxes: 64 channels x Wt x Ht pixels of one tap, or one halo box per chunk
+//                  for 3x3 convolutions with resident weights; B boxes: 64 x BN weights unless resident)
+//     warp 1       MMA issuer, one lane (4 x tcgen05.mma K=16 per 64-wide K chunk, one commit per ring stage)
+//     warps 2..17  epilogue: four groups of four warps (TMEM lane quadrant = warp % 4), each group drains a different
+//                  tile: TMEM -> registers -> scale/shift/activation/residual -> TMA store (flat bf16) or global stores
+//   A and B tiles live in 128B-swizzled shared memory, up to four accumulators (128 x BN fp32) in TMEM.
 //   Zero padding of a 3x3 convolution and ragged channel counts are TMA out-of-bounds zero fill.
 #include <stdlib.h>
 #include <string.h>
