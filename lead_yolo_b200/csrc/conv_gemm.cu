@@ -67,6 +67,8 @@ struct alignas(64) ConvGemmParams {
   int kgroup;      // K chunks per ring stage: one mbarrier phase and ONE tcgen05.commit (~340 cycles of the issuing lane,
                    // tests/dev/mma_issue.cu) cover kgroup x 4 MMAs
   int tma_store;   // epilogue stages 32-row x 64-column slabs in shared memory and stores them with TMA
+  int det_bulk;    // Detect epilogue stages raw / z rows in the warp's slab and stores them with bulk copies
+  int slab_bytes;  // shared-memory slab per epilogue warp (0: none)
   int b_resident;  // all weight chunks stay in shared memory for the whole kernel (single N tile, small K*N)
   int act, out_fp32, vec_ok, res_vec_ok;
   uint32_t a_bytes;
@@ -217,6 +219,67 @@ __device__ __forceinline__ void epilogue_detect(const ConvGemmParams& p, uint32_
   }
 }
 
+// Detect epilogue for na = 3, no = 6 when a warp's 32 pixels are one contiguous run of an image (plane % 32 == 0): the
+// lanes lay raw and z out in shared memory exactly as they sit in global memory ([anchor][pixel][6] floats, 768 B per
+// anchor) and six lanes issue one bulk copy each.  The scalar version's 36 four-byte stores per lane touch 24 sectors
+// per instruction and kept L1TEX busy for most of the kernel.
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void epilogue_detect_bulk(const ConvGemmParams& p, uint32_t trow, bool valid, long pix,
+                                                     const float* s_shift, uint8_t* slab, int lane) {
+  uint32_t acc[32];
+  {
+    uint32_t lo[16], hi[16];
+    tmem_ld16(trow, lo);
+    tmem_ld16(trow + 16u, hi);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { acc[j] = lo[j]; acc[16 + j] = hi[j]; }
+  }
+  if (lane < 6) tma_store_wait_read<0>();   // the previous tile's rows have left the slab
+  __syncwarp();
+  if (!valid) return;                       // warp-uniform: the pixel count is a multiple of 32
+  const int ny = p.det_ny, nx = p.det_nx;
+  const long plane = (long)ny * nx;
+  const long n = pix / plane;
+  const int rem = (int)(pix - n * plane);
+  const int y = rem / nx, x = rem - y * nx;
+  const float gx = ((float)x - 0.5f) * p.det_stride, gy = ((float)y - 0.5f) * p.det_stride, s2 = 2.f * p.det_stride;
+  float* zs = reinterpret_cast<float*>(slab) + lane * 6;
+  float* rs = zs + 3 * 32 * 6;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    float v[6], o[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      v[j] = __uint_as_float(acc[a * 6 + j]) + s_shift[a * 6 + j];
+      o[j] = __frcp_rn(1.f + __expf(-v[j]));
+    }
+    o[0] = fmaf(o[0], s2, gx);
+    o[1] = fmaf(o[1], s2, gy);
+    o[2] = (o[2] * 2.f) * (o[2] * 2.f) * (__ldg(p.det_anchors + a * 2) * p.det_stride);
+    o[3] = (o[3] * 2.f) * (o[3] * 2.f) * (__ldg(p.det_anchors + a * 2 + 1) * p.det_stride);
+#pragma unroll
+    for (int j = 0; j < 6; j += 2) {
+      *reinterpret_cast<float2*>(rs + a * 192 + j) = make_float2(v[j], v[j + 1]);
+      *reinterpret_cast<float2*>(zs + a * 192 + j) = make_float2(o[j], o[j + 1]);
+    }
+  }
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane < 6) {
+    const int a = lane % 3;
+    const long rem0 = rem - lane;   // first pixel of this warp inside its image
+    const float* src = reinterpret_cast<const float*>(slab) + lane * 192;   // lanes 0-2: z, lanes 3-5: raw
+    float* dst = lane < 3 ? p.det_z + (n * p.det_rows_total + p.det_row_off + a * plane + rem0) * 6
+                          : p.det_raw + ((n * 3 + a) * plane + rem0) * 6;
+    bulk_store(dst, src, 768u);
+    tma_store_commit();
+  }
+}
+
 // TMA-store epilogue (flat 1x1, bf16, no residual scatter): each warp converts its 32 rows x 64 columns into a
 // 128B-swizzled shared-memory slab and one lane issues a bulk tensor store — full 128 B lines reach L2 instead of
 // 16 B pieces of 32 B sectors.
@@ -298,7 +361,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   uint8_t* sA = smem;
   uint8_t* sB = smem + p.stages * p.kgroup * p.a_stage;
   const int b_stage = p.BN * 128;
-  // 4 KB store slab per epilogue warp, after the A/B buffers (1024-byte aligned: every piece above is)
+  // store slab per epilogue warp, after the A/B buffers (1024-byte aligned: every piece above is)
   uint8_t* slabs = sB + (p.b_resident ? p.num_kb : p.stages * p.kgroup) * b_stage;
 
   if (warp == 0 && lane == 0) {
@@ -445,7 +508,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       const int cb = part * 16, cs = nparts * 16;
       if (p.tma_store) {
         // flat rows: tile row r <-> pixel w; the whole tile's columns go through this warp's slab
-        uint8_t* slab = slabs + (warp - 2) * 4096;
+        uint8_t* slab = slabs + (warp - 2) * p.slab_bytes;
         const int row0 = tw * p.Wt + q * 32;
         if (part == 0) {
           switch (p.act) {
@@ -458,7 +521,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         }
       } else if (p.det_z != nullptr) {
         if (part == 0) {
-          if (p.det_no == 6) epilogue_detect<6>(p, trow, valid, pix, s_shift);
+          if (p.det_bulk) epilogue_detect_bulk(p, trow, valid, pix, s_shift, slabs + (warp - 2) * p.slab_bytes, lane);
+          else if (p.det_no == 6) epilogue_detect<6>(p, trow, valid, pix, s_shift);
           else epilogue_detect<0>(p, trow, valid, pix, s_shift);
         }
       } else
@@ -473,7 +537,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
     }
-    if (p.tma_store && lane == 0) tma_store_wait_all<0>();   // stores complete before the CTA retires
+    if ((p.tma_store && lane == 0) || (p.det_bulk && lane < 6)) tma_store_wait_all<0>();   // stores land before the CTA retires
     if (warp == 2) { CG_DBG_FLUSH(5, 1) }
     if (warp == 6) { CG_DBG_FLUSH(7, 1) }
   }
@@ -743,6 +807,15 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   // TMA-store epilogue: flat rows, bf16, dense-enough output, no scatter; needs nparts == 1 (one group per tile)
   p.tma_store = (flat_rows && d->patch_k == 0 && !d->out_fp32 && p.vec_ok && p.nbuf == kEpiGroups &&
                  (d->residual == nullptr || p.res_vec_ok)) ? 1 : 0;
+  if (det != nullptr) {
+    // bulk-copy epilogue: na = 3, no = 6, every warp's 32 pixels inside one image, 16-byte aligned runs
+    const long plane = (long)d->H * d->W;
+    p.tma_store = 0;
+    p.det_bulk = (flat_rows && det->na == 3 && det->no == 6 && det->raw != nullptr && plane % 32 == 0 &&
+                  det->rows_total % 2 == 0 && det->row_off % 2 == 0 && reinterpret_cast<uintptr_t>(det->z) % 16 == 0 &&
+                  reinterpret_cast<uintptr_t>(det->raw) % 16 == 0 && p.nbuf == kEpiGroups) ? 1 : 0;
+  }
+  p.slab_bytes = p.tma_store ? 4096 : (p.det_bulk ? 2 * 3 * 32 * 6 * 4 : 0);
   if (p.tma_store) {
     const uint64_t M = (uint64_t)d->N * d->H * d->W;
     uint64_t dims[2] = {(uint64_t)d->Cout, M};
@@ -751,7 +824,7 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
     rc = tmap_encode_bf16(&p.o_map, d->out, 2, dims, str, box);
     if (rc != LY_OK) return rc;
   }
-  const int budget = 196 * 1024 - (p.tma_store ? kEpiGroups * 4 * 4096 : 0);
+  const int budget = 196 * 1024 - kEpiGroups * 4 * p.slab_bytes;
   const long b_all = (long)num_k * p.BN * 128;
   p.b_resident = (ny == 1 && b_all <= 100 * 1024) ? 1 : 0;
   // K chunks per ring stage: the largest divisor of num_k (<= 4) that still leaves a ring of >= 3 stages (>= 2 when
@@ -768,7 +841,7 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   p.stages = (int)(ring_budget / (p.kgroup * chunk_bytes));
   if (p.stages > kMaxStages) p.stages = kMaxStages;
   LY_REQUIRE(p.stages >= 2, "shared-memory ring too small (BN=%d)", p.BN);
-  const size_t smem_bytes = (p.tma_store ? (size_t)kEpiGroups * 4 * 4096 : 0) + (p.b_resident ? (size_t)b_all : 0) +
+  const size_t smem_bytes = (size_t)kEpiGroups * 4 * p.slab_bytes + (p.b_resident ? (size_t)b_all : 0) +
                             (size_t)p.stages * p.kgroup * chunk_bytes + 1024;
 
   // ---- epilogue
@@ -791,7 +864,6 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
     p.det_na = det->na; p.det_no = det->no; p.det_ny = d->H; p.det_nx = d->W;
     p.det_stride = det->stride;
     p.det_anchors = det->anchors;
-    p.tma_store = 0;
   }
 
   rc = set_smem_attr_once();
