@@ -67,6 +67,7 @@ struct alignas(64) ConvGemmParams {
   int kgroup;      // K chunks per ring stage: one mbarrier phase and ONE tcgen05.commit (~340 cycles of the issuing lane,
                    // tests/dev/mma_issue.cu) cover kgroup x 4 MMAs
   int tma_store;   // epilogue stages 32-row x 64-column slabs in shared memory and stores them with TMA
+  int vec32_ok;    // bf16 output rows 32-byte aligned, no patch scatter: 16 columns go out as one 32-byte store
   int det_bulk;    // Detect epilogue stages raw / z rows in the warp's slab and stores them with bulk copies
   int slab_bytes;  // shared-memory slab per epilogue warp (0: none)
   int b_resident;  // all weight chunks stay in shared memory for the whole kernel (single N tile, small K*N)
@@ -102,6 +103,12 @@ __device__ __forceinline__ float ssa(uint32_t acc, float sc, float sh) {
   return act_apply_t<ACT>(h);
 }
 
+__device__ __forceinline__ void st_global_v8(void* ptr, const uint32_t (&w)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+               "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+
 // One epilogue thread = one output pixel (TMEM lane).  Columns [c_begin, BN) are drained 16 at a time, stride c_step.
 template <int ACT>
 __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t trow, bool valid, int n, int h, int w,
@@ -114,6 +121,33 @@ __device__ __forceinline__ void epilogue_cols(const ConvGemmParams& p, uint32_t 
     tmem_ld16(trow + (uint32_t)c0, acc);
     tmem_ld_wait();
     if (!valid) continue;
+    if (p.vec32_ok && c0 + 16 <= p.BN && n0 + c0 + 16 <= p.Cout) {
+      // 16 columns = one full 32-byte sector per lane: half the L1TEX sector operations of two 16-byte stores
+      const int c = n0 + c0;
+      uint32_t w[8];
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        const float4 sc0 = *reinterpret_cast<const float4*>(s_scale + c + g * 8);
+        const float4 sc1 = *reinterpret_cast<const float4*>(s_scale + c + g * 8 + 4);
+        const float4 sh0 = *reinterpret_cast<const float4*>(s_shift + c + g * 8);
+        const float4 sh1 = *reinterpret_cast<const float4*>(s_shift + c + g * 8 + 4);
+        const float sc[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
+        const float sh[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = ssa<ACT>(acc[g * 8 + j], sc[j], sh[j]);
+        if (p.residual != nullptr) {
+          float rr[8];
+          unpack8(*reinterpret_cast<const uint4*>(p.residual + pix * p.res_ld + c + g * 8), rr);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] += rr[j];
+        }
+        const uint4 pk = pack8(v);
+        w[g * 4 + 0] = pk.x; w[g * 4 + 1] = pk.y; w[g * 4 + 2] = pk.z; w[g * 4 + 3] = pk.w;
+      }
+      st_global_v8(reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.out_ld + c, w);
+      continue;
+    }
 #pragma unroll
     for (int g = 0; g < 2; ++g) {
       const int cl = c0 + g * 8;       // column inside the tile
@@ -804,7 +838,10 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   p.vec_ok = d->out_fp32 ? ((oa % 16 == 0) && (d->out_ld % 4 == 0)) : ((oa % 16 == 0) && (d->out_ld % 8 == 0));
   p.res_vec_ok = d->residual != nullptr && (reinterpret_cast<uintptr_t>(d->residual) % 16 == 0) &&
                  (d->res_ld % 8 == 0);
-  // TMA-store epilogue: flat rows, bf16, dense-enough output, no scatter; needs nparts == 1 (one group per tile)
+  p.vec32_ok = (!d->out_fp32 && d->patch_k == 0 && oa % 32 == 0 && d->out_ld % 16 == 0 &&
+                (d->residual == nullptr || p.res_vec_ok)) ? 1 : 0;
+  // TMA-store epilogue: flat rows, bf16, dense-enough output, no scatter; needs nparts == 1 (one group per tile).
+  // (Wide tiles, two groups per accumulator: the 64 KB of slabs cost ring stages and the layers got slower — measured.)
   p.tma_store = (flat_rows && d->patch_k == 0 && !d->out_fp32 && p.vec_ok && p.nbuf == kEpiGroups &&
                  (d->residual == nullptr || p.res_vec_ok)) ? 1 : 0;
   if (det != nullptr) {
