@@ -18,7 +18,8 @@
 //   warps 6-9  output group: copies its row of the x box to registers (the box is then released), adds it to y (TMEM)
 //            and stores; the two groups work on different phases of consecutive tiles at the same time
 // Two CTAs per SM when the buffers fit (C = 24), so one CTA's epilogues overlap the other's MMAs.
-// Supported: C in {24, 40} (the HBM-bound FasterNet stages of LEAD-YOLO); other widths use the per-layer kernels.
+// Supported by this kernel: C in {24, 40} (the HBM-bound FasterNet stages of LEAD-YOLO); C = 80 has its own kernel below;
+// other widths use the per-layer kernels.
 #include <string.h>
 
 #include "ly_common.cuh"
@@ -329,20 +330,295 @@ static int encode_sw32(CUtensorMap* out, const void* base, const uint64_t* dims,
   return LY_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// C = 80 (FasterNet stage 3: 40 x 40 maps at 640 input).  Same two-phase scheme with everything compile-time; the
+// per-layer path spent three launches of ~6 tiles per SM on this block, most of it start-up and hand-off latency.
+// Cp = 20 channels feed the 3x3, so the folded taps are two K=16 slices; channels 64..79 of x are a third K=16 (SW32)
+// box.  Shared memory is the limit (weights 145 KB + hidden tile 48 KB): inputs are single buffered, pitch is fixed at
+// P = 16 (tiles of 14 x 8 pixels), and the output group takes its residual from global memory (an L2 hit) instead of
+// keeping the x box alive.
+// ---------------------------------------------------------------------------------------------
+namespace f80 {
+constexpr int C = 80, C2 = 160, N2 = 80, P = 16, Wt = 14, Ht = 8;
+constexpr int kOffW2 = 160 * 128;                  // W1x chunk 0 [160][64] SW128
+constexpr int kOffW1b = kOffW2 + 3 * N2 * 128;     // W2: 3 chunks [80][64] SW128
+constexpr int kOffWc = kOffW1b + 160 * 32;         // W1x channels 64..79 [160][16] SW32
+constexpr int kWBytes = kOffWc + 18 * 160 * 32;    // Wc [slice][tap][160][16] SW32
+constexpr int kHalo = 5632;                        // 160 box rows x 32 B + the two rows a shifted read runs past
+constexpr int kSV = kXBytes;                       // after sX0
+constexpr int kSW = kSV + 3 * kXBytes;
+constexpr int kSX1 = kSW + kWBytes;
+constexpr int kSHalo = kSX1 + 128 * 32;
+constexpr int kSmem = kSHalo + 2 * kHalo + 1024;
+constexpr uint32_t kTxBytes = 64 * P * Ht * 2 + 16 * P * Ht * 2 + 2 * 16 * P * (Ht + 2) * 2;
+}  // namespace f80
+
+struct alignas(64) Fnb80Params {
+  CUtensorMap x_map;     // (C, W, 1, H, N) box (64, P, 1, Ht, 1)   SW128
+  CUtensorMap x1_map;    // same tensor, box (16, P, 1, Ht, 1)      SW32
+  CUtensorMap tap_map;   // same tensor, box (16, P, 1, Ht+2, 1)    SW32
+  const __nv_bfloat16* x;
+  __nv_bfloat16* y;
+  const uint8_t* wimg;
+  const float* scale;
+  const float* shift;
+  int H, W, tiles_w, tiles_h, tiles;
+};
+
+__global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_constant__ Fnb80Params p) {
+  using namespace f80;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t w_bar, in_full, u_full[2], v_ready, y_full, y_free;
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float s_sc[C2], s_sh[C2];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sX0 = smem;
+  uint8_t* sV = smem + kSV;
+  uint8_t* sW = smem + kSW;
+  uint8_t* sX1 = smem + kSX1;
+  uint8_t* sHalo = smem + kSHalo;
+
+  if (warp == 1 && lane == 0) {
+    mbar_init(&w_bar, 1);
+    mbar_init(&in_full, 1);
+    mbar_init(&u_full[0], 1);
+    mbar_init(&u_full[1], 1);
+    mbar_init(&v_ready, 128);
+    mbar_init(&y_full, 1);
+    mbar_init(&y_free, 128);
+    fence_mbar_init();
+  }
+  // K padding of the hidden tile (columns 160..191 of chunk 2) and the halo overrun rows: zeroed once
+  for (int i = threadIdx.x; i < 3 * kXBytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(sV)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < 2 * kHalo / 16; i += blockDim.x) reinterpret_cast<uint4*>(sHalo)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < C2; i += blockDim.x) { s_sc[i] = p.scale[i]; s_sh[i] = p.shift[i]; }
+  fence_proxy_async_smem();
+  if (warp == 2) tmem_alloc(&tmem_base_s, 512u);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem = tmem_base_s;
+  const uint32_t tm_y = tmem + 2u * C2;
+
+  const int mine = ((int)blockIdx.x < p.tiles) ? (p.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int tiles_img = p.tiles_w * p.tiles_h;
+
+  if (warp == 0) {
+    if (lane == 0 && mine > 0) {
+      tma_prefetch_desc(&p.x_map);
+      tma_prefetch_desc(&p.x1_map);
+      tma_prefetch_desc(&p.tap_map);
+      mbar_arrive_expect_tx(&w_bar, (uint32_t)kWBytes);
+      bulk_copy_g2s(sW, p.wimg, (uint32_t)kWBytes, &w_bar);
+      for (int i = 0; i < mine; ++i) {
+        const int t = (int)blockIdx.x + i * (int)gridDim.x;
+        const int n = t / tiles_img, tr = t - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+        const int w0 = tw * Wt, h0 = th * Ht;
+        // single input buffer: free once the phase-A MMAs of the previous tile have completed
+        if (i > 0) mbar_wait(&u_full[(i - 1) & 1], ((uint32_t)(i - 1) >> 1) & 1u);
+        mbar_arrive_expect_tx(&in_full, kTxBytes);
+        tma_load_5d(sX0, &p.x_map, &in_full, 0, w0, 0, h0, n);
+        tma_load_5d(sHalo, &p.tap_map, &in_full, 0, w0 - 1, 0, h0 - 1, n);
+        tma_load_5d(sHalo + kHalo, &p.tap_map, &in_full, 16, w0 - 1, 0, h0 - 1, n);
+        tma_load_5d(sX1, &p.x1_map, &in_full, 64, w0, 0, h0, n);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && mine > 0) {
+      const uint32_t id1 = umma_idesc_bf16_f32(128, C2, 0, 0);
+      const uint32_t id2 = umma_idesc_bf16_f32(128, N2, 0, 0);
+      const uint64_t x0_d = umma_smem_desc_sw128(smem_u32(sX0), 16, 1024);
+      const uint64_t w1a_d = umma_smem_desc_sw128(smem_u32(sW), 16, 1024);
+      const uint64_t w2_d = umma_smem_desc_sw128(smem_u32(sW + kOffW2), 16, 1024);
+      const uint64_t x1_d = desc_sw32(smem_u32(sX1));
+      const uint64_t w1b_d = desc_sw32(smem_u32(sW + kOffW1b));
+      const uint64_t wc_d = desc_sw32(smem_u32(sW + kOffWc));
+      const uint64_t halo_d = desc_sw32(smem_u32(sHalo));
+      const uint64_t v_d = umma_smem_desc_sw128(smem_u32(sV), 16, 1024);
+      mbar_wait(&w_bar, 0);
+      auto phase_a = [&](int i) {
+        const uint32_t tm_u = tmem + (uint32_t)((i & 1) * C2);
+        mbar_wait(&in_full, (uint32_t)i & 1u);
+        tc_fence_after_sync();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_bf16(tm_u, x0_d + (uint64_t)(k * 2), w1a_d + (uint64_t)(k * 2), id1, (uint32_t)(k != 0));
+        umma_bf16(tm_u, x1_d, w1b_d, id1, 1u);
+#pragma unroll
+        for (int sl = 0; sl < 2; ++sl)
+#pragma unroll
+          for (int k = 0; k < 9; ++k)
+            umma_bf16(tm_u, halo_d + (uint64_t)(sl * (kHalo >> 4) + ((k / 3) * P + (k % 3)) * 2),
+                      wc_d + (uint64_t)((sl * 9 + k) * ((C2 * 32) >> 4)), id1, 1u);
+        umma_commit(&u_full[i & 1]);
+      };
+      phase_a(0);
+      for (int i = 0; i < mine; ++i) {
+        const uint32_t ph = (uint32_t)i & 1u;
+        if (i + 1 < mine) phase_a(i + 1);
+        mbar_wait(&v_ready, ph);
+        mbar_wait(&y_free, ph ^ 1u);
+        tc_fence_after_sync();
+#pragma unroll
+        for (int k = 0; k < C2 / 16; ++k)
+          umma_bf16(tm_y, v_d + (uint64_t)((k >> 2) * (kXBytes >> 4) + (k & 3) * 2),
+                    w2_d + (uint64_t)((k >> 2) * ((N2 * 128) >> 4) + (k & 3) * 2), id2, (uint32_t)(k != 0));
+        umma_commit(&y_full);
+      }
+    }
+  } else if (warp < 6) {
+    // hidden group: v = relu(scale*u + shift) -> bf16 -> SW128 A operand of phase B
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    for (int i = 0; i < mine; ++i) {
+      mbar_wait(&u_full[i & 1], ((uint32_t)i >> 1) & 1u);
+      tc_fence_after_sync();
+      if (i > 0) mbar_wait(&y_full, (uint32_t)(i - 1) & 1u);   // phase B of the previous tile has read sV
+      const uint32_t tm_u = tmem + (uint32_t)((i & 1) * C2) + lane_addr;
+#pragma unroll
+      for (int cb = 0; cb < C2; cb += 32) {
+        uint32_t acc[2][16];
+        tmem_ld16(tm_u + (uint32_t)cb, acc[0]);
+        tmem_ld16(tm_u + (uint32_t)(cb + 16), acc[1]);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int c = cb + g * 8;
+          const float4 s0 = *reinterpret_cast<const float4*>(s_sc + c), s1 = *reinterpret_cast<const float4*>(s_sc + c + 4);
+          const float4 h0 = *reinterpret_cast<const float4*>(s_sh + c), h1 = *reinterpret_cast<const float4*>(s_sh + c + 4);
+          const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+          const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+          uint32_t w[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float lo = fmaf(__uint_as_float(acc[g >> 1][(g & 1) * 8 + 2 * j]), sc[2 * j], sh[2 * j]);
+            const float hi = fmaf(__uint_as_float(acc[g >> 1][(g & 1) * 8 + 2 * j + 1]), sc[2 * j + 1], sh[2 * j + 1]);
+            asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(w[j]) : "f"(hi), "f"(lo));
+          }
+          const int kc = c >> 6, ch = (c >> 3) & 7;
+          *reinterpret_cast<uint4*>(sV + kc * kXBytes + r * 128 + ((ch ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+      tc_fence_before_sync();
+      fence_proxy_async_smem();
+      mbar_arrive(&v_ready);
+    }
+  } else {
+    // output group: y = x + W2 v
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    const int hh = r / P, ww = r - hh * P;
+    for (int i = 0; i < mine; ++i) {
+      const uint32_t ph = (uint32_t)i & 1u;
+      const int t = (int)blockIdx.x + i * (int)gridDim.x;
+      const int n = t / tiles_img, tr = t - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+      const int h = th * Ht + hh, w = tw * Wt + ww;
+      const bool valid = ww < Wt && h < p.H && w < p.W;
+      const long pix = ((long)n * p.H + h) * p.W + w;
+      uint4 xres[C / 8];
+      if (valid) {
+#pragma unroll
+        for (int k = 0; k < C / 8; ++k) xres[k] = __ldg(reinterpret_cast<const uint4*>(p.x + pix * C) + k);
+      }
+      mbar_wait(&y_full, ph);
+      tc_fence_after_sync();
+#pragma unroll
+      for (int c0 = 0; c0 < N2; c0 += 16) {
+        uint32_t acc[16];
+        tmem_ld16(tm_y + lane_addr + (uint32_t)c0, acc);
+        tmem_ld_wait();
+        if (valid) {
+          uint32_t o[8];
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            float xr[8], v[8];
+            unpack8(xres[(c0 >> 3) + g], xr);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[g * 8 + j]) + xr[j];
+            const uint4 pk = pack8(v);
+            o[g * 4 + 0] = pk.x; o[g * 4 + 1] = pk.y; o[g * 4 + 2] = pk.z; o[g * 4 + 3] = pk.w;
+          }
+          asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p.y + pix * C + c0), "r"(o[0]),
+                       "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7])
+                       : "memory");
+        }
+      }
+      tc_fence_before_sync();
+      mbar_arrive(&y_free);
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512u);
+}
+
 }  // namespace ly
 
 using namespace ly;
 
-// x, y: dense NHWC bf16 [N][H][W][C], C in {24, 40}.  wimg: pre-swizzled weight image built by
+
+static int launch_fnb80(const void* x, void* y, int N, int H, int W, const void* wimg, int w_bytes, int off_w2,
+                        int off_wc, const float* scale, const float* shift, ly_stream_t st) {
+  using namespace f80;
+  LY_REQUIRE(w_bytes == kWBytes && off_w2 == kOffW2 && off_wc == kOffWc,
+             "ly_fasternet_block_infer: C=80 weight image layout mismatch (%d bytes, offsets %d / %d)", w_bytes, off_w2,
+             off_wc);
+  Fnb80Params p;
+  memset(&p, 0, sizeof(p));
+  p.x = (const __nv_bfloat16*)x;
+  p.y = (__nv_bfloat16*)y;
+  p.wimg = (const uint8_t*)wimg;
+  p.scale = scale;
+  p.shift = shift;
+  p.H = H;
+  p.W = W;
+  p.tiles_w = ceil_div(W, Wt);
+  p.tiles_h = ceil_div(H, Ht);
+  p.tiles = p.tiles_w * p.tiles_h * N;
+  uint64_t dims[5] = {(uint64_t)C, (uint64_t)W, 1, (uint64_t)H, (uint64_t)N};
+  uint64_t str[4] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
+  uint32_t box[5] = {64, P, 1, Ht, 1};
+  int rc = tmap_encode_bf16(&p.x_map, x, 5, dims, str, box);
+  if (rc) return rc;
+  uint32_t box1[5] = {16, P, 1, Ht, 1};
+  rc = encode_sw32(&p.x1_map, x, dims, str, box1);
+  if (rc) return rc;
+  uint64_t dims2[5] = {32, (uint64_t)W, 1, (uint64_t)H, (uint64_t)N};   // the taps see channels 0..31 only
+  uint32_t box2[5] = {16, P, 1, Ht + 2, 1};
+  rc = encode_sw32(&p.tap_map, x, dims2, str, box2);
+  if (rc) return rc;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  LY_CUDA(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    LY_CUDA(cudaFuncSetAttribute(fasternet_block80_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    attr_done[dev & 63] = true;
+  }
+  const int sms = device_sm_count();
+  const unsigned grid = (unsigned)(p.tiles < sms ? p.tiles : sms);
+  fasternet_block80_kernel<<<grid, 320, kSmem, (cudaStream_t)st>>>(p);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+// x, y: dense NHWC bf16 [N][H][W][C], C in {24, 40, 80}.  wimg: pre-swizzled weight image built by
 // lead_yolo_b200.packing.fasternet_weight_image (sections W1x | W2 | Wc, offsets passed in).
 extern "C" int ly_fasternet_block_infer(const void* x, void* y, int N, int H, int W, int C, const void* wimg,
                                         int w_bytes, int off_w2, int off_wc, const float* scale, const float* shift,
                                         ly_stream_t st) {
   LY_REQUIRE(x && y && wimg && scale && shift && N > 0 && H > 0 && W > 0, "ly_fasternet_block_infer: bad args");
-  LY_REQUIRE(C == 24 || C == 40, "ly_fasternet_block_infer: C=%d not supported (24 or 40)", C);
+  LY_REQUIRE(C == 24 || C == 40 || C == 80, "ly_fasternet_block_infer: C=%d not supported (24, 40 or 80)", C);
   LY_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0 &&
                  reinterpret_cast<uintptr_t>(wimg) % 16 == 0 && w_bytes % 16 == 0,
              "ly_fasternet_block_infer: alignment");
+  if (C == 80) {
+    LY_REQUIRE(reinterpret_cast<uintptr_t>(y) % 32 == 0, "ly_fasternet_block_infer: y must be 32-byte aligned for C=80");
+    return launch_fnb80(x, y, N, H, W, wimg, w_bytes, off_w2, off_wc, scale, shift, st);
+  }
   FnbParams p;
   memset(&p, 0, sizeof(p));
   p.x = (const __nv_bfloat16*)x;

@@ -331,7 +331,8 @@ class MLPBlock(nn.Module):
         cpp = (cp + 7) // 8 * 8
         w1, bn, act, w2 = self.mlp[0], self.mlp[1], _act_name(self.mlp[2]), self.mlp[3]
         c = x.shape[1]
-        if fast and c in (24, 40) and act == "relu" and ll.pixel_ld(x) == c and x.data_ptr() % 16 == 0:
+        if fast and c in (24, 40, 80) and act == "relu" and ll.pixel_ld(x) == c and x.data_ptr() % 16 == 0 and \
+                (c != 80 or cp == 20):
             # whole block in one kernel (csrc/fasternet_block.cu)
             from .packing import fasternet_weight_image
             img = ops.cached([w1.weight, w2.weight, pc.partial_conv3.weight], ("fnb", c), lambda: fasternet_weight_image(

@@ -105,6 +105,8 @@ def fasternet_weight_image(w1: torch.Tensor, w2: torch.Tensor, wp: torch.Tensor)
     into the first GEMM: Wc_tap = W1[:, :Cp] @ Wp[:, :, tap] (fp32 product, rounded to bf16 once)."""
     c2, c = w1.shape[0], w1.shape[1]
     cp = wp.shape[0]
+    if c == 80:
+        return _fasternet_weight_image80(w1, w2, wp)
     assert cp <= 16 and c <= 64 and c2 % 8 == 0
     n2 = (c + 15) // 16 * 16
     chunks = (c2 + 63) // 64
@@ -123,4 +125,31 @@ def fasternet_weight_image(w1: torch.Tensor, w2: torch.Tensor, wp: torch.Tensor)
     for t in range(9):
         wc = w1m[:, :cp] @ wpf[:, :, t // 3, t % 3]                      # [2C][Cp]
         parts.append(swizzle32(pad(wc, (0, 16 - cp)).to(torch.bfloat16)))
+    return torch.cat(parts).contiguous(), off_w2, off_wc
+
+
+def _fasternet_weight_image80(w1: torch.Tensor, w2: torch.Tensor, wp: torch.Tensor):
+    """C = 80 (csrc/fasternet_block.cu, namespace f80): W1x[:, :64] SW128 | W2 3 chunks [80][64] SW128 |
+    W1x[:, 64:80] SW32 | Wc [slice 0..1][tap 0..8][160][16] SW32 (Cp = 20 channels = two K=16 slices)."""
+    c2, c = w1.shape[0], w1.shape[1]
+    cp = wp.shape[0]
+    assert c == 80 and c2 == 160 and cp == 20
+    f = lambda t: t.detach().float()  # noqa: E731
+    pad = torch.nn.functional.pad
+    bf = torch.bfloat16
+    w1m = f(w1)[:, :, 0, 0]
+    w1x = w1m.clone()
+    w1x[:, :cp] = 0
+    parts = [swizzle128(w1x[:, :64].to(bf).contiguous())]
+    off_w2 = parts[0].numel() * 2
+    w2m = pad(f(w2)[:, :, 0, 0], (0, 192 - c2))
+    for kc in range(3):
+        parts.append(swizzle128(w2m[:, kc * 64:(kc + 1) * 64].to(bf).contiguous()))
+    parts.append(swizzle32(w1x[:, 64:80].to(bf).contiguous()))
+    off_wc = sum(p.numel() for p in parts) * 2
+    wpf = f(wp)
+    wcs = [pad(w1m[:, :cp] @ wpf[:, :, t // 3, t % 3], (0, 32 - cp)) for t in range(9)]     # [160][32] each
+    for sl in range(2):
+        for t in range(9):
+            parts.append(swizzle32(wcs[t][:, sl * 16:(sl + 1) * 16].to(bf).contiguous()))
     return torch.cat(parts).contiguous(), off_w2, off_wc

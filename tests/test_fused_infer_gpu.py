@@ -31,7 +31,8 @@ def test_conv3x3_halo_ragged(shape):
     assert rel_l2(y.float(), ref) < TOL_BF16
 
 
-@pytest.mark.parametrize("shape", [(2, 24, 37, 45), (1, 40, 9, 70), (2, 24, 16, 14)])
+@pytest.mark.parametrize("shape", [(2, 24, 37, 45), (1, 40, 9, 70), (2, 24, 16, 14), (2, 80, 37, 45), (3, 80, 40, 40),
+                                   (1, 80, 5, 3)])
 def test_fasternet_block_ragged(shape):
     M = _mods()
     torch.manual_seed(4)
