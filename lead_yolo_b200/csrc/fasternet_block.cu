@@ -43,10 +43,13 @@ __device__ long long fnb_dbg[296][16];
     for (int z = 0; z < nslots; ++z) fnb_dbg[blockIdx.x][base + z] = dbg_acc[z];                       \
     fnb_dbg[blockIdx.x][base + nslots] = clock64() - dbg_t0;                                           \
   }
+__device__ __forceinline__ long long fb_gtime() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define FB_STAMP(slot) if (threadIdx.x == 0 && blockIdx.x < 296) fnb_dbg[blockIdx.x][slot] = fb_gtime();
 #else
 #define FB_WAIT(slot, bar, par) mbar_wait(bar, par)
 #define FB_DBG_DECL
 #define FB_DBG_FLUSH(base, nslots)
+#define FB_STAMP(slot)
 #endif
 
 struct alignas(64) FnbParams {
@@ -367,6 +370,7 @@ struct alignas(64) Fnb80Params {
 
 __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_constant__ Fnb80Params p) {
   using namespace f80;
+  FB_STAMP(14)
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t w_bar, in_full, u_full[2], v_ready, y_full, y_free;
   __shared__ uint32_t tmem_base_s;
@@ -408,6 +412,7 @@ __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_
 
   if (warp == 0) {
     if (lane == 0 && mine > 0) {
+      FB_DBG_DECL
       tma_prefetch_desc(&p.x_map);
       tma_prefetch_desc(&p.x1_map);
       tma_prefetch_desc(&p.tap_map);
@@ -418,16 +423,18 @@ __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_
         const int n = t / tiles_img, tr = t - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
         const int w0 = tw * Wt, h0 = th * Ht;
         // single input buffer: free once the phase-A MMAs of the previous tile have completed
-        if (i > 0) mbar_wait(&u_full[(i - 1) & 1], ((uint32_t)(i - 1) >> 1) & 1u);
+        if (i > 0) FB_WAIT(1, &u_full[(i - 1) & 1], ((uint32_t)(i - 1) >> 1) & 1u);
         mbar_arrive_expect_tx(&in_full, kTxBytes);
         tma_load_5d(sX0, &p.x_map, &in_full, 0, w0, 0, h0, n);
         tma_load_5d(sHalo, &p.tap_map, &in_full, 0, w0 - 1, 0, h0 - 1, n);
         tma_load_5d(sHalo + kHalo, &p.tap_map, &in_full, 16, w0 - 1, 0, h0 - 1, n);
         tma_load_5d(sX1, &p.x1_map, &in_full, 64, w0, 0, h0, n);
       }
+      FB_DBG_FLUSH(0, 2)
     }
   } else if (warp == 1) {
     if (lane == 0 && mine > 0) {
+      FB_DBG_DECL
       const uint32_t id1 = umma_idesc_bf16_f32(128, C2, 0, 0);
       const uint32_t id2 = umma_idesc_bf16_f32(128, N2, 0, 0);
       const uint64_t x0_d = umma_smem_desc_sw128(smem_u32(sX0), 16, 1024);
@@ -441,7 +448,7 @@ __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_
       mbar_wait(&w_bar, 0);
       auto phase_a = [&](int i) {
         const uint32_t tm_u = tmem + (uint32_t)((i & 1) * C2);
-        mbar_wait(&in_full, (uint32_t)i & 1u);
+        FB_WAIT(0, &in_full, (uint32_t)i & 1u);
         tc_fence_after_sync();
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_bf16(tm_u, x0_d + (uint64_t)(k * 2), w1a_d + (uint64_t)(k * 2), id1, (uint32_t)(k != 0));
@@ -458,8 +465,8 @@ __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_
       for (int i = 0; i < mine; ++i) {
         const uint32_t ph = (uint32_t)i & 1u;
         if (i + 1 < mine) phase_a(i + 1);
-        mbar_wait(&v_ready, ph);
-        mbar_wait(&y_free, ph ^ 1u);
+        FB_WAIT(2, &v_ready, ph);
+        FB_WAIT(3, &y_free, ph ^ 1u);
         tc_fence_after_sync();
 #pragma unroll
         for (int k = 0; k < C2 / 16; ++k)
@@ -467,51 +474,61 @@ __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_
                     w2_d + (uint64_t)((k >> 2) * ((N2 * 128) >> 4) + (k & 3) * 2), id2, (uint32_t)(k != 0));
         umma_commit(&y_full);
       }
+      FB_DBG_FLUSH(3, 4)
     }
   } else if (warp < 6) {
     // hidden group: v = relu(scale*u + shift) -> bf16 -> SW128 A operand of phase B
     const int q = warp & 3;
     const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    FB_DBG_DECL
     for (int i = 0; i < mine; ++i) {
-      mbar_wait(&u_full[i & 1], ((uint32_t)i >> 1) & 1u);
+      FB_WAIT(0, &u_full[i & 1], ((uint32_t)i >> 1) & 1u);
       tc_fence_after_sync();
-      if (i > 0) mbar_wait(&y_full, (uint32_t)(i - 1) & 1u);   // phase B of the previous tile has read sV
       const uint32_t tm_u = tmem + (uint32_t)((i & 1) * C2) + lane_addr;
+      // two TMEM round trips of 80 columns; the first half is converted before sV is known to be free (phase B of the
+      // previous tile still reads it), so that wait hides behind the math
 #pragma unroll
-      for (int cb = 0; cb < C2; cb += 32) {
-        uint32_t acc[2][16];
-        tmem_ld16(tm_u + (uint32_t)cb, acc[0]);
-        tmem_ld16(tm_u + (uint32_t)(cb + 16), acc[1]);
+      for (int half = 0; half < 2; ++half) {
+        uint32_t acc[5][16];
+#pragma unroll
+        for (int b = 0; b < 5; ++b) tmem_ld16(tm_u + (uint32_t)(half * 80 + b * 16), acc[b]);
         tmem_ld_wait();
+        uint32_t w[10][4];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int c = cb + g * 8;
+        for (int g = 0; g < 10; ++g) {
+          const int c = half * 80 + g * 8;
           const float4 s0 = *reinterpret_cast<const float4*>(s_sc + c), s1 = *reinterpret_cast<const float4*>(s_sc + c + 4);
           const float4 h0 = *reinterpret_cast<const float4*>(s_sh + c), h1 = *reinterpret_cast<const float4*>(s_sh + c + 4);
           const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
           const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-          uint32_t w[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float lo = fmaf(__uint_as_float(acc[g >> 1][(g & 1) * 8 + 2 * j]), sc[2 * j], sh[2 * j]);
             const float hi = fmaf(__uint_as_float(acc[g >> 1][(g & 1) * 8 + 2 * j + 1]), sc[2 * j + 1], sh[2 * j + 1]);
-            asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(w[j]) : "f"(hi), "f"(lo));
+            asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(w[g][j]) : "f"(hi), "f"(lo));
           }
+        }
+        if (half == 0 && i > 0) FB_WAIT(1, &y_full, (uint32_t)(i - 1) & 1u);   // phase B of the previous tile has read sV
+#pragma unroll
+        for (int g = 0; g < 10; ++g) {
+          const int c = half * 80 + g * 8;
           const int kc = c >> 6, ch = (c >> 3) & 7;
-          *reinterpret_cast<uint4*>(sV + kc * kXBytes + r * 128 + ((ch ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+          *reinterpret_cast<uint4*>(sV + kc * kXBytes + r * 128 + ((ch ^ (r & 7)) << 4)) = make_uint4(w[g][0], w[g][1], w[g][2], w[g][3]);
         }
       }
       tc_fence_before_sync();
       fence_proxy_async_smem();
       mbar_arrive(&v_ready);
     }
+    if (threadIdx.x == 64) { FB_DBG_FLUSH(8, 2) }
   } else {
     // output group: y = x + W2 v
     const int q = warp & 3;
     const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const int hh = r / P, ww = r - hh * P;
+    FB_DBG_DECL
     for (int i = 0; i < mine; ++i) {
       const uint32_t ph = (uint32_t)i & 1u;
       const int t = (int)blockIdx.x + i * (int)gridDim.x;
@@ -524,7 +541,7 @@ __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_
 #pragma unroll
         for (int k = 0; k < C / 8; ++k) xres[k] = __ldg(reinterpret_cast<const uint4*>(p.x + pix * C) + k);
       }
-      mbar_wait(&y_full, ph);
+      FB_WAIT(1, &y_full, ph);
       tc_fence_after_sync();
 #pragma unroll
       for (int c0 = 0; c0 < N2; c0 += 16) {
@@ -550,10 +567,12 @@ __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_
       tc_fence_before_sync();
       mbar_arrive(&y_free);
     }
+    if (threadIdx.x == 192) { FB_DBG_FLUSH(11, 2) }
   }
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 2) tmem_dealloc(tmem, 512u);
+  FB_STAMP(15)
 }
 
 }  // namespace ly

@@ -9,7 +9,8 @@
 int main(int argc, char** argv) {
   const int C = argc > 1 ? atoi(argv[1]) : 24, HW = argc > 2 ? atoi(argv[2]) : 160, N = 64;
   const int C2 = 2 * C, N2 = (C + 15) / 16 * 16, chunks = (C2 + 63) / 64;
-  const int off_w2 = C2 * 128, off_wc = off_w2 + chunks * N2 * 128, w_bytes = off_wc + 9 * C2 * 32;
+  int off_w2 = C2 * 128, off_wc = off_w2 + chunks * N2 * 128, w_bytes = off_wc + 9 * C2 * 32;
+  if (C == 80) { off_w2 = ly::f80::kOffW2; off_wc = ly::f80::kOffWc; w_bytes = ly::f80::kWBytes; }
   void *x, *y, *w; float* sc;
   cudaMalloc(&x, (size_t)N * HW * HW * C * 2); cudaMemset(x, 0x3c, (size_t)N * HW * HW * C * 2);
   cudaMalloc(&y, (size_t)N * HW * HW * C * 2);
@@ -36,6 +37,12 @@ int main(int argc, char** argv) {
     double a = 0;
     for (int b = 0; b < 296; ++b) a += (double)h[b][idx[z]];
     printf("  %-28s %9.0f clk (%6.0f / tile)\n", names[z], a / nb, a / nb / tiles);
+  }
+  if (C == 80) {   // %globaltimer stamps at kernel entry / exit of every CTA
+    long long t0 = h[0][14], t1 = h[0][15]; double in = 0;
+    for (int b = 0; b < nb; ++b) { if (h[b][14] < t0) t0 = h[b][14]; if (h[b][15] > t1) t1 = h[b][15]; in += (double)(h[b][15] - h[b][14]); }
+    long long e_last = 0; for (int b = 0; b < nb; ++b) if (h[b][14] > e_last) e_last = h[b][14];
+    printf("  first entry -> last exit %.1f us; last entry at +%.1f us; mean CTA lifetime %.1f us\n", (t1 - t0) * 1e-3, (e_last - t0) * 1e-3, in / nb * 1e-3);
   }
   return 0;
 }
