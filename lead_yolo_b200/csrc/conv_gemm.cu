@@ -1,6 +1,6 @@
 // Implicit-GEMM convolution on tcgen05 tensor cores (sm_100a).
 //
-//   persistent grid (one CTA per SM, static tile striding);  block = 576 threads:
+//   persistent grid (one CTA per SM, static tile striding);  block = 608 threads:
 //     warp 0       TMA producer, one lane (A boxes: 64 channels x Wt x Ht pixels of one tap, or one halo box per chunk
 //                  for 3x3 convolutions with resident weights; B boxes: 64 x BN weights unless resident)
 //     warp 1       MMA issuer, one lane (4 x tcgen05.mma K=16 per 64-wide K chunk, one commit per ring stage)
@@ -8,10 +8,12 @@
 //                  tile: TMEM -> registers -> scale/shift/activation/residual -> TMA store (flat bf16) or global stores
 //   A and B tiles live in 128B-swizzled shared memory, up to four accumulators (128 x BN fp32) in TMEM.
 //   Zero padding of a 3x3 convolution and ragged channel counts are TMA out-of-bounds zero fill.
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "ly_common.cuh"
 #include "ly_tc.cuh"
@@ -68,6 +70,7 @@ struct alignas(64) ConvGemmParams {
                    // tests/dev/mma_issue.cu) cover kgroup x 4 MMAs
   int tma_store;   // epilogue stages 32-row x 64-column slabs in shared memory and stores them with TMA
   int vec32_ok;    // bf16 output rows 32-byte aligned, no patch scatter: 16 columns go out as one 32-byte store
+  int issuers;     // MMA-issuing lanes (1 or 2); the ring is split between them
   int det_bulk;    // Detect epilogue stages raw / z rows in the warp's slab and stores them with bulk copies
   int slab_bytes;  // shared-memory slab per epilogue warp (0: none)
   int b_resident;  // all weight chunks stay in shared memory for the whole kernel (single N tile, small K*N)
@@ -374,7 +377,8 @@ __device__ __forceinline__ void epilogue_cols_tma(const ConvGemmParams& p, uint3
 //                              from TMEM buffer i % nbuf while the MMA warp fills the other buffers, so up to four
 //                              tiles' TMEM->global latencies overlap on one SM
 constexpr int kEpiGroups = 4;                 // epilogue warp groups, each drains a different tile
-constexpr int kThreads = 64 + kEpiGroups * 128;
+constexpr int kIssuer2Warp = 2 + kEpiGroups * 4;   // the second MMA-issuing warp sits after the epilogue warps
+constexpr int kThreads = 64 + kEpiGroups * 128 + 32;
 constexpr int kMaxTmemBufs = 4;
 
 __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
@@ -445,8 +449,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       const uint32_t tx = (uint32_t)kg * (p.a_bytes + (p.b_resident ? 0u : (uint32_t)b_stage));
       const int tiles_img = p.tiles_w * p.tiles_h;
       int tile = (int)blockIdx.x;
-      int s = 0;
-      uint32_t ph = 1;   // parity to wait for on the empty barrier of slot s
+      // one ring per MMA-issuing lane (tile i -> ring i % issuers): s/ph of this tile's ring, s2/ph2 of the other
+      const int rs = p.issuers == 2 ? p.stages >> 1 : p.stages;
+      int s = 0, s2 = rs;
+      uint32_t ph = 1, ph2 = 1;   // parity to wait for on the empty barrier of slot s
       for (int i = 0; i < my_tiles; ++i, tile += (int)gridDim.x) {
         const int mt = tile / p.tiles_n, nt = tile - mt * p.tiles_n;
         const int n = mt / tiles_img, tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
@@ -459,14 +465,27 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
             tma_load_5d(sA + (s * kg + j) * p.a_stage, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
             if (!p.b_resident) tma_load_2d(sB + (s * kg + j) * b_stage, &p.b_map, &full_bar[s], (k + j) * 64, n0);
           }
-          if (++s == p.stages) { s = 0; ph ^= 1u; }
+          ++s;
+          if (s == rs) { s = 0; ph ^= 1u; }                       // ring 0 wraps
+          else if (s == p.stages) { s = rs; ph ^= 1u; }           // ring 1 (or the only ring) wraps
+        }
+        if (p.issuers == 2) {   // next tile: the other ring
+          const int ts = s; s = s2; s2 = ts;
+          const uint32_t tp = ph; ph = ph2; ph2 = tp;
         }
       }
       CG_DBG_FLUSH(0, 1)
     }
-  } else if (warp == 1) {
-    // ---------------- MMA issuer ----------------
-    if (lane == 0 && my_tiles > 0) {
+  } else if (warp == 1 || warp == kIssuer2Warp) {
+    // ---------------- MMA issuers ----------------
+    // Two lanes on different SM sub-partitions take alternate tiles when p.issuers == 2 (tests/dev/mma_issue.cu: one
+    // lane sustains an MMA every ~77 clk whatever N is, two lanes together ~50 clk at N = 64).  Each lane owns half of
+    // the ring: an mbarrier parity wait is only safe for a consumer that sees every phase of its barrier.
+    // `which` must be a compile-time constant: anything derived from threadIdx leaves the uniform datapath, and the
+    // descriptors of every tcgen05.mma would then be moved from vector to uniform registers one by one (R2UR).
+    auto issue = [&](auto which_c) {
+    constexpr int which = decltype(which_c)::value;
+    if (lane == 0 && my_tiles > which && which < p.issuers) {
       CG_DBG_DECL
       const uint32_t idesc = umma_idesc_bf16_f32(128, p.BN, 0, 0);
       const uint64_t a_desc0 = umma_smem_desc_sw128(smem_u32(sA), 16, 1024);
@@ -474,9 +493,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       const uint32_t a_step = (uint32_t)(p.a_stage >> 4), b_step = (uint32_t)(b_stage >> 4);
       if (p.b_resident) mbar_wait(&b_ready_bar, 0);
       const int kg = p.kgroup;
-      int s = 0, buf = 0;
+      const int istep = p.issuers;
+      const int s_lo = (which && istep == 2) ? p.stages >> 1 : 0;           // this lane's ring: slots [s_lo, s_hi)
+      const int s_hi = (!which && istep == 2) ? p.stages >> 1 : p.stages;
+      int s = s_lo, buf = which;
       uint32_t ph = 0, use_par = 1;   // use_par: parity to wait for on tmem_empty_bar[buf]
-      for (int i = 0; i < my_tiles; ++i) {
+      for (int i = which; i < my_tiles; i += istep) {
         CG_WAIT(0, &tmem_empty_bar[buf], use_par);   // epilogue has drained this accumulator
         tc_fence_after_sync();
         const uint32_t tmem_d = tmem_base + (uint32_t)(buf * p.BN);
@@ -506,13 +528,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
             umma_bf16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
           }
           umma_commit(&empty_bar[s]);
-          if (++s == p.stages) { s = 0; ph ^= 1u; }
+          if (++s == s_hi) { s = s_lo; ph ^= 1u; }
         }
         umma_commit(&tmem_full_bar[buf]);
-        if (++buf == p.nbuf) { buf = 0; use_par ^= 1u; }
+        buf += istep;
+        if (buf >= p.nbuf) { buf -= p.nbuf; use_par ^= 1u; }
       }
-      CG_DBG_FLUSH(2, 2)
+      if (which == 0) { CG_DBG_FLUSH(2, 2) }
     }
+    };
+    if (warp == 1) issue(std::integral_constant<int, 0>{});
+    else issue(std::integral_constant<int, 1>{});
   } else {
     // ---------------- epilogue ----------------
     CG_DBG_DECL
@@ -878,6 +904,16 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   p.stages = (int)(ring_budget / (p.kgroup * chunk_bytes));
   if (p.stages > kMaxStages) p.stages = kMaxStages;
   LY_REQUIRE(p.stages >= 2, "shared-memory ring too small (BN=%d)", p.BN);
+  // two issuing lanes when each can have a ring that holds a whole tile (>= 2 stages) and one lane alone is
+  // issue-bound (BN <= 128, which also means four accumulators).  With rings shorter than a tile the [128,40]->128
+  // layer went from 53 to 71 us — measured, so the rule stays strict.
+  static const bool one_issuer = getenv("LY_CONV_ONE_ISSUER") != nullptr;   // dev knob
+  p.issuers = (!one_issuer && p.stages >= 4 && p.BN <= 128 && p.stages / 2 >= p.num_k / p.kgroup) ? 2 : 1;
+  if (p.issuers == 2) p.stages &= ~1;
+  static const bool verbose = getenv("LY_CONV_VERBOSE") != nullptr;   // dev knob
+  if (verbose)
+    fprintf(stderr, "[conv] BN=%d num_k=%d kgroup=%d stages=%d issuers=%d halo=%d b_resident=%d a_stage=%d\n", p.BN, num_k,
+            p.kgroup, p.stages, p.issuers, p.halo, p.b_resident, p.a_stage);
   const size_t smem_bytes = (size_t)kEpiGroups * 4 * p.slab_bytes + (p.b_resident ? (size_t)b_all : 0) +
                             (size_t)p.stages * p.kgroup * chunk_bytes + 1024;
 
