@@ -117,10 +117,11 @@ int ly_stem_wgrad(const void* img, int img_is_u8, int N, int H, int W, int Cout,
                   float in_scale, float* dwk, ly_stream_t stream);
 
 /* Fused FasterNet block, inference (models/common.py:1432-1437,1478-1482): y = x + W2 relu(scale*(W1 [pconv3x3(x[:,:C/4])
- * | x[:,C/4:]]) + shift) in ONE persistent kernel; x and y are dense NHWC bf16 [N][H][W][C], C in {24, 40}.  The 2C-wide
+ * | x[:,C/4:]]) + shift) in ONE persistent kernel; x and y are dense NHWC bf16 [N][H][W][C], C in {24, 40, 80} (y 32-byte aligned for C = 80).  The 2C-wide
  * hidden tensor stays in TMEM / shared memory; the partial conv is folded into the first GEMM (Wc_tap = W1[:, :C/4] Wp_tap).
  * wimg: pre-swizzled bf16 weight image with sections W1x | W2 | Wc at byte offsets 0 / off_w2 / off_wc
- * (lead_yolo_b200.packing.fasternet_weight_image); scale/shift: folded mlp.1 BatchNorm [2C]. */
+ * (lead_yolo_b200.packing.fasternet_weight_image; C = 80 has a fixed layout W1x[:, :64] | W2 | W1x[:, 64:] | Wc, checked
+ * against w_bytes / off_w2 / off_wc); scale/shift: folded mlp.1 BatchNorm [2C]. */
 int ly_fasternet_block_infer(const void* x, void* y, int N, int H, int W, int C, const void* wimg, int w_bytes,
                              int off_w2, int off_wc, const float* scale, const float* shift, ly_stream_t stream);
 
