@@ -131,7 +131,9 @@ extern "C" int ly_ca_mid_infer(const void* pooled, long ldp, long rows, long nh,
                  reinterpret_cast<uintptr_t>(w1) % 16 == 0,
              "ly_ca_mid_infer: alignment / ld");
   if (mip == 8 && (C == 64 || C == 128 || C == 256) && ldg % 8 == 0 && reinterpret_cast<uintptr_t>(gates) % 16 == 0) {
-    const long per = 32;  // rows per block: four per warp, so the staged weights are reused
+    // rows per block: up to four per warp so the staged weights are reused, fewer when that would leave SMs idle
+    // (the 20x20 level has 2560 rows: 80 blocks of 32 rows ran on 80 of 148 SMs)
+    const long per = rows >= 32 * 296 ? 32 : (rows >= 16 * 296 ? 16 : 8);
     const int gh = (int)ceil_div(nh, per), gwb = (int)ceil_div(rows - nh, per);
     cudaStream_t s_ = (cudaStream_t)st;
 #define LY_CAMID(CPL)                                                                                                   \

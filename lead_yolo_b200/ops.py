@@ -239,7 +239,8 @@ class StemFn(torch.autograd.Function):
         img = img.contiguous()
         n, _, h, w = img.shape
         cout = weight.shape[0]
-        wk = weight.detach().float().reshape(cout, 48).t().contiguous()
+        # [48][Cout] fp32 copy of the weight: memoised on the weight's version, not rebuilt (one copy kernel) per step
+        wk = cached([weight], "stem_wk", lambda: weight.detach().float().reshape(cout, 48).t().contiguous())
         out = ll.empty_cl(n, cout, h // 4, w // 4, device=img.device)
         in_scale = 1.0 / 255.0 if is_u8 else 1.0
         ll.call("ly_stem_fwd", img, 1 if is_u8 else 0, n, h, w, cout, wk, scale, shift, in_scale, out, cout)
