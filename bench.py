@@ -14,6 +14,7 @@ is not present on the GPU box), fp32 on all host threads, on a bounded sample of
 from __future__ import annotations
 
 import argparse
+import collections
 import json
 import os
 import statistics
@@ -338,17 +339,20 @@ def main():
         # ---- end to end through the public serving call (lead_yolo_b200.engine.InferenceEngine): pinned host uint8
         # batch in, decoded predictions (B,25200,6) fp32 back on the host, every step; copies overlap the replay
         from lead_yolo_b200.engine import InferenceEngine
-        eng = InferenceEngine(model, args.batch, IMG, slots=int(os.environ.get("LY_ENGINE_SLOTS", "2")), device=dev)
+        eng = InferenceEngine(model, args.batch, IMG, slots=int(os.environ.get("LY_ENGINE_SLOTS", "3")), device=dev)
         out_host = eng.host_out[0]
 
         def e2e_loop(k):
-            last = None
+            # serving loop: the host keeps slots-1 batches in flight and consumes the oldest result before it submits the
+            # next batch into that result's slot.  (With one batch in flight a step costs download + upload back to back,
+            # 0.7 + 1.4 ms of PCIe time; with two the copies hide behind the replay — tests/dev/e2e_parts.py.)
+            pending = collections.deque()
             for i in range(k):
-                s_ = eng.submit(host[i % nbuf])
-                if last is not None:
-                    eng.result(last)           # the host consumes batch i-1 while batch i is in flight
-                last = s_
-            eng.result(last)
+                pending.append(eng.submit(host[i % nbuf]))
+                if len(pending) >= eng.slots:
+                    eng.result(pending.popleft())
+            while pending:
+                eng.result(pending.popleft())
 
         e2e_loop(3)
         barrier()
