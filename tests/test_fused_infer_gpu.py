@@ -15,7 +15,8 @@ def _mods():
     return M
 
 
-@pytest.mark.parametrize("shape", [(2, 64, 37, 45), (1, 64, 8, 130), (3, 32, 19, 7)])
+@pytest.mark.parametrize("shape", [(2, 64, 37, 45), (1, 64, 8, 130), (3, 32, 19, 7), (2, 128, 40, 40), (1, 128, 37, 45),
+                                   (1, 256, 33, 30)])
 def test_conv3x3_halo_ragged(shape):
     """3x3 Conv with resident weights takes the halo path (one box per K chunk, row-shifted taps)."""
     M = _mods()
