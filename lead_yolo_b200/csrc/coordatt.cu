@@ -128,16 +128,23 @@ __global__ void __launch_bounds__(256) ca_pool_kernel(const __nv_bfloat16* __res
 
 // mode 0: out = x * a_h[n,h] * a_w[n,w]                         (forward, and dx1 = dy*a_h*a_w)
 // mode 1: out = g_h[n,h]/W + g_w[n,w]/H                          (backward of the pooling)
+// IT: index type.  The (pixel, vector) decomposition is four divisions per thread; in 64 bits they were most of this
+// kernel's instructions (it ran instruction-bound at a third of the HBM rate), so the launcher picks 32-bit indices
+// whenever the element count allows.
+template <typename IT>
 __global__ void __launch_bounds__(256) ca_pointwise_kernel(const __nv_bfloat16* __restrict__ x, long ldx,
                                                            const __nv_bfloat16* __restrict__ gate, long ldg, int N,
                                                            int H, int W, int V, int mode,
                                                            __nv_bfloat16* __restrict__ out, long ldo) {
-  const long total = (long)N * H * W * V;
-  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const IT total = (IT)N * (IT)H * (IT)W * (IT)V;
+  const IT t = (IT)blockIdx.x * (IT)blockDim.x + (IT)threadIdx.x;
   if (t >= total) return;
-  const int v = (int)(t % V);
-  const long pix = t / V;
-  const int w = (int)(pix % W), h = (int)((pix / W) % H), n = (int)(pix / ((long)W * H));
+  const int v = (int)(t % (IT)V);
+  const IT pixi = t / (IT)V;
+  const int w = (int)(pixi % (IT)W);
+  const IT rowi = pixi / (IT)W;
+  const int h = (int)(rowi % (IT)H), n = (int)(rowi / (IT)H);
+  const long pix = (long)pixi;
   float ah[8], aw[8], r[8];
   unpack8(ldq(gate + ((long)n * H + h) * ldg + v * 8), ah);
   unpack8(ldq(gate + ((long)N * H + (long)n * W + w) * ldg + v * 8), aw);
@@ -201,8 +208,12 @@ extern "C" int ly_ca_apply(const void* x, long ldx, const void* gates, long ldg,
   if (rc) return rc;
   const int V = C / 8;
   const long total = (long)N * H * W * V;
-  ca_pointwise_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
-      (const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)gates, ldg, N, H, W, V, 0, (__nv_bfloat16*)out, ldo);
+  if (total < (1L << 31))
+    ca_pointwise_kernel<unsigned><<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
+        (const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)gates, ldg, N, H, W, V, 0, (__nv_bfloat16*)out, ldo);
+  else
+    ca_pointwise_kernel<long><<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
+        (const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)gates, ldg, N, H, W, V, 0, (__nv_bfloat16*)out, ldo);
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -228,8 +239,12 @@ extern "C" int ly_ca_pool_bwd(const void* dpooled, long ldp, int N, int H, int W
   if (rc) return rc;
   const int V = C / 8;
   const long total = (long)N * H * W * V;
-  ca_pointwise_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
-      nullptr, 0, (const __nv_bfloat16*)dpooled, ldp, N, H, W, V, 1, (__nv_bfloat16*)dx, ldx);
+  if (total < (1L << 31))
+    ca_pointwise_kernel<unsigned><<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
+        nullptr, 0, (const __nv_bfloat16*)dpooled, ldp, N, H, W, V, 1, (__nv_bfloat16*)dx, ldx);
+  else
+    ca_pointwise_kernel<long><<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
+        nullptr, 0, (const __nv_bfloat16*)dpooled, ldp, N, H, W, V, 1, (__nv_bfloat16*)dx, ldx);
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
