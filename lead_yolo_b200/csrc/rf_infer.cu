@@ -252,8 +252,18 @@ __global__ void __launch_bounds__(256) rf_se_att_kernel(const float* __restrict_
   const long total = (long)N * HK * WK;
   const long t = (long)(blockIdx.x - N) * blockDim.x + threadIdx.x;
   if (t >= total) return;
-  const int xq = (int)(t % WK), y = (int)((t / WK) % HK);
-  const long n = t / ((long)WK * HK);
+  int xq, y;
+  long n;
+  if (total < (1L << 31)) {   // 32-bit divisions: the 64-bit ones were most of this thread's instructions
+    const unsigned tu = (unsigned)t, row = tu / (unsigned)WK;
+    xq = (int)(tu - row * (unsigned)WK);
+    n = (long)(row / (unsigned)HK);
+    y = (int)(row - (unsigned)n * (unsigned)HK);
+  } else {
+    xq = (int)(t % WK);
+    y = (int)((t / WK) % HK);
+    n = t / ((long)WK * HK);
+  }
   float acc = 0.f;
 #pragma unroll
   for (int i = 0; i < 3; ++i)
