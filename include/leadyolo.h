@@ -106,6 +106,34 @@ int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz, long M, in
 int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, long ldy, long M, int C, int act, void* dz,
                         long lddz, ly_stream_t stream);
 
+/* Training-mode BatchNorm2d forward in two launches (nn.BatchNorm2d at the sites listed above, batch statistics):
+ * ly_bn_stats accumulates, per channel, the sums about a pivot K = x[0][c] into acc = fp32 [3][C] = K | Σ(x-K) | Σ(x-K)²
+ * (zero acc first; shifted sums keep the variance from cancelling when |mean| >> std); ly_bn_apply_train derives
+ * mean / biased variance from acc, writes y = act(gamma*(z-mean)*rstd + beta), saves stats = fp32 [4][C]
+ * (mean, rstd, scale, shift) for ly_bn_act_bwd and updates running_mean / running_var (unbiased variance, `momentum`)
+ * in place when they are non-NULL. */
+int ly_bn_stats(const void* x, long ld, long M, int C, float* acc, ly_stream_t stream);
+int ly_bn_apply_train(const void* z, long ldz, long M, int C, const float* acc, const float* gamma, const float* beta,
+                      float eps, float momentum, float* running_mean, float* running_var, float* stats, int act,
+                      void* y, long ldy, ly_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Weight layouts of the training path.  nn.Conv2d keeps fp32 OIHW parameters (optimizer, EMA, DDP and checkpoints
+ * touch them: utils/torch_utils.py:318-346, 404-432, train.py:387-403); the GEMM kernels read packed bf16.  One launch
+ * per weight and direction.  c0..c3: channels of the K-concatenated sources (0 = unused), patch = 1 for kernel == stride.
+ *   ly_pack_weight        w [Cout][Cin][kh][kw] -> wp bf16 [Cout][Kp]                         (forward operand)
+ *   ly_pack_weight_dgrad  -> weights of the input-gradient GEMM for source channels [coff, coff+cs):
+ *                            stride 1: [cs][kh*kw*P], flipped taps, K = output channel; patch: [kh*kw*cs][P];
+ *                            P = Cout rounded up to a multiple of 64 (zero filled)
+ *   ly_unpack_wgrad       dwp fp32 [>=Cout][Kp] (ly_conv_wgrad's output) -> dw [Cout][Cin][kh][kw], added when accumulate
+ * ------------------------------------------------------------------------------------------------------ */
+int ly_pack_weight(const float* w, int Cout, int kh, int kw, int patch, int c0, int c1, int c2, int c3, void* wp,
+                   ly_stream_t stream);
+int ly_pack_weight_dgrad(const float* w, int Cout, int Cin, int kh, int kw, int patch, int coff, int cs, void* wd,
+                         ly_stream_t stream);
+int ly_unpack_wgrad(const float* dwp, int Cout, int kh, int kw, int patch, int c0, int c1, int c2, int c3, float* dw,
+                    int accumulate, ly_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------------
  * Stem: PatchEmbed_FasterNet.proj on the raw image (models/common.py:1531,1537): 4x4/s4 conv, 3 -> Cout,
  * NCHW fp32 (or uint8 with in_scale = 1/255, train.py:295) -> NHWC bf16; out = scale*conv + shift.
@@ -236,6 +264,56 @@ int ly_rf_attention_bwd(const float* datt, const float* att, const float* maps, 
 int ly_rf_generate_bwd(const void* dZ, const void* x, long ldx, int N, int H, int W, int C, int k, int s, int ho,
                        int wo, const float* wgk, const float* extra, void* dx, long lddx, float* dwgk,
                        ly_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Detection loss (utils/loss.py:121-268 ComputeLoss.__call__ / build_targets with the EIoU box term of
+ * utils/metrics.py:293-354), fp32, static shapes (CUDA-graph capturable).  p[l]: raw head map of level l,
+ * logical (bs, na, ny, nx, nc+5) with element strides sb/sa/sy/sx/so; dp[l]: its gradient, same strides (backward
+ * only; every logical element is written).  targets: [nt][6] = (image, class, x, y, w, h) normalised, rows with
+ * image < 0 are padding.  anchors: [nl][na][2] in grid units (Detect.anchors).  Focal loss (fl_gamma > 0),
+ * autobalance and sort_obj_iou are not supported.  workspace: ly_yolo_loss_workspace_bytes() bytes, written by
+ * _fwd and read by _bwd.  out: [4] = (lbox + lobj + lcls) * bs | lbox | lobj | lcls (weighted by hyp box/obj/cls).
+ * grad_scale: DEVICE scalar, the upstream gradient of out[0].
+ * ------------------------------------------------------------------------------------------------------ */
+typedef struct {
+  int nl, na, nc, bs, nt;
+  int ny[3], nx[3];
+  const float* p[3];
+  float* dp[3];
+  long sb[3], sa[3], sy[3], sx[3], so[3];
+  const float* anchors;
+  const float* targets;
+  float balance[3]; /* loss.py:112: [4.0, 1.0, 0.4] */
+  float anchor_t, box, obj, cls, cls_pw, obj_pw, cp, cn; /* hyp + smooth_BCE targets */
+} ly_loss_desc;
+long ly_yolo_loss_workspace_bytes(const ly_loss_desc* d);
+int ly_yolo_loss_fwd(const ly_loss_desc* d, void* workspace, float* out, ly_stream_t stream);
+int ly_yolo_loss_bwd(const ly_loss_desc* d, const void* workspace, const float* grad_scale, ly_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Confidence filter + class-aware NMS on the decoded predictions (utils/general.py:884-994 non_max_suppression,
+ * best-class branch, around torchvision.ops.nms), static shapes, no wall-clock time limit.
+ * pred: fp32 [bs][rows][no]; det: fp32 [bs][max_det][6] = (x1, y1, x2, y2, conf, cls), rows past det_count[i] are 0;
+ * n_candidates (may be NULL): candidates above conf_thres per image — when it exceeds max_candidates (<= 8192) the
+ * surplus was dropped in arrival order and the result for that image is not the reference's.
+ * workspace: ly_nms_workspace_bytes(bs, max_candidates) bytes.
+ * ------------------------------------------------------------------------------------------------------ */
+long ly_nms_workspace_bytes(int bs, int max_candidates);
+int ly_detect_nms(const float* pred, int bs, int rows, int no, float conf_thres, float iou_thres, int agnostic,
+                  int max_det, int max_candidates, void* workspace, float* det, int* det_count, int* n_candidates,
+                  ly_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Optimiser step on flat fp32 buffers (train.py:330-341; utils/torch_utils.py:318-346 smart_optimizer = SGD with
+ * Nesterov momentum, groups [0,n0) decayed weights | [n0,n1) BatchNorm weights | [n1,n) biases; 404-432 ModelEMA):
+ * gradient scaling + norm clipping + SGD + EMA in one pass.  hp: DEVICE fp32 [8] = lr0, lr1, lr2, momentum,
+ * weight_decay, max_norm (<= 0: off), ema_decay, grad_scale.  grad_sq: DEVICE scalar Σ g² (ly_sq_sum; ADDS into out),
+ * NULL = no clipping.  ema may be NULL.  ly_ema_update: ema = d*ema + (1-d)*src (BatchNorm buffers).
+ * ------------------------------------------------------------------------------------------------------ */
+int ly_sq_sum(const float* g, long n, float* out, ly_stream_t stream);
+int ly_sgd_ema_step(float* params, const float* grads, float* momentum_buf, float* ema, long n, long n0, long n1,
+                    const float* hp, const float* grad_sq, ly_stream_t stream);
+int ly_ema_update(float* ema, const float* src, long n, const float* hp, ly_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -67,3 +67,19 @@ def stream_ptr() -> C.c_void_p:
 
 def ptr(t) -> C.c_void_p | None:
     return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class LossDesc(C.Structure):
+    """ly_loss_desc of include/leadyolo.h."""
+    _fields_ = [
+        ("nl", C.c_int), ("na", C.c_int), ("nc", C.c_int), ("bs", C.c_int), ("nt", C.c_int),
+        ("ny", C.c_int * 3), ("nx", C.c_int * 3),
+        ("p", C.c_void_p * 3),
+        ("dp", C.c_void_p * 3),
+        ("sb", C.c_long * 3), ("sa", C.c_long * 3), ("sy", C.c_long * 3), ("sx", C.c_long * 3), ("so", C.c_long * 3),
+        ("anchors", C.c_void_p),
+        ("targets", C.c_void_p),
+        ("balance", C.c_float * 3),
+        ("anchor_t", C.c_float), ("box", C.c_float), ("obj", C.c_float), ("cls", C.c_float),
+        ("cls_pw", C.c_float), ("obj_pw", C.c_float), ("cp", C.c_float), ("cn", C.c_float),
+    ]

@@ -342,3 +342,147 @@ extern "C" int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, lon
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Training-mode BatchNorm in two launches (statistics, then normalise + activation) with the finalize step folded
+// into the second one.  The sums are taken about a per-channel pivot K = x[0][c] (shifted-data algorithm):
+// var = Σ(x-K)²/n − (Σ(x-K)/n)² does not cancel when |mean| >> std, which the plain E[x²] − mean² form does.
+// acc: fp32 [3][C] = K | Σ(x-K) | Σ(x-K)²; the two sum rows are accumulated with atomics (zero them first).
+// ------------------------------------------------------------------------------------------------
+namespace ly {
+
+__global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long ld, long M, int V,
+                                                       float* __restrict__ acc) {
+  extern __shared__ float sm[];  // [2][C]
+  const int C = V * 8;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  LY_FLAT_SETUP(V)
+  float s[8], q[8], K[8];
+  unpack8(ld16(x + v * 8), K);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  if (blockIdx.x == 0 && threadIdx.x < V) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[v * 8 + j] = K[j];
+  }
+  long row = row0;
+  for (; row + 3 * rstep < M; row += 4 * rstep) {
+    uint4 u[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) u[i] = ld16(x + (row + i * rstep) * ld + v * 8);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float f[8];
+      unpack8(u[i], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = f[j] - K[j];
+        s[j] += d;
+        q[j] = fmaf(d, d, q[j]);
+      }
+    }
+  }
+  for (; row < M; row += rstep) {
+    float f[8];
+    unpack8(ld16(x + row * ld + v * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = f[j] - K[j];
+      s[j] += d;
+      q[j] = fmaf(d, d, q[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    atomicAdd(&sm[v * 8 + j], s[j]);
+    atomicAdd(&sm[C + v * 8 + j], q[j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(&acc[C + i], sm[i]);
+    atomicAdd(&acc[2 * C + i], sm[C + i]);
+  }
+}
+
+__device__ __forceinline__ void bn_moments(const float* __restrict__ acc, int C, int c, float inv_n, float& mean,
+                                           float& var) {
+  const float d = acc[C + c] * inv_n;
+  mean = acc[c] + d;
+  var = fmaxf(acc[2 * C + c] * inv_n - d * d, 0.f);
+}
+
+__global__ void __launch_bounds__(256) bn_apply_train_kernel(
+    const __nv_bfloat16* __restrict__ z, long ldz, long M, int V, const float* __restrict__ acc,
+    const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum, float* running_mean,
+    float* running_var, float* __restrict__ stats, int act, __nv_bfloat16* __restrict__ y, long ldy) {
+  LY_FLAT_SETUP(V)
+  const int C = V * 8;
+  const float n = (float)M, inv_n = 1.f / n;
+  if (blockIdx.x == 0) {
+    // saved statistics (mean, rstd, scale, shift) for the backward pass + running-statistics update
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      float mean, var;
+      bn_moments(acc, C, c, inv_n, mean, var);
+      const float rstd = rsqrtf(var + eps);
+      const float g = gamma != nullptr ? gamma[c] : 1.f, b = beta != nullptr ? beta[c] : 0.f;
+      stats[c] = mean;
+      stats[C + c] = rstd;
+      stats[2 * C + c] = g * rstd;
+      stats[3 * C + c] = b - mean * g * rstd;
+      if (running_mean != nullptr) {
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        const float unbiased = n > 1.f ? var * n / (n - 1.f) : var;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+      }
+    }
+  }
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = v * 8 + j;
+    float mean, var;
+    bn_moments(acc, C, c, inv_n, mean, var);
+    const float rstd = rsqrtf(var + eps);
+    const float g = gamma != nullptr ? gamma[c] : 1.f, b = beta != nullptr ? beta[c] : 0.f;
+    sc[j] = g * rstd;
+    sh[j] = b - mean * sc[j];
+  }
+  for (long row = row0; row < M; row += rstep) {
+    float f[8];
+    unpack8(ld16(z + row * ldz + v * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = act_apply(fmaf(f[j], sc[j], sh[j]), act);
+    st16(y + row * ldy + v * 8, pack8(f));
+  }
+}
+
+}  // namespace ly
+
+extern "C" int ly_bn_stats(const void* x, long ld, long M, int C, float* acc, ly_stream_t st) {
+  int rc = check_mat(x, ld, M, C, "ly_bn_stats");
+  if (rc) return rc;
+  LY_REQUIRE(acc != nullptr, "ly_bn_stats: null accumulator");
+  const int V = C / 8;
+  bn_stats_kernel<<<flat_grid(M, V, 256), 256, 2 * C * sizeof(float), (cudaStream_t)st>>>((const __nv_bfloat16*)x, ld,
+                                                                                          M, V, acc);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_bn_apply_train(const void* z, long ldz, long M, int C, const float* acc, const float* gamma,
+                                 const float* beta, float eps, float momentum, float* running_mean,
+                                 float* running_var, float* stats, int act, void* y, long ldy, ly_stream_t st) {
+  int rc = check_mat(z, ldz, M, C, "ly_bn_apply_train(z)");
+  if (rc) return rc;
+  rc = check_mat(y, ldy, M, C, "ly_bn_apply_train(y)");
+  if (rc) return rc;
+  LY_REQUIRE(acc && stats, "ly_bn_apply_train: null statistics");
+  LY_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "ly_bn_apply_train: running statistics come in pairs");
+  const int V = C / 8;
+  bn_apply_train_kernel<<<flat_grid(M, V, 256), 256, 0, (cudaStream_t)st>>>(
+      (const __nv_bfloat16*)z, ldz, M, V, acc, gamma, beta, eps, momentum, running_mean, running_var, stats, act,
+      (__nv_bfloat16*)y, ldy);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}

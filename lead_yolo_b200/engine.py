@@ -16,8 +16,14 @@ import torch
 
 
 class InferenceEngine:
-    def __init__(self, model: torch.nn.Module, batch: int, img: int = 640, slots: int = 2, device=None):
+    """nms=None: the result is the dense decoded tensor (B, 25200, no).  nms=(conf_thres, iou_thres[, max_det[,
+    max_candidates]]): the captured graph also runs the device NMS (postprocess.nms_static) and the result is the
+    packed tensor (B, max_det + 1, 6): rows [0, max_det) = detections (x1, y1, x2, y2, conf, cls), row max_det =
+    (count, n_candidates, 0, 0, 0, 0) — 0.5 MB instead of 38.7 MB per 64 images over PCIe."""
+
+    def __init__(self, model: torch.nn.Module, batch: int, img: int = 640, slots: int = 2, device=None, nms=None):
         self.model = model.eval()
+        self.nms = None if nms is None else tuple(nms) + (0.25, 0.45, 300, 4096)[len(tuple(nms)):]
         self.device = torch.device(device) if device is not None else next(model.parameters()).device
         self.slots = slots
         self.s_in, self.s_run, self.s_out = (torch.cuda.Stream(self.device) for _ in range(3))
@@ -29,17 +35,39 @@ class InferenceEngine:
                 for _ in range(2):          # warm-up: fills weight-pack caches, Detect grids
                     self.model(self.inp[0])
             self.s_run.synchronize()
+            if self.nms is not None:
+                with torch.cuda.stream(self.s_run):
+                    self._post(self.model(self.inp[0])[0])      # first call sets the kernel's shared-memory attribute
+                self.s_run.synchronize()
             for s in range(slots):
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g, stream=self.s_run):
                     o = self.model(self.inp[s])
+                    res = o[0] if self.nms is None else self._post(o[0])
                 self.graphs.append(g)
-                self.out.append(o[0])
+                self.out.append(res)
         self.host_out = [torch.empty(self.out[0].shape, dtype=self.out[0].dtype).pin_memory() for _ in range(slots)]
         self.ev_in = [torch.cuda.Event() for _ in range(slots)]
         self.ev_run = [torch.cuda.Event() for _ in range(slots)]
         self.ev_out = [torch.cuda.Event() for _ in range(slots)]
         self._n = 0
+
+    def _post(self, dense: torch.Tensor) -> torch.Tensor:
+        from .postprocess import nms_static
+        conf, iou, max_det, max_cand = self.nms
+        bs = dense.shape[0]
+        packed = torch.zeros((bs, max_det + 1, 6), dtype=torch.float32, device=dense.device)
+        det, count, ncand = nms_static(dense, conf, iou, max_det=max_det, max_candidates=max_cand)
+        packed[:, :max_det] = det
+        packed[:, max_det, 0] = count.float()
+        packed[:, max_det, 1] = ncand.float()
+        return packed
+
+    @staticmethod
+    def unpack(packed: torch.Tensor):
+        """Host side of nms mode: list of (n, 6) detections per image, as the reference's non_max_suppression."""
+        max_det = packed.shape[1] - 1
+        return [packed[i, :int(packed[i, max_det, 0])] for i in range(packed.shape[0])]
 
     def submit(self, host_images: torch.Tensor) -> int:
         """Enqueue one pinned uint8 (B,3,H,W) host batch; returns the slot whose host_out will hold the result."""

@@ -7,12 +7,12 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import ConvDesc, check, lib, ptr, stream_ptr
+from ._lib import ConvDesc, LeadYoloError, check, lib, ptr, stream_ptr
 
 CL = torch.channels_last
 COUNT = [0]        # kernels launched through the C-ABI (bench.py: gpu_launches)
 PROFILE = None     # when a list: (entry point, start event, end event, algorithmic bytes, flops) per call
-_LAUNCHES = {"ly_rfcbam_front_infer": 3, "ly_bn_act_bwd": 2, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 2}
+_LAUNCHES = {"ly_yolo_loss_fwd": 4, "ly_yolo_loss_bwd": 2, "ly_detect_nms": 2, "ly_rfcbam_front_infer": 3, "ly_bn_act_bwd": 2, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 2}
 
 
 class _Prof:
@@ -150,6 +150,14 @@ _SIGS = {
     "ly_bn_fold": "ifppppppppp",
     "ly_scale_shift_act": "pllippipl",
     "ly_bn_act_bwd": "plpllippppiipppl",
+    "ly_bn_stats": "pllip",
+    "ly_bn_apply_train": "pllipppffpppipl",
+    "ly_pack_weight": "piiiiiiiip",
+    "ly_pack_weight_dgrad": "piiiiiiip",
+    "ly_unpack_wgrad": "piiiiiiiipi",
+    "ly_sq_sum": "plp",
+    "ly_sgd_ema_step": "pppplllpp",
+    "ly_ema_update": "pplp",
     "ly_act_bwd_from_out": "plplliipl",
     "ly_stem_fwd": "piiiiipppfpl",
     "ly_stem_wgrad": "piiiiiplfp",
@@ -209,8 +217,9 @@ def call(name, *args):
         check(fn(*conv, torch.cuda.current_stream().cuda_stream), name)
 
 
-def conv_wgrad(srcs, dz, cout, k=1, stride=1, pad=0):
-    """fp32 [Cout, Kp] packed weight gradient of conv(cat(srcs)) given the output gradient dz (bf16 NHWC)."""
+def conv_wgrad(srcs, dz, cout, k=1, stride=1, pad=0, zeros=None):
+    """fp32 [Cout, Kp] packed weight gradient of conv(cat(srcs)) given the output gradient dz (bf16 NHWC).
+    `zeros(n)` supplies the zero-initialised accumulator (the training arena); default torch.zeros."""
     from .packing import packed_k
     d = ConvDesc()
     keep = []
@@ -228,7 +237,10 @@ def conv_wgrad(srcs, dz, cout, k=1, stride=1, pad=0):
     d.Cout = cout
     dz, dld = as_nhwc(dz)
     kp = packed_k([s.shape[1] for s in srcs], k, k, patch=(stride == k and k > 1))
-    dw = torch.zeros((cout, kp), dtype=torch.float32, device=dz.device)
+    if zeros is None:
+        dw = torch.zeros((cout, kp), dtype=torch.float32, device=dz.device)
+    else:
+        dw = zeros(cout * kp, dz.device).view(cout, kp)
     fn = lib().ly_conv_wgrad
     fn.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p]
     fn.restype = C.c_int

@@ -658,6 +658,10 @@ class Detect(nn.Module):
             rows = sum(self.na * ny * nx for ny, nx in shapes)
             zcat = torch.empty((bs, rows, self.no), dtype=torch.float32, device=x[0].device)
             off = 0
+            # strides as Python floats, read once per stride tensor: under the reference's DetectionModel._apply
+            # (models/yolo.py:239-249) `stride` lives on the GPU, and a per-forward float() would be a device sync
+            # (and an error inside CUDA-graph capture)
+            strides = ops.cached([self.stride], "strides", lambda: [float(s) for s in self.stride.detach().cpu()])
             for i in range(self.nl):
                 m = self.m[i]
                 ny, nx = shapes[i]
@@ -670,10 +674,10 @@ class Detect(nn.Module):
                     # head conv + bias + decode in one kernel (ly_detect_head_infer)
                     xi, ldx = ll.as_nhwc(xi)
                     ll.call("ly_detect_head_infer", xi, ldx, bs, ny, nx, m.in_channels, wp, b, self.na, self.no,
-                            float(self.stride[i]), anc, raw, zcat, rows, off)
+                            strides[i], anc, raw, zcat, rows, off)
                 else:
                     y = ops.conv_infer([xi], wp, m.out_channels, shift=b, out_fp32=True)
-                    ll.call("ly_detect_decode", y, bs, ny, nx, self.na, self.no, float(self.stride[i]), anc, raw, zcat,
+                    ll.call("ly_detect_decode", y, bs, ny, nx, self.na, self.no, strides[i], anc, raw, zcat,
                             rows, off)
                 x[i] = raw
                 off += self.na * ny * nx
@@ -687,8 +691,12 @@ class Detect(nn.Module):
             else:
                 y = ops.conv([x[i]], m.weight, m.bias, out_fp32=True)
             bs, _, ny, nx = y.shape
-            # y is NHWC in memory: (bs, ny, nx, na*no) -> (bs, na, ny, nx, no)
-            x[i] = y.permute(0, 2, 3, 1).reshape(bs, ny, nx, self.na, self.no).permute(0, 3, 1, 2, 4).contiguous()
+            # y is NHWC in memory: (bs, ny, nx, na*no) -> (bs, na, ny, nx, no); in training the maps stay strided views
+            # of the convolution output (the reference makes a contiguous copy, models/yolo.py:95): the loss kernels
+            # take strides, and the gradient then flows back into the head's GEMMs without a permute copy
+            x[i] = y.permute(0, 2, 3, 1).reshape(bs, ny, nx, self.na, self.no).permute(0, 3, 1, 2, 4)
+            if not self.training:
+                x[i] = x[i].contiguous()
             if not self.training:
                 if self.dynamic or self.grid[i].shape[2:4] != x[i].shape[2:4] or self.grid[i].device != y.device:
                     self.grid[i], self.anchor_grid[i] = self._make_grid(nx, ny, i)

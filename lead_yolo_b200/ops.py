@@ -11,7 +11,7 @@ import weakref
 import torch
 
 from . import lowlevel as ll
-from .packing import pack_conv_weight, unpack_conv_weight
+from .packing import pack_conv_weight
 
 BF16 = torch.bfloat16
 CL = torch.channels_last
@@ -36,6 +36,47 @@ def cached(key_tensors, tag, builder):
     return val
 
 
+# ---------------------------------------------------------------------------------------------------------
+# Zero-initialised fp32 accumulators.  Many kernels add into small fp32 buffers (BatchNorm sums, weight-gradient
+# partials, attention gradients): one torch.zeros launch each.  A training engine can open an arena instead: ONE
+# buffer zeroed once per step, handed out in 256-byte aligned slices (train.TrainEngine).  Outside an arena this
+# is plain torch.zeros.
+# ---------------------------------------------------------------------------------------------------------
+class _Arena:
+    buf = None
+    off = 0
+    need = 0
+    active = False
+
+
+def arena_begin(device, min_floats=0):
+    """Start a step: (re)allocate to the high-water mark of the previous step and zero the whole arena."""
+    want = max(int(_Arena.need * 1.05) + 1024, min_floats)
+    if _Arena.buf is None or _Arena.buf.numel() < want or _Arena.buf.device != torch.device(device):
+        _Arena.buf = torch.empty(want, dtype=torch.float32, device=device)
+    _Arena.buf.zero_()
+    _Arena.off = 0
+    _Arena.need = 0
+    _Arena.active = True
+
+
+def arena_end():
+    _Arena.active = False
+
+
+def zeros_f32(n, device):
+    """n zeroed floats: an arena slice when a training engine has one open, else torch.zeros."""
+    n = int(n)
+    padded = (n + 63) // 64 * 64
+    _Arena.need += padded
+    if _Arena.active and _Arena.buf is not None and _Arena.off + padded <= _Arena.buf.numel() and \
+            _Arena.buf.device == torch.device(device):
+        out = _Arena.buf[_Arena.off:_Arena.off + n]
+        _Arena.off += padded
+        return out
+    return torch.zeros(n, dtype=torch.float32, device=device)
+
+
 def to_act(x: torch.Tensor) -> torch.Tensor:
     """Any float NCHW tensor -> bf16 channels_last activation."""
     if x.dtype == BF16 and ll.pixel_ld(x) is not None:
@@ -57,15 +98,41 @@ def _geom(k, s):
     return patch, pad
 
 
-def _dgrad_weight(w_s: torch.Tensor, k: int, patch: bool):
-    """OIHW weight of the convolution that maps dZ -> dX_s ('Backward adds')."""
-    if patch:
-        cout, cs = w_s.shape[:2]
-        # GEMM columns (ky, kx, c), K = Cout
-        return w_s.permute(2, 3, 1, 0).reshape(k * k * cs, cout, 1, 1)
-    if k == 1:
-        return w_s.transpose(0, 1)
-    return w_s.flip(2, 3).transpose(0, 1)
+def _w32(weight):
+    w = weight.detach()
+    return w if (w.dtype == torch.float32 and w.is_contiguous()) else w.float().contiguous()
+
+
+def packed_weight(weight, chans, k, patch):
+    """bf16 [Cout][Kp] forward operand of `weight` for K-concatenated sources `chans`: one kernel launch, memoised on
+    the parameter's version (training: once per optimiser step; inference: once)."""
+    chans = tuple(int(c) for c in chans)
+
+    def build():
+        cout = weight.shape[0]
+        from .packing import packed_k
+        wp = torch.empty((cout, packed_k(list(chans), k, k, patch)), dtype=BF16, device=weight.device)
+        c4 = list(chans) + [0] * (4 - len(chans))
+        ll.call("ly_pack_weight", _w32(weight), cout, k, k, 1 if patch else 0, c4[0], c4[1], c4[2], c4[3], wp)
+        return wp
+
+    if weight.grad_fn is not None:          # derived tensor (e.g. a masked / permuted view): nothing stable to key on
+        return build()
+    return cached([weight], ("pw", chans, k, patch), build)
+
+
+def packed_weight_dgrad(weight, cout, cin, k, patch, coff, cs):
+    """bf16 weights of the GEMM that maps dZ to the gradient of source channels [coff, coff+cs) (one launch)."""
+    def build():
+        p64 = ((cout + 7) // 8 * 8 + 63) // 64 * 64
+        rows, kp = (k * k * cs, p64) if patch else (cs, k * k * p64)
+        wd = torch.empty((rows, kp), dtype=BF16, device=weight.device)
+        ll.call("ly_pack_weight_dgrad", _w32(weight), cout, cin, k, k, 1 if patch else 0, coff, cs, wd)
+        return wd
+
+    if weight.grad_fn is not None:
+        return build()
+    return cached([weight], ("pwd", k, patch, coff, cs), build)
 
 
 class ConvFn(torch.autograd.Function):
@@ -77,7 +144,7 @@ class ConvFn(torch.autograd.Function):
         srcs = [to_act(x) for x in srcs]
         chans = [x.shape[1] for x in srcs]
         cout = weight.shape[0]
-        wp = pack_conv_weight(weight, chans, patch=patch)
+        wp = packed_weight(weight, chans, k, patch)
         shift = bias.detach().float().contiguous() if bias is not None else None
         res = to_act(residual) if residual is not None else None
         y = ll.conv_gemm(srcs, wp, cout, k=k, stride=s, pad=pad, shift=shift, act=act, residual=res,
@@ -109,23 +176,19 @@ class ConvFn(torch.autograd.Function):
             dz = dzp
         d_bias = None
         if has_bias and ctx.needs_input_grad[1]:
-            sums = torch.zeros(cpad, dtype=torch.float32, device=dz.device)
+            sums = zeros_f32(cpad, dz.device)
             ll.call("ly_col_stats", dz, ll.pixel_ld(dz), _rows(dz), cpad, sums, None)
             d_bias = sums[:cout]
-        wf = weight.detach().float()
-        if cpad != cout:
-            wf = torch.nn.functional.pad(wf, (0, 0, 0, 0, 0, 0, 0, cpad - cout))
+        cin = sum(chans)
         d_srcs = []
         off = 0
         for i, x in enumerate(srcs):
             cs = chans[i]
             if ctx.needs_input_grad[7 + i]:
-                wd = _dgrad_weight(wf[:, off:off + cs], k, patch)
+                wdp = packed_weight_dgrad(weight, cout, cin, k, patch, off, cs)
                 if patch:
-                    wdp = pack_conv_weight(wd, [cpad])
                     dx = ll.conv_gemm([dz], wdp, k * k * cs, k=1, patch_scatter=(k, cs))
                 else:
-                    wdp = pack_conv_weight(wd, [cpad])
                     dx = ll.conv_gemm([dz], wdp, cs, k=k, stride=1, pad=pad)
                 d_srcs.append(dx)
             else:
@@ -133,8 +196,14 @@ class ConvFn(torch.autograd.Function):
             off += cs
         d_w = None
         if ctx.needs_input_grad[0]:
-            dwp = ll.conv_wgrad(srcs, dz, cpad, k=k, stride=s, pad=pad)
-            d_w = unpack_conv_weight(dwp, cpad, chans, k, k, patch=patch)[:cout].to(weight.dtype)
+            dwp = ll.conv_wgrad(srcs, dz, cpad, k=k, stride=s, pad=pad, zeros=zeros_f32)
+            if weight.dtype == torch.float32 and len(chans) == 1 and k == 1 and chans[0] % 64 == 0 and cpad == cout:
+                d_w = dwp.view(weight.shape)                     # packed == OIHW: nothing to unpack
+            else:
+                d_w = torch.empty(weight.shape, dtype=torch.float32, device=dz.device)
+                c4 = list(chans) + [0] * (4 - len(chans))
+                ll.call("ly_unpack_wgrad", dwp, cout, k, k, 1 if patch else 0, c4[0], c4[1], c4[2], c4[3], d_w, 0)
+                d_w = d_w.to(weight.dtype)
         return (d_w, d_bias, d_res, None, None, None, None, *d_srcs)
 
 
@@ -166,15 +235,22 @@ class BnActFn(torch.autograd.Function):
         stats = torch.empty((4, c), dtype=torch.float32, device=dev)  # mean, rstd, scale, shift
         g32, b32 = gamma.detach().float(), beta.detach().float()
         if training:
-            acc = torch.zeros((2, c), dtype=torch.float32, device=dev)
-            ll.call("ly_col_stats", z, ll.pixel_ld(z), m, c, acc[0], acc[1])
-            ll.call("ly_bn_finalize", acc[0], acc[1], c, m, eps, momentum, g32, b32, running_mean, running_var,
-                    stats[0], stats[1], stats[2], stats[3])
+            y = torch.empty_like(z, memory_format=CL)
+            acc = zeros_f32(3 * c, dev)
+            ll.call("ly_bn_stats", z, ll.pixel_ld(z), m, c, acc)
+            ll.call("ly_bn_apply_train", z, ll.pixel_ld(z), m, c, acc, g32, b32, eps, momentum, running_mean,
+                    running_var, stats, ll.ACT[act], y, ll.pixel_ld(y))
+            # the kernel updated the running statistics through raw pointers: bump their version counters so that
+            # caches keyed on them (bn_fold and everything derived from it) see the change
+            for t in (running_mean, running_var):
+                if t is not None:
+                    torch.autograd.graph.increment_version(t)
         else:
             ll.call("ly_bn_fold", c, eps, g32, b32, running_mean, running_var, None, stats[0], stats[1], stats[2],
                     stats[3])
-        y = torch.empty_like(z, memory_format=CL)
-        ll.call("ly_scale_shift_act", z, ll.pixel_ld(z), m, c, stats[2], stats[3], ll.ACT[act], y, ll.pixel_ld(y))
+            y = torch.empty_like(z, memory_format=CL)
+            ll.call("ly_scale_shift_act", z, ll.pixel_ld(z), m, c, stats[2], stats[3], ll.ACT[act], y,
+                    ll.pixel_ld(y))
         ctx.cfg = (act, training)
         ctx.save_for_backward(z, stats)
         return y
@@ -186,7 +262,7 @@ class BnActFn(torch.autograd.Function):
         dy = to_act(dy)
         c = z.shape[1]
         m = _rows(z)
-        s12 = torch.zeros((2, c), dtype=torch.float32, device=z.device)
+        s12 = zeros_f32(2 * c, z.device).view(2, c)
         dz = torch.empty_like(z, memory_format=CL)
         ll.call("ly_bn_act_bwd", dy, ll.pixel_ld(dy), z, ll.pixel_ld(z), m, c, stats[2], stats[3], stats[0],
                 stats[1], ll.ACT[act], 1 if training else 0, s12[0], s12[1], dz, ll.pixel_ld(dz))
@@ -200,7 +276,11 @@ def bn_act(z, bn, act="none", gamma=None, beta=None, rmean=None, rvar=None):
     beta = bn.bias if beta is None else beta
     rmean = bn.running_mean if rmean is None else rmean
     rvar = bn.running_var if rvar is None else rvar
-    mom = 0.1 if bn.momentum is None else bn.momentum
+    if bn.momentum is None:
+        # nn.BatchNorm2d(momentum=None) = cumulative moving average with factor 1/num_batches_tracked, which would
+        # need a host read of the counter per step; LEAD-YOLO sets momentum=0.03 (utils/torch_utils.py:212-221)
+        raise ll.LeadYoloError("BatchNorm2d(momentum=None) (cumulative average) has no kernel in lead_yolo_b200")
+    mom = bn.momentum
     y = BnActFn.apply(z, gamma, beta, rmean, rvar, float(bn.eps), float(mom), act, training)
     if training and bn.num_batches_tracked is not None:
         bn.num_batches_tracked += 1
@@ -210,6 +290,8 @@ def bn_act(z, bn, act="none", gamma=None, beta=None, rmean=None, rvar=None):
 def bn_fold(bn, conv_bias=None, perm=None):
     """(scale, shift) of an eval-mode BatchNorm folded behind a convolution (cached per parameter version)."""
     keys = [bn.weight, bn.bias, bn.running_mean, bn.running_var] + ([conv_bias] if conv_bias is not None else [])
+    if bn.num_batches_tracked is not None:
+        keys.append(bn.num_batches_tracked)     # bumped by every training-mode forward (bn_act)
 
     def build():
         c = bn.weight.numel()
@@ -254,7 +336,7 @@ class StemFn(torch.autograd.Function):
         is_u8, in_scale, cout, wdt = ctx.cfg
         dz = to_act(dz)
         n, _, h, w = img.shape
-        dwk = torch.zeros((48, cout), dtype=torch.float32, device=dz.device)
+        dwk = zeros_f32(48 * cout, dz.device).view(48, cout)
         ll.call("ly_stem_wgrad", img, 1 if is_u8 else 0, n, h, w, cout, dz, ll.pixel_ld(dz), in_scale, dwk)
         return None, dwk.t().reshape(cout, 3, 4, 4).to(wdt), None, None
 
@@ -440,7 +522,7 @@ class RfGenerateFn(torch.autograd.Function):
         dz = to_act(dz).contiguous(memory_format=CL)
         n, c, h, w = x.shape
         dx = ll.empty_cl(n, c, h, w, device=x.device) if ctx.needs_input_grad[0] else None
-        dwgk = torch.zeros_like(wgk) if ctx.needs_input_grad[1] else None
+        dwgk = zeros_f32(wgk.numel(), wgk.device).view(wgk.shape) if ctx.needs_input_grad[1] else None
         ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, dx, c, dwgk)
         dwg = None
         if dwgk is not None:
@@ -476,11 +558,11 @@ class RfGateAttFn(torch.autograd.Function):
         n, kkc, ho, wo = g.shape
         dev = g.device
         dg = torch.empty_like(g, memory_format=CL)
-        dse = torch.zeros((n, c), dtype=torch.float32, device=dev)
+        dse = zeros_f32(n * c, dev).view(n, c)
         datt = torch.empty_like(att)
         ll.call("ly_rf_gate_bwd", da, g, n, ho, wo, c, k, se, ll.pixel_ld(se), att, dg, dse, datt)
         dmaps = torch.empty_like(maps)
-        dwa = torch.zeros(18, dtype=torch.float32, device=dev)
+        dwa = zeros_f32(18, dev)
         ll.call("ly_rf_attention_bwd", datt, att, maps, amax, n, ho, wo, c, k, wa32, dmaps, dwa, dg)
         return dg, dse.to(BF16).view(n, c, 1, 1), dwa.view(1, 2, 3, 3).to(wdt), None
 

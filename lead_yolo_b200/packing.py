@@ -72,6 +72,22 @@ def unpack_conv_weight(wp: torch.Tensor, cout: int, src_channels, kh: int, kw: i
     return out
 
 
+def dgrad_weight_matrix(w: torch.Tensor, coff: int, cs: int, patch: bool) -> torch.Tensor:
+    """Packed bf16 weights of the GEMM that maps dZ to the gradient of source channels [coff, coff+cs) — the host
+    statement of what csrc/weights.cu:pack_dgrad_kernel writes (the tests pin the kernel to it).  The output
+    channel count is zero-padded to a multiple of 8 first (Detect's 18 -> 24)."""
+    cout, _, kh, kw = w.shape
+    cpad = (cout + 7) // 8 * 8
+    ws = torch.nn.functional.pad(w.detach().float()[:, coff:coff + cs], (0, 0, 0, 0, 0, 0, 0, cpad - cout))
+    if patch:
+        wd = ws.permute(2, 3, 1, 0).reshape(kh * kw * cs, cpad, 1, 1)      # rows (ky, kx, c), K = output channel
+    elif kh == 1:
+        wd = ws.transpose(0, 1)
+    else:
+        wd = ws.flip(2, 3).transpose(0, 1)
+    return pack_conv_weight(wd, [cpad])
+
+
 # ---------------------------------------------------------------------------------------------------------
 # Pre-swizzled shared-memory images (csrc/fasternet_block.cu): K-major tiles exactly as tcgen05 reads them, so
 # the kernel fetches all weights of a block with ONE bulk copy.

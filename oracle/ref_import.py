@@ -1,10 +1,11 @@
 """TEST INFRASTRUCTURE ONLY — imports the UNMODIFIED reference (qingqing-zijin/LEAD-YOLO) from
 /root/reference so that its own nn.Modules can act as the oracle in this container.
 
-The reference tree does not exist on the GPU box; nothing in the product path, `-m gpu` tests, smoke()
-or bench.py may import this file at run time there.  It is used by oracle/make_golden.py (fixture
-generation, run here) and by the CPU-only tests that check the restatement in oracle/restate.py against
-the real reference classes.
+/root/reference does not exist on the GPU box.  There, the only copy is the git-ignored `baseline/_ref/` that
+tools/install_ref.py makes (it travels with the snapshot); the drop-in GPU tests and bench.py's reference arm use it
+when present and skip / fall back to the port otherwise.  Nothing in the product path imports this file.  It is also
+used by oracle/make_golden*.py (fixture generation, run in the build container) and by the CPU-only tests that check
+the restatement in oracle/restate.py against the real reference classes.
 
 Shims (harness side only, reference untouched): the reference imports `timm`
 (models/common.py:1167,1170-1171,1408), `IPython` (common.py:24), `matplotlib`/`seaborn`
@@ -17,7 +18,20 @@ import os
 import sys
 import types
 
-REF_ROOT = os.environ.get("LEADYOLO_REFERENCE", "/root/reference")
+def _find_root() -> str:
+    """$LEADYOLO_REFERENCE, else /root/reference (build container), else the git-ignored copy tools/install_ref.py
+    leaves in baseline/_ref (the only one that exists on the GPU box)."""
+    env = os.environ.get("LEADYOLO_REFERENCE")
+    if env:
+        return env
+    here = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref")
+    for cand in ("/root/reference", here):
+        if os.path.isfile(os.path.join(cand, "models", "common.py")):
+            return cand
+    return "/root/reference"
+
+
+REF_ROOT = _find_root()
 
 
 def available() -> bool:

@@ -254,3 +254,147 @@ def model_forward(P, x, ctx, variant="lead", decode=True, upto=None):
         if upto is not None and i == upto:
             return None, None, ys
     raise AssertionError("unreachable")
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Detection loss and post-processing (the callers either side of the module path)
+# ------------------------------------------------------------------------------------------------------------
+HYP_SCRATCH_LOW = {  # data/hyps/hyp.scratch-low.yaml:14-21 (loss part), before the train.py:238-242 scaling
+    "box": 0.05, "cls": 0.5, "cls_pw": 1.0, "obj": 1.0, "obj_pw": 1.0, "anchor_t": 4.0, "fl_gamma": 0.0,
+    "label_smoothing": 0.0}
+
+
+def scaled_hyp(nl=3, nc=1, imgsz=640, hyp=None):
+    """train.py:238-242: box *= 3/nl; cls *= nc/80 * 3/nl; obj *= (imgsz/640)**2 * 3/nl; label_smoothing = 0."""
+    h = dict(HYP_SCRATCH_LOW if hyp is None else hyp)
+    h["box"] *= 3 / nl
+    h["cls"] *= nc / 80 * 3 / nl
+    h["obj"] *= (imgsz / 640) ** 2 * 3 / nl
+    return h
+
+
+def bbox_eiou(box1, box2, eps=1e-7):
+    """bbox_iou(box1, box2, xywh=True, EIoU=True), utils/metrics.py:309-347 with alpha = 1."""
+    (x1, y1, w1, h1), (x2, y2, w2, h2) = box1.chunk(4, -1), box2.chunk(4, -1)
+    b1_x1, b1_x2, b1_y1, b1_y2 = x1 - w1 / 2, x1 + w1 / 2, y1 - h1 / 2, y1 + h1 / 2
+    b2_x1, b2_x2, b2_y1, b2_y2 = x2 - w2 / 2, x2 + w2 / 2, y2 - h2 / 2, y2 + h2 / 2
+    inter = (b1_x2.minimum(b2_x2) - b1_x1.maximum(b2_x1)).clamp(0) * \
+            (b1_y2.minimum(b2_y2) - b1_y1.maximum(b2_y1)).clamp(0)
+    union = w1 * h1 + w2 * h2 - inter + eps
+    iou = inter / (union + eps)
+    cw = b1_x2.maximum(b2_x2) - b1_x1.minimum(b2_x1)
+    ch = b1_y2.maximum(b2_y2) - b1_y1.minimum(b2_y1)
+    c2 = cw ** 2 + ch ** 2 + eps
+    rho2 = ((b2_x1 + b2_x2 - b1_x1 - b1_x2) ** 2 + (b2_y1 + b2_y2 - b1_y1 - b1_y2) ** 2) / 4
+    rho_w2 = ((b2_x2 - b2_x1) - (b1_x2 - b1_x1)) ** 2
+    rho_h2 = ((b2_y2 - b2_y1) - (b1_y2 - b1_y1)) ** 2
+    return iou - (rho2 / c2 + rho_w2 / (cw ** 2 + eps) + rho_h2 / (ch ** 2 + eps))
+
+
+def build_targets(p, targets, anchors, anchor_t):
+    """ComputeLoss.build_targets, utils/loss.py:195-268.  Padding rows (image < 0) are dropped first."""
+    targets = targets[targets[:, 0] >= 0]
+    na, nt = anchors.shape[1], targets.shape[0]
+    tcls, tbox, indices, anch = [], [], [], []
+    gain = torch.ones(7)
+    ai = torch.arange(na).float().view(na, 1).repeat(1, nt)
+    targets = torch.cat((targets.repeat(na, 1, 1), ai[..., None]), 2)
+    g = 0.5
+    off = torch.tensor([[0, 0], [1, 0], [0, 1], [-1, 0], [0, -1]]).float() * g
+    for i in range(len(p)):
+        anc, shape = anchors[i], p[i].shape
+        gain[2:6] = torch.tensor(shape)[[3, 2, 3, 2]]
+        t = targets * gain
+        if nt:
+            r = t[..., 4:6] / anc[:, None]
+            j = torch.max(r, 1 / r).max(2)[0] < anchor_t
+            t = t[j]
+            gxy = t[:, 2:4]
+            gxi = gain[[2, 3]] - gxy
+            j, k = ((gxy % 1 < g) & (gxy > 1)).T
+            l, m = ((gxi % 1 < g) & (gxi > 1)).T
+            j = torch.stack((torch.ones_like(j), j, k, l, m))
+            t = t.repeat((5, 1, 1))[j]
+            offsets = (torch.zeros_like(gxy)[None] + off[:, None])[j]
+        else:
+            t = targets[0]
+            offsets = 0
+        bc, gxy, gwh, a = t.chunk(4, 1)
+        a, (b, c) = a.long().view(-1), bc.long().T
+        gij = (gxy - offsets).long()
+        gi, gj = gij.T
+        gj, gi = gj.clamp(0, shape[2] - 1), gi.clamp(0, shape[3] - 1)
+        indices.append((b, a, gj, gi))
+        tbox.append(torch.cat((gxy - torch.stack((gi, gj), 1), gwh), 1))   # the reference clamps gij in place first
+        anch.append(anc[a])
+        tcls.append(c)
+    return tcls, tbox, indices, anch
+
+
+def compute_loss(p, targets, anchors, hyp, nc=1, balance=(4.0, 1.0, 0.4), cp=1.0, cn=0.0):
+    """ComputeLoss.__call__, utils/loss.py:121-191 (EIoU box term, gr = 1, no focal loss, no autobalance).
+    p: list of (bs, na, ny, nx, nc+5); returns ((lbox+lobj+lcls)*bs, (lbox, lobj, lcls))."""
+    lcls, lbox, lobj = torch.zeros(1), torch.zeros(1), torch.zeros(1)
+    tcls, tbox, indices, anch = build_targets(p, targets, anchors, hyp["anchor_t"])
+    for i, pi in enumerate(p):
+        b, a, gj, gi = indices[i]
+        tobj = torch.zeros(pi.shape[:4], dtype=pi.dtype)
+        n = b.shape[0]
+        if n:
+            pxy, pwh, _, pcls = pi[b, a, gj, gi].split((2, 2, 1, nc), 1)
+            pxy = pxy.sigmoid() * 2 - 0.5
+            pwh = (pwh.sigmoid() * 2) ** 2 * anch[i]
+            iou = bbox_eiou(torch.cat((pxy, pwh), 1), tbox[i]).squeeze(-1)
+            lbox = lbox + (1.0 - iou).mean()
+            tobj[b, a, gj, gi] = iou.detach().clamp(0).type(tobj.dtype)   # duplicates: the last entry wins (CPU)
+            if nc > 1:
+                t = torch.full_like(pcls, cn)
+                t[range(n), tcls[i]] = cp
+                lcls = lcls + F.binary_cross_entropy_with_logits(pcls, t, pos_weight=torch.tensor([hyp["cls_pw"]]))
+        obji = F.binary_cross_entropy_with_logits(pi[..., 4], tobj, pos_weight=torch.tensor([hyp["obj_pw"]]))
+        lobj = lobj + obji * balance[i]
+    lbox, lobj, lcls = lbox * hyp["box"], lobj * hyp["obj"], lcls * hyp["cls"]
+    bs = p[0].shape[0]
+    return (lbox + lobj + lcls) * bs, torch.cat((lbox, lobj, lcls)).detach()
+
+
+def nms_greedy(boxes, scores, iou_thres):
+    """torchvision.ops.nms (CPU kernel nms_kernel_impl): visit boxes by descending score (ties: lower index), suppress
+    those with IoU > threshold against a kept box; fp32 arithmetic in the kernel's order of operations."""
+    order = torch.sort(scores, descending=True, stable=True)[1]
+    b = boxes[order].float()
+    area = (b[:, 2] - b[:, 0]) * (b[:, 3] - b[:, 1])
+    dead = torch.zeros(b.shape[0], dtype=torch.bool)
+    keep = []
+    for i in range(b.shape[0]):
+        if dead[i]:
+            continue
+        keep.append(int(order[i]))
+        w = (torch.minimum(b[i, 2], b[i + 1:, 2]) - torch.maximum(b[i, 0], b[i + 1:, 0])).clamp(min=0)
+        h = (torch.minimum(b[i, 3], b[i + 1:, 3]) - torch.maximum(b[i, 1], b[i + 1:, 1])).clamp(min=0)
+        inter = w * h
+        dead[i + 1:] |= inter / (area[i] + area[i + 1:] - inter) > iou_thres
+    return torch.tensor(keep, dtype=torch.long)
+
+
+def non_max_suppression(prediction, conf_thres=0.25, iou_thres=0.45, agnostic=False, max_det=300):
+    """utils/general.py:884-994, best-class branch (multi_label=False, no labels / masks / merge), without the
+    wall-clock time limit.  Returns a list of (n, 6) tensors (xyxy, conf, cls) per image."""
+    max_wh, max_nms = 7680, 30000
+    xc = prediction[..., 4] > conf_thres
+    out = [torch.zeros((0, 6))] * prediction.shape[0]
+    for xi, x in enumerate(prediction):
+        x = x[xc[xi]].clone()
+        if not x.shape[0]:
+            continue
+        x[:, 5:] *= x[:, 4:5]
+        box = torch.stack((x[:, 0] - x[:, 2] / 2, x[:, 1] - x[:, 3] / 2, x[:, 0] + x[:, 2] / 2, x[:, 1] + x[:, 3] / 2), 1)
+        conf, j = x[:, 5:].max(1, keepdim=True)
+        x = torch.cat((box, conf, j.float()), 1)[conf.view(-1) > conf_thres]
+        if not x.shape[0]:
+            continue
+        x = x[x[:, 4].argsort(descending=True, stable=True)[:max_nms]]
+        c = x[:, 5:6] * (0 if agnostic else max_wh)
+        i = nms_greedy(x[:, :4] + c, x[:, 4], iou_thres)[:max_det]
+        out[xi] = x[i]
+    return out
