@@ -22,12 +22,50 @@ int flat_grid(long M, int V, int block) {
   return (int)g;
 }
 
+// Grid for the REDUCING kernels (statistics, BatchNorm-backward sums): every block ends with 2*C global atomics, so the
+// block count is kept low — at least 16 rows per thread, at most two blocks per SM.
+int flat_grid_reduce(long M, int V, int block) {
+  const int m = V / gcd_i(V, block);
+  long want = (M * V + (long)block * 16 - 1) / ((long)block * 16);
+  const long cap = (long)device_sm_count() * 2;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  long g = (want + m - 1) / m * m;
+  return (int)g;
+}
+
 #define LY_FLAT_SETUP(V)                                                         \
   const long T_ = (long)gridDim.x * blockDim.x;                                  \
   const long t_ = (long)blockIdx.x * blockDim.x + threadIdx.x;                   \
   const int v = (int)(t_ % (V));                                                 \
   const long row0 = t_ / (V);                                                    \
   const long rstep = T_ / (V);
+
+// Block-level reduction of per-thread channel-vector partials a[8], b[8] (thread t owns channel vector (t_ % V)) followed
+// by ONE global atomic per (block, channel, statistic).  The partials go through shared memory and each of the 2*C
+// result slots is summed by one thread over the block's threads that own its vector — no shared-memory atomics, which
+// serialise 256 ways when V is small (CoordAtt's 8-channel matrices: 60 us for a 160 KB tensor).
+__device__ __forceinline__ void block_channel_reduce(const float (&a)[8], const float (&b)[8], int V, long t0,
+                                                     float* __restrict__ out_a, float* __restrict__ out_b) {
+  __shared__ float part[256][17];
+  const int tid = threadIdx.x;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    part[tid][j] = a[j];
+    part[tid][8 + j] = b[j];
+  }
+  __syncthreads();
+  const int C = V * 8;
+  const int first = (int)((V - (t0 % V)) % V);   // block thread index that owns vector 0
+  for (int i = tid; i < 2 * C; i += blockDim.x) {
+    const int which = i >= C, c = which ? i - C : i;
+    const int vc = c >> 3, j = c & 7;
+    float sum = 0.f;
+    for (int tt = (first + vc) % V; tt < (int)blockDim.x; tt += V) sum += part[tt][which * 8 + j];
+    if (which == 0) atomicAdd(&out_a[c], sum);
+    else if (out_b != nullptr) atomicAdd(&out_b[c], sum);
+  }
+}
 
 __device__ __forceinline__ uint4 ld16(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 __device__ __forceinline__ void st16(__nv_bfloat16* p, const uint4& u) { *reinterpret_cast<uint4*>(p) = u; }
@@ -37,10 +75,6 @@ __device__ __forceinline__ void st16(__nv_bfloat16* p, const uint4& u) { *reinte
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) col_stats_kernel(const __nv_bfloat16* __restrict__ x, long ld, long M, int V,
                                                         float* __restrict__ sum, float* __restrict__ sq) {
-  extern __shared__ float sm[];  // [2][C]
-  const int C = V * 8;
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
   LY_FLAT_SETUP(V)
   float s[8], q[8];
 #pragma unroll
@@ -71,16 +105,7 @@ __global__ void __launch_bounds__(256) col_stats_kernel(const __nv_bfloat16* __r
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    atomicAdd(&sm[v * 8 + j], s[j]);
-    atomicAdd(&sm[C + v * 8 + j], q[j]);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    atomicAdd(&sum[i], sm[i]);
-    if (sq != nullptr) atomicAdd(&sq[i], sm[C + i]);
-  }
+  block_channel_reduce(s, q, V, (long)blockIdx.x * blockDim.x, sum, sq);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -160,10 +185,6 @@ __global__ void __launch_bounds__(256) bn_act_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ dy, long lddy, const __nv_bfloat16* __restrict__ z, long ldz, long M, int V,
     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
     const float* __restrict__ rstd, int act, float* __restrict__ s1, float* __restrict__ s2) {
-  extern __shared__ float sm[];
-  const int C = V * 8;
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
   LY_FLAT_SETUP(V)
   float sc[8], sh[8], mu[8], rs[8], a1[8], a2[8];
 #pragma unroll
@@ -183,16 +204,7 @@ __global__ void __launch_bounds__(256) bn_act_bwd_reduce_kernel(
       a2[j] = fmaf(d, (f[j] - mu[j]) * rs[j], a2[j]);
     }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    atomicAdd(&sm[v * 8 + j], a1[j]);
-    atomicAdd(&sm[C + v * 8 + j], a2[j]);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    atomicAdd(&s1[i], sm[i]);
-    atomicAdd(&s2[i], sm[C + i]);
-  }
+  block_channel_reduce(a1, a2, V, (long)blockIdx.x * blockDim.x, s1, s2);
 }
 
 __global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(
@@ -263,7 +275,7 @@ extern "C" int ly_col_stats(const void* x, long ld, long M, int C, float* sum, f
   if (rc) return rc;
   LY_REQUIRE(sum != nullptr, "ly_col_stats: null sum");
   const int V = C / 8;
-  col_stats_kernel<<<flat_grid(M, V, 256), 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
+  col_stats_kernel<<<flat_grid_reduce(M, V, 256), 256, 0, (cudaStream_t)st>>>(
       (const __nv_bfloat16*)x, ld, M, V, sum, sq);
   LY_LAUNCH_CHECK();
   return LY_OK;
@@ -316,7 +328,7 @@ extern "C" int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz,
   LY_REQUIRE(scale && shift && mean && rstd && s1 && s2, "ly_bn_act_bwd: null statistics");
   const int V = C / 8;
   const int grid = flat_grid(M, V, 256);
-  bn_act_bwd_reduce_kernel<<<grid, 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
+  bn_act_bwd_reduce_kernel<<<flat_grid_reduce(M, V, 256), 256, 0, (cudaStream_t)st>>>(
       (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2);
   LY_LAUNCH_CHECK();
   bn_act_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(
@@ -353,16 +365,13 @@ namespace ly {
 
 __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long ld, long M, int V,
                                                        float* __restrict__ acc) {
-  extern __shared__ float sm[];  // [2][C]
   const int C = V * 8;
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
-  __syncthreads();
   LY_FLAT_SETUP(V)
   float s[8], q[8], K[8];
   unpack8(ld16(x + v * 8), K);
 #pragma unroll
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
-  if (blockIdx.x == 0 && threadIdx.x < V) {
+  if (t_ < V) {  // the V threads of row 0 publish the pivot (V may exceed one block)
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[v * 8 + j] = K[j];
   }
@@ -393,16 +402,7 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __re
       q[j] = fmaf(d, d, q[j]);
     }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    atomicAdd(&sm[v * 8 + j], s[j]);
-    atomicAdd(&sm[C + v * 8 + j], q[j]);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    atomicAdd(&acc[C + i], sm[i]);
-    atomicAdd(&acc[2 * C + i], sm[C + i]);
-  }
+  block_channel_reduce(s, q, V, (long)blockIdx.x * blockDim.x, acc + C, acc + 2 * C);
 }
 
 __device__ __forceinline__ void bn_moments(const float* __restrict__ acc, int C, int c, float inv_n, float& mean,
@@ -464,7 +464,7 @@ extern "C" int ly_bn_stats(const void* x, long ld, long M, int C, float* acc, ly
   if (rc) return rc;
   LY_REQUIRE(acc != nullptr, "ly_bn_stats: null accumulator");
   const int V = C / 8;
-  bn_stats_kernel<<<flat_grid(M, V, 256), 256, 2 * C * sizeof(float), (cudaStream_t)st>>>((const __nv_bfloat16*)x, ld,
+  bn_stats_kernel<<<flat_grid_reduce(M, V, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)x, ld,
                                                                                           M, V, acc);
   LY_LAUNCH_CHECK();
   return LY_OK;

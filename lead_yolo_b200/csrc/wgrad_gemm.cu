@@ -132,8 +132,12 @@ __global__ void __launch_bounds__(192) wgrad_gemm_kernel(const __grid_constant__
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, acc);
         tmem_ld_wait();
         if (o < p.Cout) {
+          // 16-byte vector reductions (rows of dWp are 256-byte aligned: Kp is a multiple of 64)
 #pragma unroll
-          for (int j = 0; j < 16; ++j) atomicAdd(drow + c0 + j, __uint_as_float(acc[j]));
+          for (int j = 0; j < 16; j += 4)
+            atomicAdd(reinterpret_cast<float4*>(drow + c0 + j),
+                      make_float4(__uint_as_float(acc[j]), __uint_as_float(acc[j + 1]), __uint_as_float(acc[j + 2]),
+                                  __uint_as_float(acc[j + 3])));
         }
       }
     }
@@ -265,7 +269,8 @@ extern "C" int ly_conv_wgrad(const ly_conv_desc* d, const void* dz, long dz_ld, 
   const int cts = ceil_div(d->Cout, 128);
   const int kgs = ceil_div(p.num_k, 4);
   const int num_tiles = p.tiles_w * p.tiles_h * p.n_img;
-  int split = ceil_div((long)device_sm_count() * 2, (long)cts * kgs);
+  // one CTA per SM (192 KB of shared memory each): exactly one wave, and half the atomic traffic of two
+  int split = ceil_div((long)device_sm_count(), (long)cts * kgs);
   if (split > num_tiles) split = num_tiles;
   if (split < 1) split = 1;
 

@@ -343,9 +343,9 @@ class MLPBlock(nn.Module):
             ll.call("ly_fasternet_block_infer", x, y, n, h, wd, c, img[0], img[0].numel() * 2, img[1], img[2], scale,
                     shift)
             return y
-        t1 = pc._t1(x, fast)
         # u = W1[:, :cp] t1 + W1[:, cp:] x[:, cp:]  ==  [W1[:, :cp] | 0] t1(8-aligned)  +  [0 | W1[:, cp:]] x
         if fast:
+            t1 = pc._t1(x, fast)
             def build():
                 w = w1.weight.detach().float()
                 wa = nn.functional.pad(w[:, :cp], (0, 0, 0, 0, 0, cpp - cp))
@@ -363,6 +363,16 @@ class MLPBlock(nn.Module):
         mask = torch.ones(c, device=w.device, dtype=w.dtype)
         mask[:cp] = 0
         wcat = torch.cat([wa, w * mask.view(1, -1, 1, 1)], 1)
+        if isinstance(bn, nn.BatchNorm2d) and bn.training and bn.running_mean is not None and act == "relu" and \
+                bn.momentum is not None and pc.partial_conv3.weight.dtype == torch.float32:
+            # training: the whole activation path as ONE autograd node (ops.MlpBlockFn)
+            wpad = nn.functional.pad(pc.partial_conv3.weight, (0, 0, 0, 0, 0, cpp - cp, 0, cpp - cp))
+            y = ops.MlpBlockFn.apply(x, wpad, wcat, w2.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var,
+                                     float(bn.eps), float(bn.momentum), cpp)
+            if bn.num_batches_tracked is not None:
+                bn.num_batches_tracked += 1
+            return y
+        t1 = pc._t1(x, fast)
         u = ops.conv([t1, x], wcat, None)
         v = ops.bn_act(u, bn, act)
         return ops.conv([v], w2.weight, None, residual=x)
@@ -551,9 +561,12 @@ class SE(nn.Module):
                                 nn.Linear(ratio, in_channel, bias=False), nn.Sigmoid())
 
     def forward(self, x):
+        return self.from_pooled(ops.GapFn.apply(x))                # (n, c, 1, 1)
+
+    def from_pooled(self, g):
+        """The two Linear layers + sigmoid on an already pooled (n, c, 1, 1) tensor."""
         fast = _fast(self)
         w1, w2 = self.fc[0].weight, self.fc[2].weight
-        g = ops.GapFn.apply(x)                                      # (n, c, 1, 1)
         if fast:
             wp1 = ops.cached([w1], "se1", lambda: pack_conv_weight(w1.detach()[:, :, None, None], None))
             wp2 = ops.cached([w2], "se2", lambda: pack_conv_weight(w2.detach()[:, :, None, None], None))
@@ -588,8 +601,7 @@ class RFCBAMConv(nn.Module):
         n, c, h, w = x.shape
         conv, cbn = self.conv[0], self.conv[1]
         cout = conv.out_channels
-        perm = ops.cached([gen.weight], ("rfperm", c, k), lambda: ops.rf_channel_perm(c, k, x.device)) \
-            if k > 1 else None
+        perm = ops.rf_channel_perm(c, k, x.device) if k > 1 else None
         if fast and c <= 256 and (gen.stride[0] == 1 or (h % 2 == 0 and w % 2 == 0)):
             # two passes over x, no receptive-field matrix in HBM (ly_rfcbam_front_infer)
             gscale, gshift = ops.bn_fold(gbn, None, perm=perm)
@@ -600,7 +612,11 @@ class RFCBAMConv(nn.Module):
                 ops.rf_conv_weight_matrix(conv.weight, k, c, tcl), None))
             scale, shift = ops.bn_fold(cbn, conv.bias)
             return ops.conv_infer([a], wp, cout, scale=scale, shift=shift, act="relu")
-        se = self.se(x)
+        if not fast:
+            z, gap = ops.RfFrontFn.apply(x, gen.weight, k, s)
+            se = self.se.from_pooled(gap)
+        else:
+            se = self.se(x)
         if fast:
             gscale, gshift = ops.bn_fold(gbn, None, perm=perm)
             g = ops.RfGenerateFn.apply(x, gen.weight, k, s, gscale, gshift, "relu")
@@ -609,7 +625,6 @@ class RFCBAMConv(nn.Module):
                 conv.weight.detach().float().permute(0, 2, 3, 1).reshape(cout, k * k * c, 1, 1), None))
             scale, shift = ops.bn_fold(cbn, conv.bias)
             return ops.conv_infer([a], wp, cout, scale=scale, shift=shift, act="relu")
-        z = ops.RfGenerateFn.apply(x, gen.weight, k, s, None, None, "none")
         if perm is None:
             g = ops.bn_act(z, gbn, "relu")
         else:

@@ -20,10 +20,16 @@ CL = torch.channels_last
 # small caches (never stored on nn.Module instances: modules stay picklable / deepcopy-able)
 # ---------------------------------------------------------------------------------------------------------
 _cache = {}
+# A captured training step replays the SAME launches while the parameters change underneath through raw pointers, so
+# everything derived from a parameter has to be recomputed inside the step: train.TrainEngine sets this flag around
+# its forward/backward and `cached` then rebuilds whatever is keyed on a tensor that requires grad.
+BYPASS_PARAM_CACHE = False
 
 
 def cached(key_tensors, tag, builder):
     """Memoise `builder()` on the identity + version of `key_tensors` (inference-time weight packing)."""
+    if BYPASS_PARAM_CACHE and any(t.requires_grad for t in key_tensors):
+        return builder()
     key = (tag,) + tuple(id(t) for t in key_tensors)
     ver = tuple((t._version, t.data_ptr()) for t in key_tensors)
     hit = _cache.get(key)
@@ -412,6 +418,18 @@ class UpsampleCatFn(torch.autograd.Function):
         return (None, *grads)
 
 
+def _gap_mean(x):
+    """(N, C, 1, 1) bf16 mean over H*W of an NHWC activation."""
+    n, c, h, w = x.shape
+    if c <= 512:
+        sums = torch.empty((n, c), dtype=torch.float32, device=x.device)
+        ll.call("ly_rf_gap_sum", x, ll.pixel_ld(x), n, h * w, c, sums)       # zeroes, then sums (fp32)
+        return (sums * (1.0 / (h * w))).to(BF16).view(n, c, 1, 1)
+    out = ll.empty_cl(n, c, 1, 1, device=x.device)
+    ll.call("ly_gap", x, ll.pixel_ld(x), n, h * w, c, out, c)
+    return out
+
+
 class GapFn(torch.autograd.Function):
     """Global average pool -> (N, C, 1, 1) bf16."""
 
@@ -419,15 +437,13 @@ class GapFn(torch.autograd.Function):
     def forward(ctx, x):
         x = to_act(x)
         n, c, h, w = x.shape
-        out = ll.empty_cl(n, c, 1, 1, device=x.device)
-        ll.call("ly_gap", x, ll.pixel_ld(x), n, h * w, c, out, c)
         ctx.shape = (n, c, h, w)
-        return out
+        return _gap_mean(x)
 
     @staticmethod
     def backward(ctx, d):
         n, c, h, w = ctx.shape
-        return (d.float() / float(h * w)).to(BF16).expand(n, c, h, w)
+        return (d.float() / float(h * w)).to(BF16).expand(n, c, h, w).contiguous(memory_format=CL)
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -493,10 +509,14 @@ def rf_pack_generate_weight(wg, c, k):
 
 
 def rf_channel_perm(c, k, device):
-    """index p with G-column (t*c + ch) <- reference channel (ch*k*k + t)."""
-    t = torch.arange(k * k, device=device).view(-1, 1)
-    ch = torch.arange(c, device=device).view(1, -1)
-    return (ch * (k * k) + t).reshape(-1)
+    """index p with G-column (t*c + ch) <- reference channel (ch*k*k + t) (a constant per (c, k, device))."""
+    key = ("rfperm", c, k, str(device))
+    hit = _cache.get(key)
+    if hit is None:
+        t = torch.arange(k * k, device=device).view(-1, 1)
+        ch = torch.arange(c, device=device).view(1, -1)
+        hit = _cache[key] = (ch * (k * k) + t).reshape(-1)
+    return hit
 
 
 class RfGenerateFn(torch.autograd.Function):
@@ -528,6 +548,114 @@ class RfGenerateFn(torch.autograd.Function):
         if dwgk is not None:
             dwg = dwgk.permute(2, 0, 1).reshape(c * k * k, 1, k, k).to(wdt)
         return dx, dwg, None, None, None, None, None
+
+
+class RfFrontFn(torch.autograd.Function):
+    """(z, gap) = (receptive-field features of x, SE average pool of x) — rfa.py:113-115 and 80,90 — as ONE autograd
+    node, so that x receives ONE gradient: the pooling gradient rides into the feature kernel's input-gradient pass
+    (`extra`) instead of being expanded to a full tensor and added by autograd."""
+
+    @staticmethod
+    def forward(ctx, x, wg, k, s):
+        x = to_act(x)
+        n, c, h, w = x.shape
+        ho, wo = rf_out_size(h, w, k, s)
+        wgk = rf_pack_generate_weight(wg, c, k)
+        g = ll.empty_cl(n, k * k * c, ho, wo, device=x.device)
+        ll.call("ly_rf_generate", x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, None, ll.ACT["none"], g)
+        gap = _gap_mean(x)
+        ctx.save_for_backward(x, wgk)
+        ctx.cfg = (k, s, ho, wo, wg.dtype)
+        return g, gap
+
+    @staticmethod
+    def backward(ctx, dz, dgap):
+        x, wgk = ctx.saved_tensors
+        k, s, ho, wo, wdt = ctx.cfg
+        dz = to_act(dz).contiguous(memory_format=CL)
+        n, c, h, w = x.shape
+        extra = None
+        if dgap is not None:
+            extra = (dgap.float() * (1.0 / (h * w))).reshape(n, c).contiguous()
+        dx = ll.empty_cl(n, c, h, w, device=x.device) if ctx.needs_input_grad[0] else None
+        dwgk = zeros_f32(wgk.numel(), wgk.device).view(wgk.shape) if ctx.needs_input_grad[1] else None
+        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, extra, dx, c, dwgk)
+        dwg = None
+        if dwgk is not None:
+            dwg = dwgk.permute(2, 0, 1).reshape(c * k * k, 1, k, k).to(wdt)
+        return dx, dwg, None, None
+
+
+class MlpBlockFn(torch.autograd.Function):
+    """FasterNet block body on the activation path (models/common.py:1432-1437, 1478-1482):
+        t1 = conv3x3(x[:, :cpp], Wp);  u = W1 [t1 | x];  v = relu(BN(u));  y = x + W2 v
+    with every weight-side tensor prepared by the caller under autograd (wp = partial conv padded to the 8-aligned
+    slice, wcat = [W1[:, :cp] padded | W1 with its first cp columns zeroed]).  One node instead of a chain: x gets ONE
+    gradient, written in NHWC — the slice, the two convolutions reading x and the residual would otherwise be summed by
+    autograd through a zero-filled NCHW tensor and two extra adds."""
+
+    @staticmethod
+    def forward(ctx, x, wp, wcat, w2, gamma, beta, rmean, rvar, eps, momentum, cpp):
+        x = to_act(x)
+        n, c, h, w = x.shape
+        m = n * h * w
+        hid = wcat.shape[0]
+        xs = x[:, :cpp]
+        t1 = ll.conv_gemm([xs], packed_weight(wp, [cpp], 3, False), cpp, k=3, stride=1, pad=1)
+        u = ll.conv_gemm([t1, x], packed_weight(wcat, [cpp, c], 1, False), hid)
+        v = torch.empty_like(u, memory_format=CL)
+        stats = torch.empty((4, hid), dtype=torch.float32, device=x.device)
+        acc = zeros_f32(3 * hid, x.device)
+        ll.call("ly_bn_stats", u, ll.pixel_ld(u), m, hid, acc)
+        ll.call("ly_bn_apply_train", u, ll.pixel_ld(u), m, hid, acc, gamma.detach().float(), beta.detach().float(), eps,
+                momentum, rmean, rvar, stats, ll.ACT["relu"], v, ll.pixel_ld(v))
+        for t in (rmean, rvar):
+            torch.autograd.graph.increment_version(t)
+        y = ll.conv_gemm([v], packed_weight(w2, [hid], 1, False), c, residual=x)
+        ctx.save_for_backward(x, t1, u, v, stats, wp, wcat, w2)
+        ctx.cpp = cpp
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, t1, u, v, stats, wp, wcat, w2 = ctx.saved_tensors
+        cpp = ctx.cpp
+        dy = to_act(dy)
+        n, c, h, w = x.shape
+        m = n * h * w
+        hid = wcat.shape[0]
+        dev = x.device
+        # mlp.3: dv, dW2
+        dv = ll.conv_gemm([dy], packed_weight_dgrad(w2, c, hid, 1, False, 0, hid), hid)
+        d_w2 = _wgrad_oihw([v], dy, w2, [hid], 1, 1, 0, False)
+        # BatchNorm + ReLU
+        s12 = zeros_f32(2 * hid, dev).view(2, hid)
+        du = torch.empty_like(u, memory_format=CL)
+        ll.call("ly_bn_act_bwd", dv, ll.pixel_ld(dv), u, ll.pixel_ld(u), m, hid, stats[2], stats[3], stats[0], stats[1],
+                ll.ACT["relu"], 1, s12[0], s12[1], du, ll.pixel_ld(du))
+        # mlp.0: gradient of the x source lands on top of the residual gradient; t1 source separately
+        dx = ll.conv_gemm([du], packed_weight_dgrad(wcat, hid, cpp + c, 1, False, cpp, c), c, residual=dy)
+        dt1 = ll.conv_gemm([du], packed_weight_dgrad(wcat, hid, cpp + c, 1, False, 0, cpp), cpp)
+        d_wcat = _wgrad_oihw([t1, x], du, wcat, [cpp, c], 1, 1, 0, False)
+        # partial conv: accumulate into the first cpp channels of dx in place
+        dxs = dx[:, :cpp]
+        ll.conv_gemm([dt1], packed_weight_dgrad(wp, cpp, cpp, 3, False, 0, cpp), cpp, k=3, stride=1, pad=1, residual=dxs,
+                     out=dxs)
+        d_wp = _wgrad_oihw([x[:, :cpp]], dt1, wp, [cpp], 3, 1, 1, False)
+        return dx, d_wp, d_wcat, d_w2, s12[1], s12[0], None, None, None, None, None
+
+
+def _wgrad_oihw(srcs, dz, weight, chans, k, s, pad, patch):
+    """fp32 OIHW weight gradient of conv(cat(srcs), weight) given dz (the tail of ConvFn.backward)."""
+    cout = weight.shape[0]
+    cpad = (cout + 7) // 8 * 8
+    dwp = ll.conv_wgrad(srcs, dz, cpad, k=k, stride=s, pad=pad, zeros=zeros_f32)
+    if len(chans) == 1 and k == 1 and chans[0] % 64 == 0 and cpad == cout:
+        return dwp.view(weight.shape).to(weight.dtype)
+    d_w = torch.empty(weight.shape, dtype=torch.float32, device=dz.device)
+    c4 = list(chans) + [0] * (4 - len(chans))
+    ll.call("ly_unpack_wgrad", dwp, cout, k, k, 1 if patch else 0, c4[0], c4[1], c4[2], c4[3], d_w, 0)
+    return d_w.to(weight.dtype)
 
 
 class RfGateAttFn(torch.autograd.Function):

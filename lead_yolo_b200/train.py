@@ -140,12 +140,14 @@ class TrainEngine:
     # -- the step, as enqueued work
     def _forward_backward(self):
         ops.arena_begin(self.device)
+        ops.BYPASS_PARAM_CACHE = True     # replayed launches must re-derive everything that depends on a parameter
         try:
             raw = self.model(self.images)
             loss, _ = self.compute_loss(raw, self.targets)
             total = loss * float(self.world)                      # train.py:321-322
             grads = torch.autograd.grad(total, self.params, allow_unused=False)
         finally:
+            ops.BYPASS_PARAM_CACHE = False
             ops.arena_end()
         torch._foreach_copy_(self.grad_views, list(grads))
         return loss.detach()
