@@ -97,18 +97,25 @@ int ly_bn_fold(int C, float eps, const float* gamma, const float* beta, const fl
 /* y = act(x*scale[c] + shift[c]) */
 int ly_scale_shift_act(const void* x, long ldx, long M, int C, const float* scale, const float* shift, int act,
                        void* y, long ldy, ly_stream_t stream);
-/* Backward of y = act(scale*z + shift): s1 += Σ dact, s2 += Σ dact*xhat (= dbeta, dgamma); dz per BatchNorm
- * backward (training: batch statistics; otherwise dz = scale*dact).  s1/s2 must be zeroed by the caller. */
+/* Backward of y = act(scale*z + shift): s1 = Σ dact, s2 = Σ dact*xhat (= dbeta, dgamma); dz per BatchNorm
+ * backward (training: batch statistics; otherwise dz = scale*dact).
+ * parts == NULL: the sums are ADDED into s1/s2 with float atomics (zero them first; order-dependent rounding).
+ * parts != NULL: fp32 scratch [ly_reduce_blocks(M, C)][2*C]; every block stores its partial sums and a small second
+ * launch adds them in block order into s1/s2 (written, no zeroing needed) — bit-reproducible, which matters because
+ * s1/n and s2/n are subtracted from EVERY element of dz. */
+int ly_reduce_blocks(long M, int C);
 int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz, long M, int C, const float* scale,
                   const float* shift, const float* mean, const float* rstd, int act, int training, float* s1,
-                  float* s2, void* dz, long lddz, ly_stream_t stream);
+                  float* s2, float* parts, void* dz, long lddz, ly_stream_t stream);
 /* dz = dy * act'(.) with the derivative taken from the activation OUTPUT y (none / relu / sigmoid). */
 int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, long ldy, long M, int C, int act, void* dz,
                         long lddz, ly_stream_t stream);
 
 /* Training-mode BatchNorm2d forward in two launches (nn.BatchNorm2d at the sites listed above, batch statistics):
- * ly_bn_stats accumulates, per channel, the sums about a pivot K = x[0][c] into acc = fp32 [3][C] = K | Σ(x-K) | Σ(x-K)²
- * (zero acc first; shifted sums keep the variance from cancelling when |mean| >> std); ly_bn_apply_train derives
+ * ly_bn_stats accumulates, per channel, the sums about a pivot K = x[0][c] into acc = [C] fp32 K | [C] int64 Σ(x-K)·2^24
+ * | [C] int64 Σ(x-K)²·2^20, i.e. 5*C floats of space (zero acc first).  Shifted sums keep the variance from cancelling
+ * when |mean| >> std; the cross-block step is 64-bit fixed point, so the statistics — and the training forward — are
+ * bit-reproducible from run to run (valid for Σ(x-K)² < 8e12).  ly_bn_apply_train derives
  * mean / biased variance from acc, writes y = act(gamma*(z-mean)*rstd + beta), saves stats = fp32 [4][C]
  * (mean, rstd, scale, shift) for ly_bn_act_bwd and updates running_mean / running_var (unbiased variance, `momentum`)
  * in place when they are non-NULL. */
@@ -254,8 +261,15 @@ int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int C, int s, i
                    const void* shift, const float* se, const float* att, void* A, ly_stream_t stream);
 /* gap_sum[n][c] = sum_hw x (zeroed by the call);  se = sigmoid(W2 relu(W1 gap_sum/HW)), att = sigmoid(conv3x3(maps)). */
 int ly_rf_gap_sum(const void* x, long ldx, int N, int HW, int C, float* gap_sum, ly_stream_t stream);
+/* Training-path average pool of rfa.SE (models/rfa.py:80,90), bit-reproducible: out bf16 [N][C] = mean over HW;
+ * parts: fp32 scratch [LY_GAP_PARTS][N][C] (per-block partial sums, added in index order).  C <= 512. */
+#define LY_GAP_PARTS 16
+int ly_gap_mean(const void* x, long ldx, int N, int HW, int C, float* parts, void* out, ly_stream_t stream);
 int ly_rf_se_att(const float* gap_sum, int N, int C, int HW, const float* w1, const float* w2, int R, const float* maps,
                  int HK, int WK, const float* wa, float* se, float* att, ly_stream_t stream);
+/* dse: fp32 [LY_RF_GATE_PARTS][N][C] per-block partial sums, WRITTEN (not accumulated); the gradient of the SE gate is
+ * their sum over the first axis in index order (deterministic — the value is broadcast over every pixel afterwards). */
+#define LY_RF_GATE_PARTS 16
 int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int wo, int C, int k, const void* se, long ldse,
                    const float* att, void* dG, float* dse, float* datt, ly_stream_t stream);
 int ly_rf_attention_bwd(const float* datt, const float* att, const float* maps, const int16_t* amax, int N, int ho,

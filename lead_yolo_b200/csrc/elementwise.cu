@@ -46,7 +46,8 @@ int flat_grid_reduce(long M, int V, int block) {
 // result slots is summed by one thread over the block's threads that own its vector — no shared-memory atomics, which
 // serialise 256 ways when V is small (CoordAtt's 8-channel matrices: 60 us for a 160 KB tensor).
 __device__ __forceinline__ void block_channel_reduce(const float (&a)[8], const float (&b)[8], int V, long t0,
-                                                     float* __restrict__ out_a, float* __restrict__ out_b) {
+                                                     float* __restrict__ out_a, float* __restrict__ out_b,
+                                                     float* __restrict__ parts = nullptr) {
   __shared__ float part[256][17];
   const int tid = threadIdx.x;
 #pragma unroll
@@ -62,8 +63,47 @@ __device__ __forceinline__ void block_channel_reduce(const float (&a)[8], const 
     const int vc = c >> 3, j = c & 7;
     float sum = 0.f;
     for (int tt = (first + vc) % V; tt < (int)blockDim.x; tt += V) sum += part[tt][which * 8 + j];
-    if (which == 0) atomicAdd(&out_a[c], sum);
+    if (parts != nullptr) parts[(long)blockIdx.x * 2 * C + i] = sum;   // ordered finalize follows (deterministic)
+    else if (which == 0) atomicAdd(&out_a[c], sum);
     else if (out_b != nullptr) atomicAdd(&out_b[c], sum);
+  }
+}
+
+// s1 | s2 = Σ_b parts[b][0..2C) in block order
+__global__ void ordered_finalize_kernel(const float* __restrict__ parts, int B, int C, float* __restrict__ s1,
+                                        float* __restrict__ s2) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 2 * C) return;
+  float a = 0.f;
+  for (int b = 0; b < B; ++b) a += parts[(long)b * 2 * C + i];
+  if (i < C) s1[i] = a;
+  else s2[i - C] = a;
+}
+
+// Same, but the block sums are added as 64-bit FIXED-POINT integers (value * 2^fa / 2^fb): integer addition is
+// associative, so the total does not depend on the order in which the blocks arrive — training-mode BatchNorm
+// statistics, and with them the whole forward pass, are bit-reproducible from run to run.  Per-thread and per-block
+// partial sums are fp32 in a fixed order; only the cross-block step is fixed point.
+__device__ __forceinline__ void block_channel_reduce_fx(const float (&a)[8], const float (&b)[8], int V, long t0,
+                                                        long long* __restrict__ out_a, long long* __restrict__ out_b,
+                                                        float scale_a, float scale_b) {
+  __shared__ float part[256][17];
+  const int tid = threadIdx.x;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    part[tid][j] = a[j];
+    part[tid][8 + j] = b[j];
+  }
+  __syncthreads();
+  const int C = V * 8;
+  const int first = (int)((V - (t0 % V)) % V);
+  for (int i = tid; i < 2 * C; i += blockDim.x) {
+    const int which = i >= C, c = which ? i - C : i;
+    const int vc = c >> 3, j = c & 7;
+    float sum = 0.f;
+    for (int tt = (first + vc) % V; tt < (int)blockDim.x; tt += V) sum += part[tt][which * 8 + j];
+    const long long q = __double2ll_rn((double)sum * (double)(which ? scale_b : scale_a));
+    atomicAdd(reinterpret_cast<unsigned long long*>(which ? &out_b[c] : &out_a[c]), (unsigned long long)q);
   }
 }
 
@@ -184,7 +224,8 @@ __global__ void __launch_bounds__(256) scale_shift_act_kernel(const __nv_bfloat1
 __global__ void __launch_bounds__(256) bn_act_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ dy, long lddy, const __nv_bfloat16* __restrict__ z, long ldz, long M, int V,
     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
-    const float* __restrict__ rstd, int act, float* __restrict__ s1, float* __restrict__ s2) {
+    const float* __restrict__ rstd, int act, float* __restrict__ s1, float* __restrict__ s2,
+    float* __restrict__ parts) {
   LY_FLAT_SETUP(V)
   float sc[8], sh[8], mu[8], rs[8], a1[8], a2[8];
 #pragma unroll
@@ -204,7 +245,7 @@ __global__ void __launch_bounds__(256) bn_act_bwd_reduce_kernel(
       a2[j] = fmaf(d, (f[j] - mu[j]) * rs[j], a2[j]);
     }
   }
-  block_channel_reduce(a1, a2, V, (long)blockIdx.x * blockDim.x, s1, s2);
+  block_channel_reduce(a1, a2, V, (long)blockIdx.x * blockDim.x, s1, s2, parts);
 }
 
 __global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(
@@ -316,9 +357,14 @@ extern "C" int ly_scale_shift_act(const void* x, long ldx, long M, int C, const 
   return LY_OK;
 }
 
+extern "C" int ly_reduce_blocks(long M, int C) {
+  if (M <= 0 || C <= 0 || C % 8 != 0) return -1;
+  return flat_grid_reduce(M, C / 8, 256);
+}
+
 extern "C" int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz, long M, int C, const float* scale,
                              const float* shift, const float* mean, const float* rstd, int act, int training,
-                             float* s1, float* s2, void* dz, long lddz, ly_stream_t st) {
+                             float* s1, float* s2, float* parts, void* dz, long lddz, ly_stream_t st) {
   int rc = check_mat(dy, lddy, M, C, "ly_bn_act_bwd(dy)");
   if (rc) return rc;
   rc = check_mat(z, ldz, M, C, "ly_bn_act_bwd(z)");
@@ -328,9 +374,14 @@ extern "C" int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz,
   LY_REQUIRE(scale && shift && mean && rstd && s1 && s2, "ly_bn_act_bwd: null statistics");
   const int V = C / 8;
   const int grid = flat_grid(M, V, 256);
-  bn_act_bwd_reduce_kernel<<<flat_grid_reduce(M, V, 256), 256, 0, (cudaStream_t)st>>>(
-      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2);
+  const int rgrid = flat_grid_reduce(M, V, 256);
+  bn_act_bwd_reduce_kernel<<<rgrid, 256, 0, (cudaStream_t)st>>>(
+      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2, parts);
   LY_LAUNCH_CHECK();
+  if (parts != nullptr) {
+    ordered_finalize_kernel<<<ceil_div(2 * C, 256), 256, 0, (cudaStream_t)st>>>(parts, rgrid, C, s1, s2);
+    LY_LAUNCH_CHECK();
+  }
   bn_act_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(
       (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2,
       1.f / (float)M, training, (__nv_bfloat16*)dz, lddz);
@@ -359,9 +410,14 @@ extern "C" int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, lon
 // Training-mode BatchNorm in two launches (statistics, then normalise + activation) with the finalize step folded
 // into the second one.  The sums are taken about a per-channel pivot K = x[0][c] (shifted-data algorithm):
 // var = Σ(x-K)²/n − (Σ(x-K)/n)² does not cancel when |mean| >> std, which the plain E[x²] − mean² form does.
-// acc: fp32 [3][C] = K | Σ(x-K) | Σ(x-K)²; the two sum rows are accumulated with atomics (zero them first).
+// acc: [C] fp32 pivot K | [C] int64 Σ(x-K)·2^24 | [C] int64 Σ(x-K)²·2^20  (5*C floats of space, zeroed by the caller).
 // ------------------------------------------------------------------------------------------------
 namespace ly {
+
+// fixed-point scales of the two sums: |Σ(x-K)| < 5e11 and Σ(x-K)² < 8e12 are representable (activations up to the
+// thousands on 1.6 M pixels); resolutions 6e-8 and 1e-6
+constexpr float kBnScale1 = 16777216.f;   // 2^24
+constexpr float kBnScale2 = 1048576.f;    // 2^20
 
 __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long ld, long M, int V,
                                                        float* __restrict__ acc) {
@@ -402,14 +458,17 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __re
       q[j] = fmaf(d, d, q[j]);
     }
   }
-  block_channel_reduce(s, q, V, (long)blockIdx.x * blockDim.x, acc + C, acc + 2 * C);
+  long long* fx = reinterpret_cast<long long*>(acc + C);
+  block_channel_reduce_fx(s, q, V, (long)blockIdx.x * blockDim.x, fx, fx + C, kBnScale1, kBnScale2);
 }
 
 __device__ __forceinline__ void bn_moments(const float* __restrict__ acc, int C, int c, float inv_n, float& mean,
                                            float& var) {
-  const float d = acc[C + c] * inv_n;
+  const long long* fx = reinterpret_cast<const long long*>(acc + C);
+  const double s1 = (double)fx[c] * (1.0 / (double)kBnScale1), s2 = (double)fx[C + c] * (1.0 / (double)kBnScale2);
+  const float d = (float)(s1 * (double)inv_n);
   mean = acc[c] + d;
-  var = fmaxf(acc[2 * C + c] * inv_n - d * d, 0.f);
+  var = fmaxf((float)(s2 * (double)inv_n) - d * d, 0.f);
 }
 
 __global__ void __launch_bounds__(256) bn_apply_train_kernel(

@@ -589,6 +589,7 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
 // (csrc/rf_generate_tc.cu): SE channel sums, SE gate + spatial attention, gating of the stored features.
 namespace ly {
 // block = (Vp lanes over 16-byte channel vectors) x (256 / Vp pixel rows); 4 independent loads in flight per thread
+template <bool PARTS>
 __global__ void __launch_bounds__(256) rf_gap_sum_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int HW, int V,
                                                          int Vp, float* __restrict__ gap_sum) {
   __shared__ float red[256 * 8];
@@ -628,8 +629,18 @@ __global__ void __launch_bounds__(256) rf_gap_sum_kernel(const __nv_bfloat16* __
     const int e = i % 8, vv = i / 8;
     float a = 0.f;
     for (int r = 0; r < rows; ++r) a += red[e * 256 + r * Vp + vv];
-    atomicAdd(&gap_sum[(long)n * V * 8 + vv * 8 + e], a);
+    if (PARTS) gap_sum[((long)blockIdx.x * gridDim.y + n) * V * 8 + vv * 8 + e] = a;   // this block's partial
+    else atomicAdd(&gap_sum[(long)n * V * 8 + vv * 8 + e], a);
   }
+}
+
+// out[n][c] = bf16( (Σ_b parts[b][n][c]) / HW ), the partials added in index order
+__global__ void gap_finish_kernel(const float* __restrict__ parts, int B, long NC, float inv, __nv_bfloat16* __restrict__ out) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= NC) return;
+  float a = 0.f;
+  for (int b = 0; b < B; ++b) a += parts[(long)b * NC + i];
+  out[i] = __float2bfloat16(a * inv);
 }
 }  // namespace ly
 
@@ -646,8 +657,27 @@ extern "C" int ly_rf_gap_sum(const void* x, long ldx, int N, int HW, int C, floa
   const long cap = ceil_div(8L * device_sm_count(), (long)N);
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
-  rf_gap_sum_kernel<<<dim3((unsigned)bx, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, HW, V, Vp,
-                                                                        gap_sum);
+  rf_gap_sum_kernel<false><<<dim3((unsigned)bx, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, HW, V, Vp,
+                                                                               gap_sum);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+// Deterministic global average pool for the training path (rfa.SE, models/rfa.py:80,90): LY_GAP_PARTS blocks per image
+// store their partial sums, a second launch adds them in order and writes the bf16 mean [N][C].
+extern "C" int ly_gap_mean(const void* x, long ldx, int N, int HW, int C, float* parts, void* out, ly_stream_t st) {
+  LY_REQUIRE(x && parts && out && C % 8 == 0 && C <= 512 && ldx % 8 == 0 && ldx >= C && N > 0 && HW > 0,
+             "ly_gap_mean: bad args");
+  cudaStream_t stream = (cudaStream_t)st;
+  const int V = C / 8;
+  int Vp = 1;
+  while (Vp < V) Vp *= 2;
+  rf_gap_sum_kernel<true><<<dim3(LY_GAP_PARTS, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, HW, V, Vp,
+                                                                              parts);
+  LY_LAUNCH_CHECK();
+  const long NC = (long)N * C;
+  gap_finish_kernel<<<ceil_div(NC, 256), 256, 0, stream>>>(parts, LY_GAP_PARTS, NC, 1.f / (float)HW,
+                                                           (__nv_bfloat16*)out);
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

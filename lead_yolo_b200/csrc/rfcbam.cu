@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(256) rf_gate_kernel(const __nv_bfloat16* __res
 
 // ------------------------------------------------------------------------------------------------
 // Backward of the gating: given dA, G, se, att ->
-//   dG1 = dA*se*att (written to dG), dse[n,c] += Σ dA*G*att, datt[pos] = Σ_c dA*G*se.
+//   dG1 = dA*se*att (written to dG), dse[part][n,c] = this block's share of Σ dA*G*att, datt[pos] = Σ_c dA*G*se.
 // grid = (blocks per image, N); each warp strides over the (m, t) pairs of its image.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) rf_gate_bwd_kernel(const __nv_bfloat16* __restrict__ dA,
@@ -214,13 +214,26 @@ __global__ void __launch_bounds__(256) rf_gate_bwd_kernel(const __nv_bfloat16* _
     da_att = warp_sum(da_att);
     if (lane == 0) datt[pos] = da_att;
   }
+  // Deterministic reduction: the eight warps of the block are summed in warp order through shared memory and the block
+  // STORES its partial at dse[blockIdx.x][n][c]; the caller adds the gridDim.x partials in order.  (dse is broadcast back
+  // over all pixels of the image after a bf16 rounding: with order-dependent float atomics a rounding flip of one value
+  // shifted a whole channel's input gradient from run to run.)
+  __shared__ float red[8][512];
+  const int warp = threadIdx.x >> 5;
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
     const int v = lane + q * 32;
     if (v < V) {
 #pragma unroll
-      for (int e = 0; e < 8; ++e) atomicAdd(&dse[(long)n * C + v * 8 + e], ds[q][e]);
+      for (int e = 0; e < 8; ++e) red[warp][v * 8 + e] = ds[q][e];
     }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f;
+#pragma unroll
+    for (int w8 = 0; w8 < 8; ++w8) a += red[w8][c];
+    dse[((long)blockIdx.x * gridDim.y + n) * C + c] = a;
   }
 }
 
@@ -471,11 +484,8 @@ extern "C" int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int 
   LY_REQUIRE(dA && G && se && att && dG && dse && datt && C % 8 == 0 && C <= 512, "ly_rf_gate_bwd: bad args");
   const int V = C / 8, KK = k * k;
   const long per_img = (long)ho * wo * KK;
-  int bx = ceil_div(per_img, 8 * 16);  // 8 warps per block, ~16 rows per warp
-  const int cap = ceil_div((long)device_sm_count() * 8, N);
-  if (bx > cap) bx = cap;
-  if (bx < 1) bx = 1;
-  dim3 grid(bx, N);
+  (void)per_img;
+  dim3 grid(LY_RF_GATE_PARTS, N);   // fixed: the caller sizes dse as [LY_RF_GATE_PARTS][N][C]
   rf_gate_bwd_kernel<<<grid, 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)dA, (const __nv_bfloat16*)G, KK, k, V,
                                                         ho, wo, (const __nv_bfloat16*)se, ldse, att,
                                                         (__nv_bfloat16*)dG, dse, datt);

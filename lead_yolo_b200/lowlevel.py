@@ -12,7 +12,7 @@ from ._lib import ConvDesc, LeadYoloError, check, lib, ptr, stream_ptr
 CL = torch.channels_last
 COUNT = [0]        # kernels launched through the C-ABI (bench.py: gpu_launches)
 PROFILE = None     # when a list: (entry point, start event, end event, algorithmic bytes, flops) per call
-_LAUNCHES = {"ly_yolo_loss_fwd": 4, "ly_yolo_loss_bwd": 2, "ly_detect_nms": 2, "ly_rfcbam_front_infer": 3, "ly_bn_act_bwd": 2, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 2}
+_LAUNCHES = {"ly_gap_mean": 2, "ly_yolo_loss_fwd": 4, "ly_yolo_loss_bwd": 2, "ly_detect_nms": 2, "ly_rfcbam_front_infer": 3, "ly_bn_act_bwd": 3, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 2}
 
 
 class _Prof:
@@ -149,7 +149,7 @@ _SIGS = {
     "ly_bn_finalize": "ppilffpppppppp",
     "ly_bn_fold": "ifppppppppp",
     "ly_scale_shift_act": "pllippipl",
-    "ly_bn_act_bwd": "plpllippppiipppl",
+    "ly_bn_act_bwd": "plpllippppiippppl",
     "ly_bn_stats": "pllip",
     "ly_bn_apply_train": "pllipppffpppipl",
     "ly_pack_weight": "piiiiiiiip",
@@ -184,6 +184,7 @@ _SIGS = {
     "ly_rf_tc_stats": "pliiiiiiippp",
     "ly_rf_tc_apply": "pliiiiiiippppp",
     "ly_rf_gap_sum": "pliiip",
+    "ly_gap_mean": "pliiipp",
     "ly_rf_se_att": "piiippipiippp",
     "ly_rf_gate_bwd": "ppiiiiiplpppp",
     "ly_rf_attention_bwd": "ppppiiiiipppp",
@@ -215,6 +216,14 @@ def call(name, *args):
         nbytes = float(sum(a.numel() * a.element_size() for a in args if isinstance(a, torch.Tensor)))
     with _Prof(name, nbytes, 0.0):
         check(fn(*conv, torch.cuda.current_stream().cuda_stream), name)
+
+
+def reduce_blocks(m, c):
+    """Blocks the library's reducing kernels use for an [m][c] matrix (size of their partial-sum scratch)."""
+    fn = lib().ly_reduce_blocks
+    fn.argtypes = [C.c_long, C.c_int]
+    fn.restype = C.c_int
+    return int(fn(m, c))
 
 
 def conv_wgrad(srcs, dz, cout, k=1, stride=1, pad=0, zeros=None):

@@ -242,7 +242,7 @@ class BnActFn(torch.autograd.Function):
         g32, b32 = gamma.detach().float(), beta.detach().float()
         if training:
             y = torch.empty_like(z, memory_format=CL)
-            acc = zeros_f32(3 * c, dev)
+            acc = zeros_f32(5 * c, dev)
             ll.call("ly_bn_stats", z, ll.pixel_ld(z), m, c, acc)
             ll.call("ly_bn_apply_train", z, ll.pixel_ld(z), m, c, acc, g32, b32, eps, momentum, running_mean,
                     running_var, stats, ll.ACT[act], y, ll.pixel_ld(y))
@@ -268,10 +268,11 @@ class BnActFn(torch.autograd.Function):
         dy = to_act(dy)
         c = z.shape[1]
         m = _rows(z)
-        s12 = zeros_f32(2 * c, z.device).view(2, c)
+        s12 = torch.empty((2, c), dtype=torch.float32, device=z.device)
+        parts = torch.empty(ll.reduce_blocks(m, c) * 2 * c, dtype=torch.float32, device=z.device)
         dz = torch.empty_like(z, memory_format=CL)
         ll.call("ly_bn_act_bwd", dy, ll.pixel_ld(dy), z, ll.pixel_ld(z), m, c, stats[2], stats[3], stats[0],
-                stats[1], ll.ACT[act], 1 if training else 0, s12[0], s12[1], dz, ll.pixel_ld(dz))
+                stats[1], ll.ACT[act], 1 if training else 0, s12[0], s12[1], parts, dz, ll.pixel_ld(dz))
         return dz, s12[1], s12[0], None, None, None, None, None, None
 
 
@@ -418,13 +419,17 @@ class UpsampleCatFn(torch.autograd.Function):
         return (None, *grads)
 
 
+GAP_PARTS = 16   # LY_GAP_PARTS of include/leadyolo.h
+
+
 def _gap_mean(x):
     """(N, C, 1, 1) bf16 mean over H*W of an NHWC activation."""
     n, c, h, w = x.shape
     if c <= 512:
-        sums = torch.empty((n, c), dtype=torch.float32, device=x.device)
-        ll.call("ly_rf_gap_sum", x, ll.pixel_ld(x), n, h * w, c, sums)       # zeroes, then sums (fp32)
-        return (sums * (1.0 / (h * w))).to(BF16).view(n, c, 1, 1)
+        parts = torch.empty((GAP_PARTS, n, c), dtype=torch.float32, device=x.device)
+        out = ll.empty_cl(n, c, 1, 1, device=x.device)
+        ll.call("ly_gap_mean", x, ll.pixel_ld(x), n, h * w, c, parts, out)   # ordered partial sums: deterministic
+        return out
     out = ll.empty_cl(n, c, 1, 1, device=x.device)
     ll.call("ly_gap", x, ll.pixel_ld(x), n, h * w, c, out, c)
     return out
@@ -605,7 +610,7 @@ class MlpBlockFn(torch.autograd.Function):
         u = ll.conv_gemm([t1, x], packed_weight(wcat, [cpp, c], 1, False), hid)
         v = torch.empty_like(u, memory_format=CL)
         stats = torch.empty((4, hid), dtype=torch.float32, device=x.device)
-        acc = zeros_f32(3 * hid, x.device)
+        acc = zeros_f32(5 * hid, x.device)
         ll.call("ly_bn_stats", u, ll.pixel_ld(u), m, hid, acc)
         ll.call("ly_bn_apply_train", u, ll.pixel_ld(u), m, hid, acc, gamma.detach().float(), beta.detach().float(), eps,
                 momentum, rmean, rvar, stats, ll.ACT["relu"], v, ll.pixel_ld(v))
@@ -629,10 +634,11 @@ class MlpBlockFn(torch.autograd.Function):
         dv = ll.conv_gemm([dy], packed_weight_dgrad(w2, c, hid, 1, False, 0, hid), hid)
         d_w2 = _wgrad_oihw([v], dy, w2, [hid], 1, 1, 0, False)
         # BatchNorm + ReLU
-        s12 = zeros_f32(2 * hid, dev).view(2, hid)
+        s12 = torch.empty((2, hid), dtype=torch.float32, device=dev)
+        parts = torch.empty(ll.reduce_blocks(m, hid) * 2 * hid, dtype=torch.float32, device=dev)
         du = torch.empty_like(u, memory_format=CL)
         ll.call("ly_bn_act_bwd", dv, ll.pixel_ld(dv), u, ll.pixel_ld(u), m, hid, stats[2], stats[3], stats[0], stats[1],
-                ll.ACT["relu"], 1, s12[0], s12[1], du, ll.pixel_ld(du))
+                ll.ACT["relu"], 1, s12[0], s12[1], parts, du, ll.pixel_ld(du))
         # mlp.0: gradient of the x source lands on top of the residual gradient; t1 source separately
         dx = ll.conv_gemm([du], packed_weight_dgrad(wcat, hid, cpp + c, 1, False, cpp, c), c, residual=dy)
         dt1 = ll.conv_gemm([du], packed_weight_dgrad(wcat, hid, cpp + c, 1, False, 0, cpp), cpp)
@@ -656,6 +662,9 @@ def _wgrad_oihw(srcs, dz, weight, chans, k, s, pad, patch):
     c4 = list(chans) + [0] * (4 - len(chans))
     ll.call("ly_unpack_wgrad", dwp, cout, k, k, 1 if patch else 0, c4[0], c4[1], c4[2], c4[3], d_w, 0)
     return d_w.to(weight.dtype)
+
+
+RF_GATE_PARTS = 16   # LY_RF_GATE_PARTS of include/leadyolo.h
 
 
 class RfGateAttFn(torch.autograd.Function):
@@ -686,9 +695,10 @@ class RfGateAttFn(torch.autograd.Function):
         n, kkc, ho, wo = g.shape
         dev = g.device
         dg = torch.empty_like(g, memory_format=CL)
-        dse = zeros_f32(n * c, dev).view(n, c)
+        dse_parts = torch.empty((RF_GATE_PARTS, n, c), dtype=torch.float32, device=dev)
         datt = torch.empty_like(att)
-        ll.call("ly_rf_gate_bwd", da, g, n, ho, wo, c, k, se, ll.pixel_ld(se), att, dg, dse, datt)
+        ll.call("ly_rf_gate_bwd", da, g, n, ho, wo, c, k, se, ll.pixel_ld(se), att, dg, dse_parts, datt)
+        dse = dse_parts.sum(0)                                  # fixed order: deterministic
         dmaps = torch.empty_like(maps)
         dwa = zeros_f32(18, dev)
         ll.call("ly_rf_attention_bwd", datt, att, maps, amax, n, ho, wo, c, k, wa32, dmaps, dwa, dg)

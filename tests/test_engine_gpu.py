@@ -92,9 +92,12 @@ def _train_pair(graph_a, graph_b, steps=3):
 def test_train_engine_graph_replay_equals_eager_step():
     (la, da, ea), (lb, db, _) = _train_pair(True, False)
     assert ea.graphs is not None and ea.launches_per_step > 100
+    # the forward pass is bit-reproducible (fixed-point BatchNorm statistics, ordered pooling sums): the first loss is
+    # identical, later ones differ only through the fp32 atomics of the weight-gradient kernels
+    assert la[0] == lb[0], (la, lb)
     for a, b in zip(la, lb):
-        assert abs(a - b) <= 5e-3 * abs(b), (la, lb)
-    assert ((da - db).norm() / db.norm()).item() < 3e-2
+        assert abs(a - b) <= 1e-3 * abs(b), (la, lb)
+    assert ((da - db).norm() / db.norm()).item() < 1e-2
     # a model whose weights moved through the engine must not serve stale packed weights at inference
     m = ea.model.eval()
     x = torch.randint(0, 256, (2, 3, 128, 128), dtype=torch.uint8).cuda()
@@ -137,7 +140,7 @@ def test_train_engine_matches_torch_sgd_reference_loop():
     for im in imgs:
         eng.step(im, tg)
     d_eng = torch.cat([p.detach().flatten() for p in eng.params]) - before2
-    assert ((d_eng - d_ref).norm() / d_ref.norm()).item() < 3e-2
+    assert ((d_eng - d_ref).norm() / d_ref.norm()).item() < 1e-2
     # EMA follows ModelEMA.update: d = decay * (1 - exp(-updates / tau))
     ema = eng.ema_model()
     assert not any(p.requires_grad for p in ema.parameters()) and not ema.training

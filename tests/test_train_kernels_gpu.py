@@ -202,3 +202,27 @@ def test_fused_sgd_ema_matches_torch():
         ema_ref = d * ema_ref + (1 - d) * torch.cat([q.detach() for q in p_ref])
         assert torch.allclose(p, torch.cat([q.detach() for q in p_ref]), rtol=1e-5, atol=1e-6)
         assert torch.allclose(ema, ema_ref, rtol=1e-5, atol=1e-6)
+
+
+def test_training_forward_is_bit_reproducible_and_gradients_agree():
+    """Two identical training steps: raw heads and loss bit-identical (fixed-point BatchNorm statistics, ordered SE
+    pooling), gradients equal up to the fp32 atomics of the weight-gradient kernels."""
+    from lead_yolo_b200.loss import ComputeLoss
+    from lead_yolo_b200.model import build_lead_yolo
+    from lead_yolo_b200.train import HYP_DEFAULT, scale_hyp
+    g = torch.Generator().manual_seed(9)
+    img = torch.randint(0, 256, (4, 3, 128, 128), generator=g, dtype=torch.uint8).cuda()
+    tg = torch.tensor([[i, 0, 0.3 + 0.1 * i, 0.5, 0.2, 0.25] for i in range(4)], device=DEV)
+    outs = []
+    for _ in range(4):
+        m = build_lead_yolo("lead", 1, DEV, seed=1).train()
+        m.hyp = scale_hyp(HYP_DEFAULT, 3, 1, 128)
+        raw = m(img)
+        loss, _ = ComputeLoss(m)(raw, tg)
+        loss.backward()
+        outs.append(([r.detach().clone() for r in raw], loss.detach().clone(),
+                     torch.cat([p.grad.flatten() for p in m.parameters()])))
+    for raw, loss, grad in outs[1:]:
+        assert all(torch.equal(a, b) for a, b in zip(raw, outs[0][0]))
+        assert torch.equal(loss, outs[0][1])
+        assert ((grad - outs[0][2]).norm() / outs[0][2].norm()).item() < 1e-4
