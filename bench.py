@@ -111,7 +111,10 @@ def dist_setup(n):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if world > 1 and not dist.is_initialized():
         torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        # a short timeout: a collective mismatch should fail the run in minutes, not hold N GPUs for ten
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local),
+                                timeout=datetime.timedelta(seconds=180))
     return rank, local, world
 
 
@@ -337,13 +340,13 @@ def train_measure(batch, steps, warm, rank, local, world, dev, profile=True, var
            "allreduce_ms_exposed": ar_ms, "loss_last_step": loss_val,
            "e2e": {"value": batch * world * steps / (ms_e2e / 1e3), "unit": "images/s",
                    "h2d_bytes_per_step": int(host[0].numel() + tgt_host[0].numel() * 4), "d2h_bytes_per_step": 4}}
-    if profile and rank == 0:
-        # per-entry-point device time of ONE eager step (events around every C-ABI call, device kept busy ahead)
-        eng2 = eng
-        eng2.use_graph = False
+    if profile:
+        # per-entry-point device time of ONE eager step (events around every C-ABI call, device kept busy ahead).
+        # Every rank takes the step (it contains the collectives); rank 0's table is reported.
+        eng.use_graph = False
         ll.PROFILE = []
         torch.cuda._sleep(int(2e8))
-        eng2.step(dimg[0], tgt[0])
+        eng.step(dimg[0], tgt[0])
         torch.cuda.synchronize()
         prof = {}
         for name, a, b, nbytes, flops in ll.PROFILE:
@@ -351,7 +354,7 @@ def train_measure(batch, steps, warm, rank, local, world, dev, profile=True, var
             d[0] += a.elapsed_time(b)
             d[1] += 1
         ll.PROFILE = None
-        eng2.use_graph = True
+        eng.use_graph = True
         out["kernel_ms_per_step"] = {k: round(v[0], 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])[:10]}
         out["kernel_ms_total"] = round(sum(v[0] for v in prof.values()), 3)
     del eng

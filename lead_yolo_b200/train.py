@@ -170,9 +170,11 @@ class TrainEngine:
         torch.cuda.synchronize(self.device)
         g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         ll.COUNT[0] = 0
-        with torch.cuda.graph(g1):
+        # thread_local: other threads of the process (NCCL's watchdog polls events, a DDP reducer may be alive) must not
+        # invalidate the capture; the kernels the autograd worker thread launches still land in the capturing stream
+        with torch.cuda.graph(g1, capture_error_mode="thread_local"):
             self.loss_out = self._forward_backward()
-        with torch.cuda.graph(g2):
+        with torch.cuda.graph(g2, capture_error_mode="thread_local"):
             self._optimizer()
         self.launches_per_step = ll.COUNT[0]
         self.graphs = (g1, g2)
