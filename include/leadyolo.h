@@ -259,6 +259,15 @@ int ly_rf_tc_stats(const void* x, long ldx, int N, int H, int W, int C, int s, i
                    const void* shift, float* maps, ly_stream_t stream);
 int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
                    const void* shift, const float* se, const float* att, void* A, ly_stream_t stream);
+/* ly_rf_tc_apply fused with RFCBAMConv.conv + its BatchNorm + ReLU (models/rfa.py:121-129): the gated receptive-field
+ * matrix (9*C wide) never reaches HBM — each [128 pixels][144] tile goes from the gating epilogue through shared memory
+ * straight into a second tcgen05 accumulation over the channel groups.  out: bf16 NHWC [N][ho][wo][Cout] (pixel stride
+ * ld_out, multiple of 16; 32-byte aligned).  w2: bf16 [C/16][9 t][Cout][16] = conv.weight[o][g*16+j][t/3][t%3], every
+ * [Cout][16] tile in the SW32 shared-memory image (lead_yolo_b200.packing.rf_fused_weight_image); scale2/shift2 fp32
+ * [Cout]: conv.1 BatchNorm folded with conv.0.bias.  C % 16 == 0, Cout in {128, 256}, s in {1, 2}. */
+int ly_rfcbam_fused_infer(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
+                          const void* shift, const float* se, const float* att, const void* w2, const float* scale2,
+                          const float* shift2, int Cout, void* out, long ld_out, ly_stream_t stream);
 /* gap_sum[n][c] = sum_hw x (zeroed by the call);  se = sigmoid(W2 relu(W1 gap_sum/HW)), att = sigmoid(conv3x3(maps)). */
 int ly_rf_gap_sum(const void* x, long ldx, int N, int HW, int C, float* gap_sum, ly_stream_t stream);
 /* Training-path average pool of rfa.SE (models/rfa.py:80,90), bit-reproducible: out bf16 [N][C] = mean over HW;

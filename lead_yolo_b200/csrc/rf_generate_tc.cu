@@ -20,6 +20,8 @@
 //          RFCBAMConv.conv, staged in shared memory and written back by TMA (288 contiguous bytes per pixel and item)
 #include <string.h>
 
+#include <atomic>
+
 #include "ly_common.cuh"
 #include "ly_tc.cuh"
 
@@ -378,6 +380,328 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
   if (warp == 2) tmem_dealloc(tmem, 512);
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// FUSED pass 2 (inference): generate -> BN -> ReLU -> SE x spatial-attention gate -> the k x k / stride-k convolution of
+// RFCBAMConv (models/rfa.py:121-129) -> its BatchNorm + ReLU, in ONE kernel.  The gated receptive-field matrix (9*C wide,
+// the largest tensor of the module) never exists in HBM: an item's gated [128 pixels][144] tile is written by the epilogue
+// warps into shared memory as nine SW32 K-major tiles and consumed from there as the A operand of a second accumulation
+//     OUT[128 pixels][Cout] += G_item[128][144] * W2[group][Cout][144]^T            (tcgen05, fp32 in TMEM)
+// over the C/16 channel groups of the pixel tile; W2 streams through a ring of bulk copies from a pre-swizzled image.
+// Work unit = a whole pixel tile (all its channel groups stay on one CTA).  Single-buffered generate accumulator, weight
+// tiles and gated tile: the second GEMM of item i is issued after the generate MMAs of item i+1, so it runs while the
+// epilogue warps gate item i+1.
+//   TMEM: generate accumulator at column 0 (144 columns), OUT at column 256 (Cout <= 256 columns).
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int kFuStages = 3;     // tap ring: one item
+constexpr int kFuW2Stages = 4;   // W2 ring, 3 K-tiles (taps t) per stage
+
+struct alignas(64) RfFusedParams {
+  CUtensorMap a_map[4];
+  int tiles_w, tiles_h, n_img, groups;
+  int Wt, Ht, ho, wo, C, s, Cout;
+  int tiles, per_cta;
+  uint32_t a_bytes;
+  const __nv_bfloat16* wc;
+  const uint32_t* shift;
+  const float* se;
+  const float* att;
+  const __nv_bfloat16* w2;   // [groups][9][Cout][16] bf16, every [Cout][16] tile SW32-swizzled
+  const float* scale2;       // [Cout] folded conv BatchNorm
+  const float* shift2;       // [Cout] (conv bias folded in)
+  __nv_bfloat16* out;        // NHWC [N][ho][wo][Cout], pixel stride ld_out
+  long ld_out;
+};
+
+__global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_constant__ RfFusedParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[kFuStages], empty_bar[kFuStages], w2_full[kFuW2Stages], w2_empty[kFuW2Stages];
+  __shared__ uint64_t tfull, tempty, b1_full, b1_empty, st_full, st_empty, out_full, out_empty;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sA = smem;                                  // kFuStages x 3 tap boxes
+  uint8_t* sOnes = sA + kFuStages * 3 * kRtA;
+  uint8_t* sB = sOnes + kRtA;                          // generate weight tiles of the current group
+  uint8_t* sStage = sB + kRtB1;                        // gated tile: 9 x [128][16] SW32
+  uint8_t* sW2 = sStage + 9 * kRtA;                    // kFuW2Stages x 3 x [Cout][16] SW32
+  const uint32_t w2_tile = (uint32_t)p.Cout * 32u;
+
+  for (int i = threadIdx.x; i < (kRtA + kRtB1) / 16; i += kRtThreads)
+    reinterpret_cast<uint4*>(sOnes)[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  if (threadIdx.x < 128)
+    *reinterpret_cast<uint32_t*>(sOnes + threadIdx.x * 32 + ((threadIdx.x >> 2) & 1) * 16) = 0x3F803F80u;
+  fence_proxy_async_smem();
+  if (warp == 0 && lane < (p.s == 2 ? 4 : 1)) tma_prefetch_desc(&p.a_map[lane]);
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kFuStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < kFuW2Stages; ++s) { mbar_init(&w2_full[s], 1); mbar_init(&w2_empty[s], 1); }
+    mbar_init(&tfull, 1); mbar_init(&tempty, 16);
+    mbar_init(&b1_full, 1); mbar_init(&b1_empty, 1);
+    mbar_init(&st_full, 16); mbar_init(&st_empty, 1);
+    mbar_init(&out_full, 1); mbar_init(&out_empty, 16);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(&tmem_base_s, 512);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem = tmem_base_s;
+
+  const int tile0 = (int)blockIdx.x * p.per_cta;
+  const int my_tiles = min(p.per_cta, p.tiles - tile0);
+  const int mine = my_tiles > 0 ? my_tiles * p.groups : 0;   // items, channel group fastest
+  const int tiles_img = p.tiles_w * p.tiles_h;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int cg = 0, mt = tile0;
+      uint32_t s = 0, ph = 1, ws = 0, wph = 1;
+      for (int i = 0; i < mine; ++i) {
+        const int n = mt / tiles_img, tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+        const int c0 = cg * 16;
+        for (int ti = 0; ti < 3; ++ti) {
+          mbar_wait(&empty_bar[s], ph);
+          mbar_arrive_expect_tx(&full_bar[s], 3u * p.a_bytes);
+          uint8_t* dst = sA + s * 3 * kRtA;
+          if (p.s == 2) {
+            const int row = th * p.Ht - (ti == 0), col = tw * p.Wt;
+            const CUtensorMap* m0 = &p.a_map[((ti + 1) & 1) * 2];
+            tma_load_5d(dst, m0 + 1, &full_bar[s], c0, col - 1, 0, row, n);
+            tma_load_5d(dst + kRtA, m0, &full_bar[s], c0, col, 0, row, n);
+            tma_load_5d(dst + 2 * kRtA, m0 + 1, &full_bar[s], c0, col, 0, row, n);
+          } else {
+            const int row = th * p.Ht + ti - 1, col = tw * p.Wt;
+            tma_load_5d(dst, &p.a_map[0], &full_bar[s], c0, col - 1, 0, row, n);
+            tma_load_5d(dst + kRtA, &p.a_map[0], &full_bar[s], c0, col, 0, row, n);
+            tma_load_5d(dst + 2 * kRtA, &p.a_map[0], &full_bar[s], c0, col + 1, 0, row, n);
+          }
+          if (++s == kFuStages) { s = 0; ph ^= 1u; }
+        }
+        // this item's W2 tiles: three stages of three K-tiles, contiguous in the image
+        const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.w2) + (size_t)cg * 9u * w2_tile;
+        for (int ti = 0; ti < 3; ++ti) {
+          mbar_wait(&w2_empty[ws], wph);
+          mbar_arrive_expect_tx(&w2_full[ws], 3u * w2_tile);
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                           smem_u32(sW2 + (size_t)ws * 3u * w2_tile)),
+                       "l"(wsrc + (size_t)ti * 3u * w2_tile), "r"(3u * w2_tile), "r"(smem_u32(&w2_full[ws]))
+                       : "memory");
+          if (++ws == kFuW2Stages) { ws = 0; wph ^= 1u; }
+        }
+        if (++cg == p.groups) { cg = 0; ++mt; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16_f32(128, 144, 0, 0);
+      const uint32_t idesc2 = umma_idesc_bf16_f32(128, p.Cout, 0, 0);
+      const uint64_t a_desc0 = rt_desc_sw32(smem_u32(sA)), b_desc = rt_desc_sw32(smem_u32(sB));
+      const uint64_t ones_desc = rt_desc_sw32(smem_u32(sOnes));
+      const uint64_t g_desc0 = rt_desc_sw32(smem_u32(sStage)), w_desc0 = rt_desc_sw32(smem_u32(sW2));
+      const uint32_t d_gen = tmem, d_out = tmem + 256u;
+      uint32_t s = 0, ph = 0, ws = 0, wph = 0;
+      auto gen = [&](int i) {
+        mbar_wait(&tempty, ((uint32_t)i & 1u) ^ 1u);
+        mbar_wait(&b1_full, (uint32_t)i & 1u);
+        tc_fence_after_sync();
+        umma_bf16(d_gen, ones_desc, b_desc + (uint64_t)(9 * (kRtB >> 4)), idesc, 0u);   // acc = shift
+        for (int ti = 0; ti < 3; ++ti) {
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after_sync();
+          const uint64_t a_desc = a_desc0 + (uint64_t)(s * (3 * kRtA >> 4));
+#pragma unroll
+          for (int tj = 0; tj < 3; ++tj)
+            umma_bf16(d_gen, a_desc + (uint64_t)(tj * (kRtA >> 4)), b_desc + (uint64_t)((ti * 3 + tj) * (kRtB >> 4)), idesc, 1u);
+          umma_commit(&empty_bar[s]);
+          if (++s == kFuStages) { s = 0; ph ^= 1u; }
+        }
+        umma_commit(&tfull);
+        umma_commit(&b1_empty);
+      };
+      if (mine > 0) gen(0);
+      int cg = 0, tile = 0;
+      for (int i = 0; i < mine; ++i) {
+        if (i + 1 < mine) gen(i + 1);
+        // second GEMM of item i
+        if (cg == 0) mbar_wait(&out_empty, ((uint32_t)tile & 1u) ^ 1u);   // previous tile's output has left TMEM
+        mbar_wait(&st_full, (uint32_t)i & 1u);
+        tc_fence_after_sync();
+        for (int ti = 0; ti < 3; ++ti) {
+          mbar_wait(&w2_full[ws], wph);
+          tc_fence_after_sync();
+          const uint64_t w_desc = w_desc0 + (uint64_t)((ws * 3u * w2_tile) >> 4);
+#pragma unroll
+          for (int tj = 0; tj < 3; ++tj)
+            umma_bf16(d_out, g_desc0 + (uint64_t)((ti * 3 + tj) * (kRtA >> 4)), w_desc + (uint64_t)((tj * w2_tile) >> 4), idesc2,
+                      (uint32_t)((cg | ti | tj) != 0));
+          umma_commit(&w2_empty[ws]);
+          if (++ws == kFuW2Stages) { ws = 0; wph ^= 1u; }
+        }
+        umma_commit(&st_empty);
+        if (++cg == p.groups) {
+          umma_commit(&out_full);
+          cg = 0;
+          ++tile;
+        }
+      }
+    }
+  } else if (warp == 18) {
+    uint32_t off[5], soff[5];
+#pragma unroll
+    for (int m = 0; m < 5; ++m) {
+      const int n = lane + 32 * m;
+      off[m] = smem_u32(sB) + (uint32_t)(n * 32 + ((((n >> 3) ^ (n >> 2)) & 1) << 4) + (n & 7) * 2);
+      soff[m] = smem_u32(sB) + (uint32_t)(9 * kRtB + n * 32 + ((n >> 2) & 1) * 16);
+    }
+    uint16_t v[9][5];
+    uint32_t sh[5];
+    auto fetch = [&](int cg) {
+      const uint16_t* src = reinterpret_cast<const uint16_t*>(p.wc) + (long)cg * 1296 + lane;
+#pragma unroll
+      for (int k = 0; k < 9; ++k)
+#pragma unroll
+        for (int m = 0; m < 5; ++m) v[k][m] = (m < 4 || lane < 16) ? __ldg(src + k * 144 + 32 * m) : (uint16_t)0;
+#pragma unroll
+      for (int m = 0; m < 5; ++m) sh[m] = (m < 4 || lane < 16) ? __ldg(p.shift + cg * 144 + lane + 32 * m) : 0u;
+    };
+    int cg = 0;
+    if (mine > 0) fetch(0);
+    for (int i = 0; i < mine; ++i) {
+      mbar_wait(&b1_empty, ((uint32_t)i & 1u) ^ 1u);
+#pragma unroll
+      for (int k = 0; k < 9; ++k)
+#pragma unroll
+        for (int m = 0; m < 5; ++m)
+          if (m < 4 || lane < 16)
+            asm volatile("st.shared.b16 [%0], %1;" ::"r"(off[m] + (uint32_t)(k * kRtB)), "h"(v[k][m]) : "memory");
+#pragma unroll
+      for (int m = 0; m < 5; ++m)
+        if (m < 4 || lane < 16) asm volatile("st.shared.b32 [%0], %1;" ::"r"(soff[m]), "r"(sh[m]) : "memory");
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&b1_full);
+      if (++cg == p.groups) cg = 0;
+      if (i + 1 < mine) fetch(cg);
+    }
+  } else {
+    const int q = warp & 3;
+    const int eg = (warp - 2) >> 2;                 // t = 0..2 | 3,4 | 5,6 | 7,8;  output columns eg * Cout/4 ..
+    const int t0 = eg == 0 ? 0 : 1 + 2 * eg, nt = eg == 0 ? 3 : 2;
+    const int r = q * 32 + lane;
+    const int hh = r / p.Wt, ww = r - hh * p.Wt;
+    const uint32_t swz = (uint32_t)((r >> 2) & 1);
+    float va[3];
+    int cg = 0, mt = tile0, tile = 0;
+    int n = 0, h = 0, w = 0;
+    bool valid = false, fresh = true;
+    const float* se_row = nullptr;
+    for (int i = 0; i < mine; ++i) {
+      if (fresh) {
+        fresh = false;
+        n = mt / tiles_img;
+        const int tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+        h = th * p.Ht + hh; w = tw * p.Wt + ww;
+        valid = (r < p.Wt * p.Ht) && h < p.ho && w < p.wo;
+#pragma unroll
+        for (int tt = 0; tt < 3; ++tt) {
+          va[tt] = 0.f;
+          if (valid && tt < nt) {
+            const int t = t0 + tt;
+            va[tt] = __ldg(p.att + ((long)n * (p.ho * 3) + (h * 3 + t / 3)) * (long)(p.wo * 3) + (w * 3 + t % 3));
+          }
+        }
+        se_row = p.se + (long)n * p.C;
+      }
+      uint64_t se2[8];
+      {
+        const float4* sp = reinterpret_cast<const float4*>(se_row + cg * 16);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float4 e = __ldg(sp + j);
+          se2[2 * j] = f2_pack(e.x, e.y); se2[2 * j + 1] = f2_pack(e.z, e.w);
+        }
+      }
+      mbar_wait(&tfull, (uint32_t)i & 1u);
+      tc_fence_after_sync();
+      const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(t0 * 16);
+      uint32_t acc[3][16];
+      tmem_ld16(trow, acc[0]);
+      tmem_ld16(trow + 16u, acc[1]);
+      if (nt == 3) tmem_ld16(trow + 32u, acc[2]);
+      tmem_ld_wait();
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty);
+      uint32_t wds[3][8];
+#pragma unroll
+      for (int tt = 0; tt < 3; ++tt) {
+        if (tt < nt) {
+          const uint64_t att2 = f2_pack(va[tt], va[tt]);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint64_t x2 = f2_pack(__uint_as_float(acc[tt][2 * j]), __uint_as_float(acc[tt][2 * j + 1]));
+            wds[tt][j] = relu_bf16x2(f2_mul(x2, f2_mul(se2[j], att2)));
+          }
+        }
+      }
+      // the second GEMM of the previous item has finished reading the gated tile
+      mbar_wait(&st_empty, ((uint32_t)i & 1u) ^ 1u);
+#pragma unroll
+      for (int tt = 0; tt < 3; ++tt) {
+        if (tt < nt) {
+          uint8_t* row = sStage + (t0 + tt) * kRtA + r * 32;
+          *reinterpret_cast<uint4*>(row + (swz << 4)) = make_uint4(wds[tt][0], wds[tt][1], wds[tt][2], wds[tt][3]);
+          *reinterpret_cast<uint4*>(row + ((swz ^ 1u) << 4)) = make_uint4(wds[tt][4], wds[tt][5], wds[tt][6], wds[tt][7]);
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&st_full);
+      if (++cg == p.groups) {
+        // the tile's OUT accumulator is complete: BatchNorm + ReLU, bf16, NHWC rows
+        mbar_wait(&out_full, (uint32_t)tile & 1u);
+        tc_fence_after_sync();
+        const int ncol = p.Cout >> 2;                // columns of this epilogue group: 32 or 64 (16-column steps)
+        const uint32_t orow = tmem + ((uint32_t)(q * 32) << 16) + 256u + (uint32_t)(eg * ncol);
+        __nv_bfloat16* dst = p.out + (((long)n * p.ho + h) * p.wo + w) * p.ld_out + eg * ncol;
+        for (int c0 = 0; c0 < ncol; c0 += 32) {
+          uint32_t o[2][16];
+          tmem_ld16(orow + (uint32_t)c0, o[0]);
+          tmem_ld16(orow + (uint32_t)c0 + 16u, o[1]);     // ncol is a multiple of 32 (Cout = 128 or 256)
+          tmem_ld_wait();
+          if (c0 + 32 >= ncol) {       // last read of this warp: hand the accumulator back
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&out_empty);
+          }
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            if (valid) {
+              const int cb = eg * ncol + c0 + half * 16;
+              uint32_t wo8[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float2 sc = __ldg(reinterpret_cast<const float2*>(p.scale2 + cb) + j);
+                const float2 sf = __ldg(reinterpret_cast<const float2*>(p.shift2 + cb) + j);
+                const float y0 = fmaf(__uint_as_float(o[half][2 * j]), sc.x, sf.x);
+                const float y1 = fmaf(__uint_as_float(o[half][2 * j + 1]), sc.y, sf.y);
+                wo8[j] = relu_bf16x2(f2_pack(y0, y1));
+              }
+              st_global_256(dst + c0 + half * 16, wo8);
+            }
+          }
+        }
+        cg = 0; ++mt; ++tile; fresh = true;
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
 typedef CUresult (*rt_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -479,6 +803,70 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   return LY_OK;
 }
 
+static int rf_fused_launch(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
+                           const void* shift, const float* se, const float* att, const void* w2, const float* scale2,
+                           const float* shift2, int Cout, void* out, long ld_out, cudaStream_t stream) {
+  LY_REQUIRE(x && wc && shift && se && att && w2 && scale2 && shift2 && out, "ly_rfcbam_fused_infer: null pointer");
+  LY_REQUIRE(C % 16 == 0 && C > 0 && (s == 1 || s == 2) && ldx % 8 == 0 && ldx >= C, "ly_rfcbam_fused_infer: bad C/s/ld");
+  LY_REQUIRE(Cout == 128 || Cout == 256, "ly_rfcbam_fused_infer: Cout=%d must be 128 or 256", Cout);
+  LY_REQUIRE(ho == (H + 2 - 3) / s + 1 && wo == (W + 2 - 3) / s + 1, "ly_rfcbam_fused_infer: output size mismatch");
+  LY_REQUIRE(ld_out % 16 == 0 && ld_out >= Cout && reinterpret_cast<uintptr_t>(out) % 32 == 0,
+             "ly_rfcbam_fused_infer: out must be 32-byte aligned with a pixel stride that is a multiple of 16");
+  LY_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(wc) % 16 == 0 &&
+                 reinterpret_cast<uintptr_t>(w2) % 16 == 0 && reinterpret_cast<uintptr_t>(se) % 16 == 0 &&
+                 reinterpret_cast<uintptr_t>(scale2) % 8 == 0 && reinterpret_cast<uintptr_t>(shift2) % 8 == 0,
+             "ly_rfcbam_fused_infer: alignment");
+  RfFusedParams p;
+  memset(&p, 0, sizeof(p));
+  int bw = 16, bh = 8;
+  double best = -1;
+  const int cand[6] = {8, 16, 32, 64, 128, wo <= 128 ? wo : 128};
+  for (int i = 0; i < 6; ++i) {
+    const int wt = cand[i];
+    if (wt <= 0 || wt > 128) continue;
+    int ht = 128 / wt;
+    if (ht > ho) ht = ho;
+    const double eff = (double)ho * wo / ((double)ceil_div(wo, wt) * ceil_div(ho, ht) * 128.0);
+    if (eff > best + 1e-9) { best = eff; bw = wt; bh = ht; }
+  }
+  p.Wt = bw; p.Ht = bh;
+  p.tiles_w = ceil_div(wo, bw); p.tiles_h = ceil_div(ho, bh); p.n_img = N;
+  p.groups = C / 16;
+  p.ho = ho; p.wo = wo; p.C = C; p.s = s; p.Cout = Cout;
+  p.a_bytes = (uint32_t)(16 * bw * bh * 2);
+  p.wc = (const __nv_bfloat16*)wc; p.shift = (const uint32_t*)shift; p.se = se; p.att = att;
+  p.w2 = (const __nv_bfloat16*)w2; p.scale2 = scale2; p.shift2 = shift2;
+  p.out = (__nv_bfloat16*)out; p.ld_out = ld_out;
+  for (int par = 0; par < (s == 2 ? 4 : 1); ++par) {
+    const int ph = par >> 1, pw = par & 1;
+    const uint64_t Hp = (uint64_t)(H - ph + s - 1) / s, Wp = (uint64_t)(W - pw + s - 1) / s;
+    if (Hp == 0 || Wp == 0) { memcpy(&p.a_map[par], &p.a_map[0], sizeof(CUtensorMap)); continue; }
+    uint64_t dims[5] = {(uint64_t)C, Wp, 1, Hp, (uint64_t)N};
+    uint64_t str[4] = {(uint64_t)s * ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)s * W * ldx * 2,
+                       (uint64_t)H * W * ldx * 2};
+    uint32_t box[5] = {16, (uint32_t)bw, 1, (uint32_t)bh, 1};
+    uint32_t es[5] = {1, 1, 1, 1, 1};
+    int rc = rt_encode(&p.a_map[par], (const __nv_bfloat16*)x + ((long)ph * W + pw) * ldx, 5, dims, str, box, es);
+    if (rc) return rc;
+  }
+  const long tiles = (long)p.tiles_w * p.tiles_h * N;
+  LY_REQUIRE(tiles * p.groups < (1L << 30), "ly_rfcbam_fused_infer: problem too large");
+  p.tiles = (int)tiles;
+  p.per_cta = (int)ceil_div(tiles, (long)device_sm_count());
+  const unsigned grid = (unsigned)ceil_div(tiles, (long)p.per_cta);
+  const size_t smem = (size_t)kFuStages * 3 * kRtA + kRtA + kRtB1 + 9 * kRtA + (size_t)kFuW2Stages * 3 * Cout * 32 + 1024;
+  static std::atomic<size_t> attr_set[64];
+  int dev = 0;
+  LY_CUDA(cudaGetDevice(&dev));
+  if (attr_set[dev & 63].load() < smem) {
+    LY_CUDA(cudaFuncSetAttribute(rf_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set[dev & 63].store(smem);
+  }
+  rf_fused_kernel<<<grid, kRtThreads, smem, stream>>>(p);
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
 }  // namespace ly
 
 using namespace ly;
@@ -500,4 +888,16 @@ extern "C" int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int 
   LY_REQUIRE(se && att && A && reinterpret_cast<uintptr_t>(A) % 16 == 0 && reinterpret_cast<uintptr_t>(se) % 16 == 0,
              "ly_rf_tc_apply: null or misaligned pointer");
   return rf_tc_launch(1, x, ldx, N, H, W, C, s, ho, wo, wc, shift, se, att, A, nullptr, (cudaStream_t)st);
+}
+
+// Pass 2 fused with RFCBAMConv.conv (models/rfa.py:121-129): out bf16 NHWC [N][ho][wo][Cout] = relu(scale2 * (gated
+// receptive-field matrix x W2) + shift2); the gated matrix never reaches HBM.  w2: bf16 [C/16][9 t][Cout][16], value
+// conv.weight[o][g*16+j][t/3][t%3] at tile row o, column j, every [Cout][16] tile in the SW32 shared-memory image
+// (16-byte chunk c of row o stored at chunk c ^ ((o >> 2) & 1)); scale2/shift2: conv BatchNorm folded with the conv bias.
+extern "C" int ly_rfcbam_fused_infer(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo,
+                                     const void* wc, const void* shift, const float* se, const float* att, const void* w2,
+                                     const float* scale2, const float* shift2, int Cout, void* out, long ld_out,
+                                     ly_stream_t st) {
+  return rf_fused_launch(x, ldx, N, H, W, C, s, ho, wo, wc, shift, se, att, w2, scale2, shift2, Cout, out, ld_out,
+                         (cudaStream_t)st);
 }

@@ -183,6 +183,7 @@ _SIGS = {
     "ly_rfcbam_front_infer": "pliiiiiiiipppppipppppp",
     "ly_rf_tc_stats": "pliiiiiiippp",
     "ly_rf_tc_apply": "pliiiiiiippppp",
+    "ly_rfcbam_fused_infer": "pliiiiiiipppppppipl",
     "ly_rf_gap_sum": "pliiip",
     "ly_gap_mean": "pliiipp",
     "ly_rf_se_att": "piiippipiippp",

@@ -551,6 +551,10 @@ class C3_CA(nn.Module):
 # ------------------------------------------------------------------------------------------------------------
 # RFCBAMConv — reference models/rfa.py:77-129
 # ------------------------------------------------------------------------------------------------------------
+# A/B knob: LY_RF_UNFUSED=1 keeps the k = 3 RFCBAMConv on the round-1 path (gated matrix written to HBM, separate GEMM)
+_RF_UNFUSED = bool(__import__('os').environ.get('LY_RF_UNFUSED'))
+
+
 class SE(nn.Module):
     """rfa.SE — reference models/rfa.py:77-92 (hidden width is the literal `ratio`)."""
 
@@ -605,6 +609,10 @@ class RFCBAMConv(nn.Module):
         if fast and c <= 256 and (gen.stride[0] == 1 or (h % 2 == 0 and w % 2 == 0)):
             # two passes over x, no receptive-field matrix in HBM (ly_rfcbam_front_infer)
             gscale, gshift = ops.bn_fold(gbn, None, perm=perm)
+            if ops.rfcbam_fused_ok(k, c, cout) and not _RF_UNFUSED:
+                scale, shift = ops.bn_fold(cbn, conv.bias)
+                return ops.rfcbam_infer_fused(x, gen.weight, s, gscale, gshift, self.se.fc[0].weight,
+                                              self.se.fc[2].weight, self.get_weight[0].weight, conv.weight, scale, shift)
             a = ops.rfcbam_front_infer(x, gen.weight, k, s, gscale, gshift, self.se.fc[0].weight,
                                        self.se.fc[2].weight, self.get_weight[0].weight)
             tcl = ops.rf_tc_layout(k, c)

@@ -771,6 +771,41 @@ def rfcbam_front_infer(x, wg, k, s, gscale, gshift, w1, w2, wa):
     return a
 
 
+def rfcbam_fused_ok(k, c, cout):
+    """True when the whole k = 3 module runs as two tensor-core passes with the final convolution fused in
+    (ly_rfcbam_fused_infer): the gated receptive-field matrix never reaches HBM."""
+    return rf_tc_layout(k, c) and cout in (128, 256)
+
+
+def rfcbam_infer_fused(x, wg, s, gscale, gshift, w1, w2, wa, conv_weight, scale2, shift2):
+    """Inference, k = 3: x -> RFCBAMConv output (N, Cout, ho, wo).  Pass 1 (ly_rf_tc_stats) gives the channel max / mean
+    maps, ly_rf_se_att the SE gate and the spatial attention, pass 2 (ly_rfcbam_fused_infer) regenerates the features,
+    gates them and multiplies by the stride-k convolution's weights inside the same kernel, with BatchNorm + ReLU."""
+    from .packing import rf_fused_weight_image
+    x = to_act(x)
+    n, c, h, w = x.shape
+    ho, wo = rf_out_size(h, w, 3, s)
+    dev = x.device
+    cout = conv_weight.shape[0]
+    wc, sh = cached([wg, gscale, gshift], ("rftc", c), lambda: _rf_tc_weights(wg, c, gscale, gshift))
+    w1f = cached([w1], "sew1", lambda: w1.detach().float().contiguous())
+    w2f = cached([w2], "sew2", lambda: w2.detach().float().contiguous())
+    wa32 = cached([wa], "wa32", lambda: wa.detach().float().reshape(18).contiguous())
+    w2img = cached([conv_weight], ("rffw", c), lambda: rf_fused_weight_image(conv_weight, c))
+    nm = n * ho * 3 * wo * 3
+    nmp = (nm + 3) // 4 * 4
+    ws = torch.empty(3 * nmp + 2 * n * c, dtype=torch.float32, device=dev)
+    maps, att = ws[:2 * nm], ws[2 * nmp:2 * nmp + nm]
+    gap, se = ws[3 * nmp:3 * nmp + n * c], ws[3 * nmp + n * c:]
+    y = ll.empty_cl(n, cout, ho, wo, device=dev)
+    ld = ll.pixel_ld(x)
+    ll.call("ly_rf_gap_sum", x, ld, n, h * w, c, gap)
+    ll.call("ly_rf_tc_stats", x, ld, n, h, w, c, s, ho, wo, wc, sh, maps)
+    ll.call("ly_rf_se_att", gap, n, c, h * w, w1f, w2f, int(w1.shape[0]), maps, ho * 3, wo * 3, wa32, se, att)
+    ll.call("ly_rfcbam_fused_infer", x, ld, n, h, w, c, s, ho, wo, wc, sh, se, att, w2img, scale2, shift2, cout, y, cout)
+    return y
+
+
 def rf_gate_att_infer(g, se, wa, k):
     n, kkc, ho, wo = g.shape
     c = kkc // (k * k)

@@ -169,3 +169,14 @@ def _fasternet_weight_image80(w1: torch.Tensor, w2: torch.Tensor, wp: torch.Tens
         for t in range(9):
             parts.append(swizzle32(wcs[t][:, sl * 16:(sl + 1) * 16].to(bf).contiguous()))
     return torch.cat(parts).contiguous(), off_w2, off_wc
+
+
+def rf_fused_weight_image(w: torch.Tensor, c: int) -> torch.Tensor:
+    """RFCBAMConv.conv weight [Cout, C, 3, 3] -> bf16 [C/16][9 t][Cout][16] with every [Cout][16] tile in the SW32
+    shared-memory image (csrc/rf_generate_tc.cu: rf_fused_kernel streams it with plain bulk copies)."""
+    cout = w.shape[0]
+    assert w.shape[1] == c and c % 16 == 0 and tuple(w.shape[2:]) == (3, 3) and cout % 8 == 0
+    m = w.detach().float().permute(1, 2, 3, 0).reshape(c // 16, 16, 9, cout)          # [g][j][t][o]
+    m = m.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)                          # [g][t][o][j]
+    tiles = [swizzle32(m[g, t]) for g in range(c // 16) for t in range(9)]
+    return torch.cat(tiles).contiguous()
