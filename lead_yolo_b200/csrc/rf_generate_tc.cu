@@ -392,14 +392,12 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
 // epilogue warps gate item i+1.
 //   TMEM: generate accumulator at column 0 (144 columns), OUT at column 256 (Cout <= 256 columns).
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kFuStages = 3;     // tap ring: one item
-constexpr int kFuW2Stages = 4;   // W2 ring, 3 K-tiles (taps t) per stage
-
 struct alignas(64) RfFusedParams {
   CUtensorMap a_map[4];
   int tiles_w, tiles_h, n_img, groups;
   int Wt, Ht, ho, wo, C, s, Cout;
   int tiles, per_cta;
+  int a_slots;               // tap buffers of one whole item (nine boxes) each: 1 or 2
   uint32_t a_bytes;
   const __nv_bfloat16* wc;
   const uint32_t* shift;
@@ -412,19 +410,25 @@ struct alignas(64) RfFusedParams {
   long ld_out;
 };
 
+// Barriers are per ITEM, not per ring stage: the MMA-issuing lane pays ~340 cycles per tcgen05.commit against ~80 per
+// tcgen05.mma (tests/dev/mma_issue.cu), so an item costs it 19 MMAs and three commits (taps free + accumulator ready,
+// W2 and gated tile free) — with one commit per three-box stage it was nine, and the lane was the bottleneck.
 __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_constant__ RfFusedParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t full_bar[kFuStages], empty_bar[kFuStages], w2_full[kFuW2Stages], w2_empty[kFuW2Stages];
-  __shared__ uint64_t tfull, tempty, b1_full, b1_empty, st_full, st_empty, out_full, out_empty;
+  // gen_ready: 16 epilogue warps (accumulator of the previous item read) + the weight-tile writer (this item's diagonal in
+  // place); g2_ready: 16 epilogue warps (gated tile written) + the W2 bulk copy (one arrive.expect_tx).  A lone issuing
+  // lane pays ~250 cycles per mbarrier round trip, so what it waits on is merged wherever no arriver can run a phase ahead.
+  __shared__ uint64_t a_full[2], a_empty[2], w_empty, tfull, gen_ready, g2_ready, out_full, out_empty;
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
-  uint8_t* sA = smem;                                  // kFuStages x 3 tap boxes
-  uint8_t* sOnes = sA + kFuStages * 3 * kRtA;
+  const int nA = p.a_slots;
+  uint8_t* sA = smem;                                  // nA x 9 tap boxes
+  uint8_t* sOnes = sA + nA * 9 * kRtA;
   uint8_t* sB = sOnes + kRtA;                          // generate weight tiles of the current group
   uint8_t* sStage = sB + kRtB1;                        // gated tile: 9 x [128][16] SW32
-  uint8_t* sW2 = sStage + 9 * kRtA;                    // kFuW2Stages x 3 x [Cout][16] SW32
+  uint8_t* sW2 = sStage + 9 * kRtA;                    // 9 x [Cout][16] SW32: the current group's slice of W2
   const uint32_t w2_tile = (uint32_t)p.Cout * 32u;
 
   for (int i = threadIdx.x; i < (kRtA + kRtB1) / 16; i += kRtThreads)
@@ -435,11 +439,11 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
   fence_proxy_async_smem();
   if (warp == 0 && lane < (p.s == 2 ? 4 : 1)) tma_prefetch_desc(&p.a_map[lane]);
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kFuStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int s = 0; s < kFuW2Stages; ++s) { mbar_init(&w2_full[s], 1); mbar_init(&w2_empty[s], 1); }
-    mbar_init(&tfull, 1); mbar_init(&tempty, 16);
-    mbar_init(&b1_full, 1); mbar_init(&b1_empty, 1);
-    mbar_init(&st_full, 16); mbar_init(&st_empty, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+    mbar_init(&w_empty, 1);
+    mbar_init(&tfull, 1);
+    mbar_init(&gen_ready, 17);
+    mbar_init(&g2_ready, 17);
     mbar_init(&out_full, 1); mbar_init(&out_empty, 16);
     fence_mbar_init();
   }
@@ -456,94 +460,95 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
 
   if (warp == 0) {
     if (lane == 0) {
-      int cg = 0, mt = tile0;
-      uint32_t s = 0, ph = 1, ws = 0, wph = 1;
-      for (int i = 0; i < mine; ++i) {
-        const int n = mt / tiles_img, tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
-        const int c0 = cg * 16;
-        for (int ti = 0; ti < 3; ++ti) {
-          mbar_wait(&empty_bar[s], ph);
-          mbar_arrive_expect_tx(&full_bar[s], 3u * p.a_bytes);
-          uint8_t* dst = sA + s * 3 * kRtA;
-          if (p.s == 2) {
-            const int row = th * p.Ht - (ti == 0), col = tw * p.Wt;
-            const CUtensorMap* m0 = &p.a_map[((ti + 1) & 1) * 2];
-            tma_load_5d(dst, m0 + 1, &full_bar[s], c0, col - 1, 0, row, n);
-            tma_load_5d(dst + kRtA, m0, &full_bar[s], c0, col, 0, row, n);
-            tma_load_5d(dst + 2 * kRtA, m0 + 1, &full_bar[s], c0, col, 0, row, n);
-          } else {
-            const int row = th * p.Ht + ti - 1, col = tw * p.Wt;
-            tma_load_5d(dst, &p.a_map[0], &full_bar[s], c0, col - 1, 0, row, n);
-            tma_load_5d(dst + kRtA, &p.a_map[0], &full_bar[s], c0, col, 0, row, n);
-            tma_load_5d(dst + 2 * kRtA, &p.a_map[0], &full_bar[s], c0, col + 1, 0, row, n);
+      // Two independent streams from one lane — an item's nine tap boxes (what the generate MMAs wait on) and its W2
+      // slice (what the second GEMM waits on) — polled without blocking, so neither holds the other back.
+      int cgA = 0, mtA = tile0, itemA = 0, cgB = 0, itemB = 0;
+      long long t_idle = clock64();
+      while (itemA < mine || itemB < mine) {
+        bool moved = false;
+        const int slot = nA == 2 ? (itemA & 1) : 0;
+        const uint32_t useA = (uint32_t)(nA == 2 ? (itemA >> 1) : itemA);
+        if (itemA < mine && mbar_try_wait(&a_empty[slot], (useA & 1u) ^ 1u)) {
+          const int n = mtA / tiles_img, tr = mtA - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+          const int c0 = cgA * 16;
+          uint64_t* bar = &a_full[slot];
+          mbar_arrive_expect_tx(bar, 9u * p.a_bytes);
+          uint8_t* dst = sA + slot * 9 * kRtA;
+#pragma unroll
+          for (int ti = 0; ti < 3; ++ti, dst += 3 * kRtA) {
+            if (p.s == 2) {   // input row 2h + ti - 1: parity (ti + 1) & 1, plane row h - (ti == 0)
+              const int row = th * p.Ht - (ti == 0), col = tw * p.Wt;
+              const CUtensorMap* m0 = &p.a_map[((ti + 1) & 1) * 2];
+              tma_load_5d(dst, m0 + 1, bar, c0, col - 1, 0, row, n);
+              tma_load_5d(dst + kRtA, m0, bar, c0, col, 0, row, n);
+              tma_load_5d(dst + 2 * kRtA, m0 + 1, bar, c0, col, 0, row, n);
+            } else {
+              const int row = th * p.Ht + ti - 1, col = tw * p.Wt;
+              tma_load_5d(dst, &p.a_map[0], bar, c0, col - 1, 0, row, n);
+              tma_load_5d(dst + kRtA, &p.a_map[0], bar, c0, col, 0, row, n);
+              tma_load_5d(dst + 2 * kRtA, &p.a_map[0], bar, c0, col + 1, 0, row, n);
+            }
           }
-          if (++s == kFuStages) { s = 0; ph ^= 1u; }
+          ++itemA;
+          if (++cgA == p.groups) { cgA = 0; ++mtA; }
+          moved = true;
         }
-        // this item's W2 tiles: three stages of three K-tiles, contiguous in the image
-        const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.w2) + (size_t)cg * 9u * w2_tile;
-        for (int ti = 0; ti < 3; ++ti) {
-          mbar_wait(&w2_empty[ws], wph);
-          mbar_arrive_expect_tx(&w2_full[ws], 3u * w2_tile);
+        if (itemB < mine && mbar_try_wait(&w_empty, ((uint32_t)itemB & 1u) ^ 1u)) {
+          const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.w2) + (size_t)cgB * 9u * w2_tile;
+          mbar_arrive_expect_tx(&g2_ready, 9u * w2_tile);
           asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                           smem_u32(sW2 + (size_t)ws * 3u * w2_tile)),
-                       "l"(wsrc + (size_t)ti * 3u * w2_tile), "r"(3u * w2_tile), "r"(smem_u32(&w2_full[ws]))
+                           smem_u32(sW2)),
+                       "l"(wsrc), "r"(9u * w2_tile), "r"(smem_u32(&g2_ready))
                        : "memory");
-          if (++ws == kFuW2Stages) { ws = 0; wph ^= 1u; }
+          ++itemB;
+          if (++cgB == p.groups) cgB = 0;
+          moved = true;
         }
-        if (++cg == p.groups) { cg = 0; ++mt; }
+        if (moved) t_idle = clock64();
+        else if (clock64() - t_idle > 4000000000LL) __trap();   // a pipeline bug must surface as an error, not a hang
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
+      // One lane issues everything: the generate MMAs of item i+1 go out before the second GEMM of item i, so the
+      // tensor pipe works on them while the epilogue warps gate item i.  (Measured: handing the second GEMM to a
+      // second issuing lane in warp 18 was slower — it delayed that warp's rewrite of the generate weight tiles.)
       const uint32_t idesc = umma_idesc_bf16_f32(128, 144, 0, 0);
       const uint32_t idesc2 = umma_idesc_bf16_f32(128, p.Cout, 0, 0);
       const uint64_t a_desc0 = rt_desc_sw32(smem_u32(sA)), b_desc = rt_desc_sw32(smem_u32(sB));
       const uint64_t ones_desc = rt_desc_sw32(smem_u32(sOnes));
       const uint64_t g_desc0 = rt_desc_sw32(smem_u32(sStage)), w_desc0 = rt_desc_sw32(smem_u32(sW2));
       const uint32_t d_gen = tmem, d_out = tmem + 256u;
-      uint32_t s = 0, ph = 0, ws = 0, wph = 0;
-      auto gen = [&](int i) {
-        mbar_wait(&tempty, ((uint32_t)i & 1u) ^ 1u);
-        mbar_wait(&b1_full, (uint32_t)i & 1u);
-        tc_fence_after_sync();
-        umma_bf16(d_gen, ones_desc, b_desc + (uint64_t)(9 * (kRtB >> 4)), idesc, 0u);   // acc = shift
-        for (int ti = 0; ti < 3; ++ti) {
-          mbar_wait(&full_bar[s], ph);
+      int cg2 = 0, tile = 0;
+      for (int i = 0; i <= mine; ++i) {
+        if (i < mine) {
+          const int slot = nA == 2 ? (i & 1) : 0;
+          const uint32_t use = (uint32_t)(nA == 2 ? (i >> 1) : i);
+          mbar_wait(&gen_ready, (uint32_t)i & 1u);
+          mbar_wait(&a_full[slot], use & 1u);
           tc_fence_after_sync();
-          const uint64_t a_desc = a_desc0 + (uint64_t)(s * (3 * kRtA >> 4));
+          umma_bf16(d_gen, ones_desc, b_desc + (uint64_t)(9 * (kRtB >> 4)), idesc, 0u);   // acc = shift
+          const uint64_t a_desc = a_desc0 + (uint64_t)(slot * (9 * kRtA >> 4));
 #pragma unroll
-          for (int tj = 0; tj < 3; ++tj)
-            umma_bf16(d_gen, a_desc + (uint64_t)(tj * (kRtA >> 4)), b_desc + (uint64_t)((ti * 3 + tj) * (kRtB >> 4)), idesc, 1u);
-          umma_commit(&empty_bar[s]);
-          if (++s == kFuStages) { s = 0; ph ^= 1u; }
+          for (int t = 0; t < 9; ++t)
+            umma_bf16(d_gen, a_desc + (uint64_t)(t * (kRtA >> 4)), b_desc + (uint64_t)(t * (kRtB >> 4)), idesc, 1u);
+          umma_commit(&a_empty[slot]);
+          umma_commit(&tfull);
         }
-        umma_commit(&tfull);
-        umma_commit(&b1_empty);
-      };
-      if (mine > 0) gen(0);
-      int cg = 0, tile = 0;
-      for (int i = 0; i < mine; ++i) {
-        if (i + 1 < mine) gen(i + 1);
-        // second GEMM of item i
-        if (cg == 0) mbar_wait(&out_empty, ((uint32_t)tile & 1u) ^ 1u);   // previous tile's output has left TMEM
-        mbar_wait(&st_full, (uint32_t)i & 1u);
-        tc_fence_after_sync();
-        for (int ti = 0; ti < 3; ++ti) {
-          mbar_wait(&w2_full[ws], wph);
+        if (i > 0) {   // second GEMM of item i-1: OUT (+)= gated tile x its W2 slice
+          if (cg2 == 0) mbar_wait(&out_empty, ((uint32_t)tile & 1u) ^ 1u);   // previous tile's output has left TMEM
+          mbar_wait(&g2_ready, (uint32_t)(i - 1) & 1u);
           tc_fence_after_sync();
-          const uint64_t w_desc = w_desc0 + (uint64_t)((ws * 3u * w2_tile) >> 4);
 #pragma unroll
-          for (int tj = 0; tj < 3; ++tj)
-            umma_bf16(d_out, g_desc0 + (uint64_t)((ti * 3 + tj) * (kRtA >> 4)), w_desc + (uint64_t)((tj * w2_tile) >> 4), idesc2,
-                      (uint32_t)((cg | ti | tj) != 0));
-          umma_commit(&w2_empty[ws]);
-          if (++ws == kFuW2Stages) { ws = 0; wph ^= 1u; }
-        }
-        umma_commit(&st_empty);
-        if (++cg == p.groups) {
-          umma_commit(&out_full);
-          cg = 0;
-          ++tile;
+          for (int t = 0; t < 9; ++t)
+            umma_bf16(d_out, g_desc0 + (uint64_t)(t * (kRtA >> 4)), w_desc0 + (uint64_t)((t * w2_tile) >> 4), idesc2,
+                      (uint32_t)((cg2 | t) != 0));
+          umma_commit(&w_empty);          // W2 slice AND gated tile are free again
+          if (++cg2 == p.groups) {
+            umma_commit(&out_full);
+            cg2 = 0;
+            ++tile;
+          }
         }
       }
     }
@@ -569,7 +574,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
     int cg = 0;
     if (mine > 0) fetch(0);
     for (int i = 0; i < mine; ++i) {
-      mbar_wait(&b1_empty, ((uint32_t)i & 1u) ^ 1u);
+      if (i > 0) mbar_wait(&tfull, ((uint32_t)i & 1u) ^ 1u);   // the generate MMAs of item i-1 have read the tiles
 #pragma unroll
       for (int k = 0; k < 9; ++k)
 #pragma unroll
@@ -581,7 +586,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
         if (m < 4 || lane < 16) asm volatile("st.shared.b32 [%0], %1;" ::"r"(soff[m]), "r"(sh[m]) : "memory");
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&b1_full);
+      if (lane == 0) mbar_arrive(&gen_ready);
       if (++cg == p.groups) cg = 0;
       if (i + 1 < mine) fetch(cg);
     }
@@ -597,6 +602,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
     int n = 0, h = 0, w = 0;
     bool valid = false, fresh = true;
     const float* se_row = nullptr;
+    if (mine > 0 && lane == 0) mbar_arrive(&gen_ready);   // item 0: there is no previous accumulator to drain
     for (int i = 0; i < mine; ++i) {
       if (fresh) {
         fresh = false;
@@ -633,7 +639,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
       tmem_ld_wait();
       tc_fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty);
+      if (lane == 0 && i + 1 < mine) mbar_arrive(&gen_ready);   // the accumulator may be overwritten by item i+1
       uint32_t wds[3][8];
 #pragma unroll
       for (int tt = 0; tt < 3; ++tt) {
@@ -646,8 +652,8 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
           }
         }
       }
-      // the second GEMM of the previous item has finished reading the gated tile
-      mbar_wait(&st_empty, ((uint32_t)i & 1u) ^ 1u);
+      // the second GEMM of the previous item has finished reading the gated tile (and its W2 slice)
+      mbar_wait(&w_empty, ((uint32_t)i & 1u) ^ 1u);
 #pragma unroll
       for (int tt = 0; tt < 3; ++tt) {
         if (tt < nt) {
@@ -658,12 +664,12 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
       }
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&st_full);
+      if (lane == 0) mbar_arrive(&g2_ready);
       if (++cg == p.groups) {
         // the tile's OUT accumulator is complete: BatchNorm + ReLU, bf16, NHWC rows
         mbar_wait(&out_full, (uint32_t)tile & 1u);
         tc_fence_after_sync();
-        const int ncol = p.Cout >> 2;                // columns of this epilogue group: 32 or 64 (16-column steps)
+        const int ncol = p.Cout >> 2;                // columns of this epilogue group: 32 or 64
         const uint32_t orow = tmem + ((uint32_t)(q * 32) << 16) + 256u + (uint32_t)(eg * ncol);
         __nv_bfloat16* dst = p.out + (((long)n * p.ho + h) * p.wo + w) * p.ld_out + eg * ncol;
         for (int c0 = 0; c0 < ncol; c0 += 32) {
@@ -854,7 +860,9 @@ static int rf_fused_launch(const void* x, long ldx, int N, int H, int W, int C, 
   p.tiles = (int)tiles;
   p.per_cta = (int)ceil_div(tiles, (long)device_sm_count());
   const unsigned grid = (unsigned)ceil_div(tiles, (long)p.per_cta);
-  const size_t smem = (size_t)kFuStages * 3 * kRtA + kRtA + kRtB1 + 9 * kRtA + (size_t)kFuW2Stages * 3 * Cout * 32 + 1024;
+  // two whole-item tap buffers when the W2 slice leaves room for them (Cout = 128), else one
+  p.a_slots = Cout <= 128 ? 2 : 1;
+  const size_t smem = (size_t)p.a_slots * 9 * kRtA + kRtA + kRtB1 + 9 * kRtA + (size_t)9 * Cout * 32 + 1024;
   static std::atomic<size_t> attr_set[64];
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
