@@ -511,8 +511,10 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
   } else if (warp == 1) {
     if (lane == 0) {
       // One lane issues everything: the generate MMAs of item i+1 go out before the second GEMM of item i, so the
-      // tensor pipe works on them while the epilogue warps gate item i.  (Measured: handing the second GEMM to a
-      // second issuing lane in warp 18 was slower — it delayed that warp's rewrite of the generate weight tiles.)
+      // tensor pipe works on them while the epilogue warps gate item i.  (Measured with tests/dev/rf_fused_probe.cu: a
+      // second issuing lane for the second GEMM — in warp 18 or in a twentieth warp of its own — was SLOWER, 110 -> 125 us
+      // on the 128-channel layer: the sixteen gating warps are the critical chain at ~2400 busy cycles per item, and the
+      // single lane's 19 MMAs + 3 commits fit inside it.)
       const uint32_t idesc = umma_idesc_bf16_f32(128, 144, 0, 0);
       const uint32_t idesc2 = umma_idesc_bf16_f32(128, p.Cout, 0, 0);
       const uint64_t a_desc0 = rt_desc_sw32(smem_u32(sA)), b_desc = rt_desc_sw32(smem_u32(sB));
@@ -520,12 +522,13 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
       const uint64_t g_desc0 = rt_desc_sw32(smem_u32(sStage)), w_desc0 = rt_desc_sw32(smem_u32(sW2));
       const uint32_t d_gen = tmem, d_out = tmem + 256u;
       int cg2 = 0, tile = 0;
+      RT_DBG_DECL
       for (int i = 0; i <= mine; ++i) {
         if (i < mine) {
           const int slot = nA == 2 ? (i & 1) : 0;
           const uint32_t use = (uint32_t)(nA == 2 ? (i >> 1) : i);
-          mbar_wait(&gen_ready, (uint32_t)i & 1u);
-          mbar_wait(&a_full[slot], use & 1u);
+          RT_WAIT(0, &gen_ready, (uint32_t)i & 1u);
+          RT_WAIT(1, &a_full[slot], use & 1u);
           tc_fence_after_sync();
           umma_bf16(d_gen, ones_desc, b_desc + (uint64_t)(9 * (kRtB >> 4)), idesc, 0u);   // acc = shift
           const uint64_t a_desc = a_desc0 + (uint64_t)(slot * (9 * kRtA >> 4));
@@ -537,7 +540,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
         }
         if (i > 0) {   // second GEMM of item i-1: OUT (+)= gated tile x its W2 slice
           if (cg2 == 0) mbar_wait(&out_empty, ((uint32_t)tile & 1u) ^ 1u);   // previous tile's output has left TMEM
-          mbar_wait(&g2_ready, (uint32_t)(i - 1) & 1u);
+          RT_WAIT(2, &g2_ready, (uint32_t)(i - 1) & 1u);
           tc_fence_after_sync();
 #pragma unroll
           for (int t = 0; t < 9; ++t)
@@ -551,8 +554,10 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
           }
         }
       }
+      RT_DBG_FLUSH(2, 3)
     }
   } else if (warp == 18) {
+    RT_DBG_DECL
     uint32_t off[5], soff[5];
 #pragma unroll
     for (int m = 0; m < 5; ++m) {
@@ -574,7 +579,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
     int cg = 0;
     if (mine > 0) fetch(0);
     for (int i = 0; i < mine; ++i) {
-      if (i > 0) mbar_wait(&tfull, ((uint32_t)i & 1u) ^ 1u);   // the generate MMAs of item i-1 have read the tiles
+      if (i > 0) RT_WAIT(0, &tfull, ((uint32_t)i & 1u) ^ 1u);   // the generate MMAs of item i-1 have read the tiles
 #pragma unroll
       for (int k = 0; k < 9; ++k)
 #pragma unroll
@@ -590,7 +595,9 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
       if (++cg == p.groups) cg = 0;
       if (i + 1 < mine) fetch(cg);
     }
+    RT_DBG_FLUSH(6, 1)
   } else {
+    RT_DBG_DECL
     const int q = warp & 3;
     const int eg = (warp - 2) >> 2;                 // t = 0..2 | 3,4 | 5,6 | 7,8;  output columns eg * Cout/4 ..
     const int t0 = eg == 0 ? 0 : 1 + 2 * eg, nt = eg == 0 ? 3 : 2;
@@ -629,7 +636,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
           se2[2 * j] = f2_pack(e.x, e.y); se2[2 * j + 1] = f2_pack(e.z, e.w);
         }
       }
-      mbar_wait(&tfull, (uint32_t)i & 1u);
+      RT_WAIT(0, &tfull, (uint32_t)i & 1u);
       tc_fence_after_sync();
       const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(t0 * 16);
       uint32_t acc[3][16];
@@ -653,7 +660,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
         }
       }
       // the second GEMM of the previous item has finished reading the gated tile (and its W2 slice)
-      mbar_wait(&w_empty, ((uint32_t)i & 1u) ^ 1u);
+      RT_WAIT(1, &w_empty, ((uint32_t)i & 1u) ^ 1u);
 #pragma unroll
       for (int tt = 0; tt < 3; ++tt) {
         if (tt < nt) {
@@ -667,7 +674,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
       if (lane == 0) mbar_arrive(&g2_ready);
       if (++cg == p.groups) {
         // the tile's OUT accumulator is complete: BatchNorm + ReLU, bf16, NHWC rows
-        mbar_wait(&out_full, (uint32_t)tile & 1u);
+        RT_WAIT(2, &out_full, (uint32_t)tile & 1u);
         tc_fence_after_sync();
         const int ncol = p.Cout >> 2;                // columns of this epilogue group: 32 or 64
         const uint32_t orow = tmem + ((uint32_t)(q * 32) << 16) + 256u + (uint32_t)(eg * ncol);
@@ -702,6 +709,7 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
         cg = 0; ++mt; ++tile; fresh = true;
       }
     }
+    if (warp == 2) { RT_DBG_FLUSH(8, 3) }
   }
   tc_fence_before_sync();
   __syncthreads();
