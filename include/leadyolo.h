@@ -284,9 +284,14 @@ int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int wo, int C, 
 int ly_rf_attention_bwd(const float* datt, const float* att, const float* maps, const int16_t* amax, int N, int ho,
                         int wo, int C, int k, const float* wa, float* dmaps, float* dwa, void* dG,
                         ly_stream_t stream); /* dG += route(dmax) + dmean/C ; dwa += */
+/* dx (may be NULL) = input gradient (+ extra[n][c], the SE pooling gradient already divided by H*W, may be NULL);
+ * dwgk (may be NULL) += weight gradient in the wgk layout.  wscratch (may be NULL): ly_rf_wgrad_scratch_floats(C, k) floats
+ * — with it every pixel lane stores its partial sums and a second launch adds them in order (no atomics, reproducible);
+ * without it the sums are added with float atomics. */
+long ly_rf_wgrad_scratch_floats(int C, int k);
 int ly_rf_generate_bwd(const void* dZ, const void* x, long ldx, int N, int H, int W, int C, int k, int s, int ho,
                        int wo, const float* wgk, const float* extra, void* dx, long lddx, float* dwgk,
-                       ly_stream_t stream);
+                       float* wscratch, long wscratch_floats, ly_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
  * Detection loss (utils/loss.py:121-268 ComputeLoss.__call__ / build_targets with the EIoU box term of

@@ -69,15 +69,20 @@ __device__ __forceinline__ void block_channel_reduce(const float (&a)[8], const 
   }
 }
 
-// s1 | s2 = Σ_b parts[b][0..2C) in block order
-__global__ void ordered_finalize_kernel(const float* __restrict__ parts, int B, int C, float* __restrict__ s1,
-                                        float* __restrict__ s2) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// s1 | s2 = Σ_b parts[b][0..2C): one warp per output, lane l adds blocks l, l+32, ... in order and the 32 lane sums are
+// folded by a fixed shuffle tree — the same order on every run.
+__global__ void __launch_bounds__(256) ordered_finalize_kernel(const float* __restrict__ parts, int B, int C,
+                                                               float* __restrict__ s1, float* __restrict__ s2) {
+  const int i = (int)(((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int lane = threadIdx.x & 31;
   if (i >= 2 * C) return;
   float a = 0.f;
-  for (int b = 0; b < B; ++b) a += parts[(long)b * 2 * C + i];
-  if (i < C) s1[i] = a;
-  else s2[i - C] = a;
+  for (int b = lane; b < B; b += 32) a += parts[(long)b * 2 * C + i];
+  a = warp_sum(a);
+  if (lane == 0) {
+    if (i < C) s1[i] = a;
+    else s2[i - C] = a;
+  }
 }
 
 // Same, but the block sums are added as 64-bit FIXED-POINT integers (value * 2^fa / 2^fb): integer addition is
@@ -379,7 +384,7 @@ extern "C" int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz,
       (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2, parts);
   LY_LAUNCH_CHECK();
   if (parts != nullptr) {
-    ordered_finalize_kernel<<<ceil_div(2 * C, 256), 256, 0, (cudaStream_t)st>>>(parts, rgrid, C, s1, s2);
+    ordered_finalize_kernel<<<ceil_div(2L * C * 32, 256), 256, 0, (cudaStream_t)st>>>(parts, rgrid, C, s1, s2);
     LY_LAUNCH_CHECK();
   }
   bn_act_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(

@@ -89,16 +89,26 @@ __global__ void __launch_bounds__(192) stem_wgrad_kernel(const Tin* __restrict__
   for (int j = 0; j < CG; ++j) acc[j] = 0.f;
   for (long base = (long)blockIdx.x * P; base < total; base += (long)gridDim.x * P) {
     __syncthreads();
-    for (int i = threadIdx.x; i < P * 48; i += blockDim.x) {
-      const int p = i / 48, kk = i % 48;
+    // one thread per (pixel, channel, kernel row): the four kx values are one aligned 4-element run of the image
+    for (int i = threadIdx.x; i < P * 12; i += blockDim.x) {
+      const int p = i / 12, ck = i % 12;
       const long pix = base + p;
-      float v = 0.f;
+      float v4[4] = {0.f, 0.f, 0.f, 0.f};
       if (pix < total) {
         const int wo = (int)(pix % Wo), ho = (int)((pix / Wo) % Ho), n = (int)(pix / ((long)Wo * Ho));
-        const int c = kk / 16, ky = (kk / 4) % 4, kx = kk % 4;
-        v = (float)img[(((long)n * 3 + c) * H + (ho * 4 + ky)) * W + wo * 4 + kx] * in_scale;
+        const int c = ck >> 2, ky = ck & 3;
+        const Tin* src = img + (((long)n * 3 + c) * H + (ho * 4 + ky)) * W + wo * 4;
+        if (sizeof(Tin) == 1) {
+          const uchar4 u = *reinterpret_cast<const uchar4*>(src);
+          v4[0] = (float)u.x * in_scale; v4[1] = (float)u.y * in_scale;
+          v4[2] = (float)u.z * in_scale; v4[3] = (float)u.w * in_scale;
+        } else {
+          const float4 f = *reinterpret_cast<const float4*>(src);
+          v4[0] = f.x * in_scale; v4[1] = f.y * in_scale; v4[2] = f.z * in_scale; v4[3] = f.w * in_scale;
+        }
       }
-      sx[p][kk] = v;
+#pragma unroll
+      for (int kx = 0; kx < 4; ++kx) sx[p][ck * 4 + kx] = v4[kx];
     }
     for (int i = threadIdx.x; i < P * COUT; i += blockDim.x) {
       const int p = i / COUT, co = i % COUT;

@@ -12,7 +12,7 @@ from ._lib import ConvDesc, LeadYoloError, check, lib, ptr, stream_ptr
 CL = torch.channels_last
 COUNT = [0]        # kernels launched through the C-ABI (bench.py: gpu_launches)
 PROFILE = None     # when a list: (entry point, start event, end event, algorithmic bytes, flops) per call
-_LAUNCHES = {"ly_gap_mean": 2, "ly_yolo_loss_fwd": 4, "ly_yolo_loss_bwd": 2, "ly_detect_nms": 2, "ly_rfcbam_front_infer": 3, "ly_bn_act_bwd": 3, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 2}
+_LAUNCHES = {"ly_gap_mean": 2, "ly_yolo_loss_fwd": 4, "ly_yolo_loss_bwd": 2, "ly_detect_nms": 2, "ly_rfcbam_front_infer": 3, "ly_bn_act_bwd": 3, "ly_rf_attention": 2, "ly_rf_attention_bwd": 2, "ly_rf_generate_bwd": 3}
 
 
 class _Prof:
@@ -189,7 +189,7 @@ _SIGS = {
     "ly_rf_se_att": "piiippipiippp",
     "ly_rf_gate_bwd": "ppiiiiiplpppp",
     "ly_rf_attention_bwd": "ppppiiiiipppp",
-    "ly_rf_generate_bwd": "ppliiiiiiiippplp",
+    "ly_rf_generate_bwd": "ppliiiiiiiippplppl",
 }
 _CT = {"p": C.c_void_p, "i": C.c_int, "l": C.c_long, "f": C.c_float}
 _prepared = {}
@@ -217,6 +217,14 @@ def call(name, *args):
         nbytes = float(sum(a.numel() * a.element_size() for a in args if isinstance(a, torch.Tensor)))
     with _Prof(name, nbytes, 0.0):
         check(fn(*conv, torch.cuda.current_stream().cuda_stream), name)
+
+
+def rf_wgrad_scratch(c, k, device):
+    """fp32 scratch of ly_rf_generate_bwd's weight-gradient pass (per-lane partial sums)."""
+    fn = lib().ly_rf_wgrad_scratch_floats
+    fn.argtypes = [C.c_int, C.c_int]
+    fn.restype = C.c_long
+    return torch.empty(int(fn(c, k)), dtype=torch.float32, device=device)
 
 
 def reduce_blocks(m, c):

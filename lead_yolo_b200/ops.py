@@ -548,7 +548,9 @@ class RfGenerateFn(torch.autograd.Function):
         n, c, h, w = x.shape
         dx = ll.empty_cl(n, c, h, w, device=x.device) if ctx.needs_input_grad[0] else None
         dwgk = zeros_f32(wgk.numel(), wgk.device).view(wgk.shape) if ctx.needs_input_grad[1] else None
-        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, dx, c, dwgk)
+        scr = ll.rf_wgrad_scratch(c, k, x.device) if dwgk is not None else None
+        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, dx, c, dwgk, scr,
+                0 if scr is None else scr.numel())
         dwg = None
         if dwgk is not None:
             dwg = dwgk.permute(2, 0, 1).reshape(c * k * k, 1, k, k).to(wdt)
@@ -584,7 +586,9 @@ class RfFrontFn(torch.autograd.Function):
             extra = (dgap.float() * (1.0 / (h * w))).reshape(n, c).contiguous()
         dx = ll.empty_cl(n, c, h, w, device=x.device) if ctx.needs_input_grad[0] else None
         dwgk = zeros_f32(wgk.numel(), wgk.device).view(wgk.shape) if ctx.needs_input_grad[1] else None
-        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, extra, dx, c, dwgk)
+        scr = ll.rf_wgrad_scratch(c, k, x.device) if dwgk is not None else None
+        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, extra, dx, c, dwgk, scr,
+                0 if scr is None else scr.numel())
         dwg = None
         if dwgk is not None:
             dwg = dwgk.permute(2, 0, 1).reshape(c * k * k, 1, k, k).to(wdt)
