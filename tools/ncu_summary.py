@@ -39,34 +39,52 @@ def launches(path, anchor="stem_"):
 
 
 def raw(path):
-    r = list(csv.reader(open(path)))
+    """Per-launch table from an `ncu --set full --csv --page raw` log: duration, DRAM bytes, DRAM / tensor-pipe / issue
+    utilisation, occupancy.  Column names are matched by suffix (recent ncu prefixes some with their section)."""
+    lines = [l for l in open(path) if not l.startswith("==")]
+    r = [row for row in csv.reader(lines) if row]
     hdr, units, rows = r[0], r[1], r[2:]
-    col = {h: i for i, h in enumerate(hdr)}
-    want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
-            "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
-            "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
-            "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size"]
-    print("kernel | " + " | ".join(f"{w} [{units[col[w]]}]" for w in want if w in col))
 
-    def val(row, w):
-        v = row[col[w]].replace(",", "")
+    def find(suffix):
+        for i, h in enumerate(hdr):
+            if h == suffix or h.endswith("." + suffix):
+                return i
+        return None
+
+    want = [("us", "gpu__time_duration.sum"), ("dram_rd_MB", "dram__bytes_read.sum"), ("dram_wr_MB", "dram__bytes_write.sum"),
+            ("dram_%", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+            ("tensor_%", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"),
+            ("issue_%", "sm__issue_active.avg.pct_of_peak_sustained_elapsed"),
+            ("warps_%", "sm__warps_active.avg.pct_of_peak_sustained_active"),
+            ("regs", "launch__registers_per_thread")]
+    cols = [(n, find(m)) for n, m in want]
+    kn, gs = find("Kernel Name"), find("Grid Size")
+
+    def val(row, i, name):
+        if i is None:
+            return float("nan")
         try:
-            f = float(v)
+            f = float(row[i].replace(",", ""))
         except ValueError:
-            return 0.0
-        u = units[col[w]].lower()
-        if w.startswith("dram__bytes"):
-            f *= {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(u, 1)
+            return float("nan")
+        u = units[i].lower()
+        if name == "us":
+            f *= {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6, "nsecond": 1e-3, "usecond": 1.0, "msecond": 1e3}.get(u, 1e-3)
+        if name.endswith("_MB"):
+            f *= {"byte": 1e-6, "kbyte": 1e-3, "mbyte": 1.0, "gbyte": 1e3}.get(u, 1e-6)
         return f
 
-    tot_r = tot_w = tot_t = 0.0
+    print(f"{'kernel':34s} {'grid':>14s} " + " ".join(f"{n:>10s}" for n, _ in cols))
+    tot = collections.defaultdict(float)
     for row in rows:
-        name = re.sub(r"\(.*", "", row[col["Kernel Name"]]).split("::")[-1][:28]
-        print(name + " | " + " | ".join(row[col[w]] for w in want if w in col))
-        tot_r += val(row, "dram__bytes_read.sum")
-        tot_w += val(row, "dram__bytes_write.sum")
-        tot_t += val(row, "gpu__time_duration.sum")
-    print(f"# totals over {len(rows)} launches: dram read {tot_r / 1e6:.1f} MB, write {tot_w / 1e6:.1f} MB")
+        name = re.sub(r"\(.*", "", row[kn]).split("::")[-1].replace("void ", "")[:34]
+        vals = [val(row, i, n) for n, i in cols]
+        print(f"{name:34s} {row[gs]:>14s} " + " ".join(f"{v:10.1f}" for v in vals))
+        for (n, _), v in zip(cols, vals):
+            if n in ("us", "dram_rd_MB", "dram_wr_MB") and v == v:
+                tot[n] += v
+    print(f"# totals over {len(rows)} launches: {tot['us']:.1f} us, DRAM read {tot['dram_rd_MB']:.1f} MB, "
+          f"write {tot['dram_wr_MB']:.1f} MB")
 
 
 if __name__ == "__main__":
