@@ -23,11 +23,12 @@ int flat_grid(long M, int V, int block) {
 }
 
 // Grid for the REDUCING kernels (statistics, BatchNorm-backward sums): every block ends with 2*C global atomics, so the
-// block count is kept low — at least 16 rows per thread, at most two blocks per SM.
+// block count is kept low — at least 16 rows per thread, at most four blocks per SM (1024 threads x 4-8 loads of 16 B
+// in flight per SM: the kernels are HBM-latency bound below that).
 int flat_grid_reduce(long M, int V, int block) {
   const int m = V / gcd_i(V, block);
   long want = (M * V + (long)block * 16 - 1) / ((long)block * 16);
-  const long cap = (long)device_sm_count() * 2;
+  const long cap = (long)device_sm_count() * 4;
   if (want > cap) want = cap;
   if (want < 1) want = 1;
   long g = (want + m - 1) / m * m;
@@ -239,17 +240,29 @@ __global__ void __launch_bounds__(256) bn_act_bwd_reduce_kernel(
     mu[j] = mean[v * 8 + j]; rs[j] = rstd[v * 8 + j];
     a1[j] = a2[j] = 0.f;
   }
-  for (long row = row0; row < M; row += rstep) {
+  auto accum = [&](const uint4& ug, const uint4& uf) {
     float g[8], f[8];
-    unpack8(ld16(dy + row * lddy + v * 8), g);
-    unpack8(ld16(z + row * ldz + v * 8), f);
+    unpack8(ug, g);
+    unpack8(uf, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float d = g[j] * act_grad(fmaf(f[j], sc[j], sh[j]), act);
       a1[j] += d;
       a2[j] = fmaf(d, (f[j] - mu[j]) * rs[j], a2[j]);
     }
+  };
+  long row = row0;
+  for (; row + 3 * rstep < M; row += 4 * rstep) {       // eight 16-byte loads in flight per thread
+    uint4 ug[4], uf[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      ug[i] = ld16(dy + (row + i * rstep) * lddy + v * 8);
+      uf[i] = ld16(z + (row + i * rstep) * ldz + v * 8);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) accum(ug[i], uf[i]);
   }
+  for (; row < M; row += rstep) accum(ld16(dy + row * lddy + v * 8), ld16(z + row * ldz + v * 8));
   block_channel_reduce(a1, a2, V, (long)blockIdx.x * blockDim.x, s1, s2, parts);
 }
 
@@ -268,10 +281,10 @@ __global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(
     m1[j] = training ? s1[v * 8 + j] * inv_n : 0.f;
     m2[j] = training ? s2[v * 8 + j] * inv_n : 0.f;
   }
-  for (long row = row0; row < M; row += rstep) {
+  auto apply = [&](long row, const uint4& ug, const uint4& uf) {
     float g[8], f[8];
-    unpack8(ld16(dy + row * lddy + v * 8), g);
-    unpack8(ld16(z + row * ldz + v * 8), f);
+    unpack8(ug, g);
+    unpack8(uf, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float d = g[j] * act_grad(fmaf(f[j], sc[j], sh[j]), act);
@@ -279,7 +292,15 @@ __global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(
       f[j] = sc[j] * (d - m1[j] - xh * m2[j]);
     }
     st16(dz + row * lddz + v * 8, pack8(f));
+  };
+  long row = row0;
+  for (; row + rstep < M; row += 2 * rstep) {           // four loads in flight per thread
+    const uint4 g0 = ld16(dy + row * lddy + v * 8), f0 = ld16(z + row * ldz + v * 8);
+    const uint4 g1 = ld16(dy + (row + rstep) * lddy + v * 8), f1 = ld16(z + (row + rstep) * ldz + v * 8);
+    apply(row, g0, f0);
+    apply(row + rstep, g1, f1);
   }
+  if (row < M) apply(row, ld16(dy + row * lddy + v * 8), ld16(z + row * ldz + v * 8));
 }
 
 // dz = dy * act'(.) where the derivative is taken from the OUTPUT y (relu, sigmoid, none).
@@ -512,13 +533,22 @@ __global__ void __launch_bounds__(256) bn_apply_train_kernel(
     sc[j] = g * rstd;
     sh[j] = b - mean * sc[j];
   }
-  for (long row = row0; row < M; row += rstep) {
+  auto apply = [&](long row, const uint4& u) {
     float f[8];
-    unpack8(ld16(z + row * ldz + v * 8), f);
+    unpack8(u, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = act_apply(fmaf(f[j], sc[j], sh[j]), act);
     st16(y + row * ldy + v * 8, pack8(f));
+  };
+  long row = row0;
+  for (; row + 3 * rstep < M; row += 4 * rstep) {
+    uint4 u[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) u[i] = ld16(z + (row + i * rstep) * ldz + v * 8);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) apply(row + i * rstep, u[i]);
   }
+  for (; row < M; row += rstep) apply(row, ld16(z + row * ldz + v * 8));
 }
 
 }  // namespace ly
