@@ -160,12 +160,6 @@ int ly_stem_wgrad(const void* img, int img_is_u8, int N, int H, int W, int Cout,
 int ly_fasternet_block_infer(const void* x, void* y, int N, int H, int W, int C, const void* wimg, int w_bytes,
                              int off_w2, int off_wc, const float* scale, const float* shift, ly_stream_t stream);
 
-/* FasterNet partial 3x3 convolution, inference (models/common.py:1416,1432-1437): out[p][co] = sum over the 3x3
- * taps and the first `cpp` channels of x (8-aligned slice; real width dim//4, the rest has zero weights).
- * wk: fp32 [9][cpp][cpp] (tap, ci, co); cpp in {8,16,24,32,40}.  CUDA cores, warp-uniform weights. */
-int ly_pconv3x3_fwd(const void* x, long ldx, int N, int H, int W, int cpp, const float* wk, void* out, long ldo,
-                    ly_stream_t stream);
-
 /* SPPF pooling (models/common.py:356,364-367): 5x5 / stride 1 / pad 2 max pool on an NHWC channel slice.
  * idx (optional, uint8 [pixels][C]) records the arg-max tap for ly_maxpool5_bwd. */
 int ly_maxpool5_fwd(const void* x, long ldx, int N, int H, int W, int C, void* y, long ldy, uint8_t* idx,

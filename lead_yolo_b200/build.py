@@ -67,6 +67,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         objs = list(ex.map(compile_one, sources()))
+    for stale in set(OBJ.glob("*.o")) - set(objs):      # objects of sources that no longer exist
+        stale.unlink()
     cmd = [nvcc, "-shared", "-o", str(OUT), *[str(o) for o in objs], "-cudart", "static"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

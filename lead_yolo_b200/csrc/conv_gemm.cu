@@ -15,6 +15,8 @@
 #include <mutex>
 #include <type_traits>
 
+#include <atomic>
+
 #include "ly_common.cuh"
 #include "ly_tc.cuh"
 #include "ly_tmap.h"
@@ -681,14 +683,14 @@ static void pick_tile(int Hout, int Wout, int* Wt, int* Ht) {
 }
 
 static int set_smem_attr_once() {
-  static std::once_flag flags[64];
+  // per device; the flag is set only after success, so a failed attempt is reported to every caller and retried
+  static std::atomic<bool> done[64];
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
-  cudaError_t err = cudaSuccess;
-  std::call_once(flags[dev & 63], [&] {
-    err = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  });
-  if (err != cudaSuccess) return fail(LY_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(err));
+  if (!done[dev & 63].load()) {
+    LY_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    done[dev & 63].store(true);
+  }
   return LY_OK;
 }
 

@@ -22,6 +22,8 @@
 // other widths use the per-layer kernels.
 #include <string.h>
 
+#include <atomic>
+
 #include "ly_common.cuh"
 #include "ly_tc.cuh"
 #include "ly_tmap.h"
@@ -610,12 +612,12 @@ static int launch_fnb80(const void* x, void* y, int N, int H, int W, const void*
   uint32_t box2[5] = {16, P, 1, Ht + 2, 1};
   rc = encode_sw32(&p.tap_map, x, dims2, str, box2);
   if (rc) return rc;
-  static bool attr_done[64] = {false};
+  static std::atomic<bool> attr_done[64];   // zero-initialised; set only after the attribute call succeeded
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
-  if (!attr_done[dev & 63]) {
+  if (!attr_done[dev & 63].load()) {
     LY_CUDA(cudaFuncSetAttribute(fasternet_block80_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    attr_done[dev & 63] = true;
+    attr_done[dev & 63].store(true);
   }
   const int sms = device_sm_count();
   const unsigned grid = (unsigned)(p.tiles < sms ? p.tiles : sms);
@@ -687,12 +689,12 @@ extern "C" int ly_fasternet_block_infer(const void* x, void* y, int N, int H, in
   const size_t fixed = (size_t)2 * kHaloBytes + (size_t)p.v_chunks * kXBytes + (size_t)w_bytes + 1024;
   p.xbufs = (fixed + 2 * kXBytes <= 112 * 1024) ? 2 : 1;
   const size_t smem = fixed + (size_t)p.xbufs * kXBytes;
-  static bool attr_done[64] = {false};
+  static std::atomic<bool> attr_done[64];   // zero-initialised; set only after the attribute call succeeded
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
-  if (!attr_done[dev & 63]) {
+  if (!attr_done[dev & 63].load()) {
     LY_CUDA(cudaFuncSetAttribute(fasternet_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_done[dev & 63] = true;
+    attr_done[dev & 63].store(true);
   }
   LY_REQUIRE(smem <= 200 * 1024, "ly_fasternet_block_infer: weight image too large (%d bytes)", w_bytes);
   p.tiles = p.tiles_w * p.tiles_h * N;

@@ -799,13 +799,13 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   const unsigned grid = (unsigned)ceil_div(items, (long)p.per_cta);
   const size_t smem0 = (size_t)6 * 3 * kRtA + kRtA + 2 * kRtB1 + 1024;
   const size_t smem1 = (size_t)4 * 3 * kRtA + kRtA + 2 * kRtB1 + 2 * kRtStage + 1024;
-  static bool attr_done[64] = {false};
+  static std::atomic<bool> attr_done[64];   // zero-initialised; set only after the attribute call succeeded
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
-  if (!attr_done[dev & 63]) {
+  if (!attr_done[dev & 63].load()) {
     LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem0));
     LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-    attr_done[dev & 63] = true;
+    attr_done[dev & 63].store(true);
   }
   if (mode == 0) {
     LY_CUDA(cudaMemsetAsync(maps, 0, sizeof(float) * 2 * (size_t)N * ho * 3 * wo * 3, stream));

@@ -9,6 +9,8 @@
 // Thread mapping of both passes: a warp = 32 consecutive output pixels x ONE 8-channel vector, so the k*k x k*k
 // depthwise weights, BN scale/shift of that vector are warp-uniform loads (one sector per warp instead of one per
 // lane); the kernels are then bound by the FMA pipe (k^4 MACs per output channel), not by weight traffic.
+#include <atomic>
+
 #include "ly_common.cuh"
 
 namespace ly {
@@ -541,13 +543,13 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
         rf1_stats_kernel<false><<<dim3((unsigned)bx1, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W,
                                                                                      V, wgk, scale, shift, maps, gap_sum);
     } else {
-      static bool attr_done[64] = {false};
+      static std::atomic<bool> attr_done[64];   // zero-initialised; set only after the attribute call succeeded
       int dev = 0;
       LY_CUDA(cudaGetDevice(&dev));
-      if (!attr_done[dev & 63]) {
+      if (!attr_done[dev & 63].load()) {
         LY_CUDA(cudaFuncSetAttribute(rf_stats_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
         LY_CUDA(cudaFuncSetAttribute(rf_apply_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-        attr_done[dev & 63] = true;
+        attr_done[dev & 63].store(true);
       }
       // k = 3: the features cost k^4 = 81 MACs per channel; store them once (in A) instead of recomputing in pass 2
       rf_stats_kernel<3><<<grid1, WPB * 32, sm1, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, WPB, s, ho, wo,

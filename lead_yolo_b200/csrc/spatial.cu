@@ -1,5 +1,7 @@
 // Spatial helper kernels (CUDA cores, HBM-bound): stem patch embedding from the raw image, 5x5 max pooling
 // chain of SPPF, nearest 2x upsample / concat slice copies, global average pooling.
+#include <atomic>
+
 #include "ly_common.cuh"
 
 namespace ly {
@@ -494,12 +496,12 @@ extern "C" int ly_sppf_pool3(const void* x, long ldx, int N, int H, int W, int C
   LY_REQUIRE(ystep % 8 == 0 && ystep >= C && 3 * ystep <= ldy, "ly_sppf_pool3: ystep=%ld invalid", ystep);
   LY_REQUIRE((long)H * W <= 1600, "ly_sppf_pool3: H*W=%ld exceeds 1600", (long)H * W);
   const size_t smem = (size_t)4 * H * W * sizeof(uint4);
-  static bool attr_done[64] = {false};
+  static std::atomic<bool> attr_done[64];   // zero-initialised; set only after the attribute call succeeded
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
-  if (!attr_done[dev & 63]) {
+  if (!attr_done[dev & 63].load()) {
     LY_CUDA(cudaFuncSetAttribute(sppf_pool3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 1600 * 16));
-    attr_done[dev & 63] = true;
+    attr_done[dev & 63].store(true);
   }
   sppf_pool3_kernel<<<(unsigned)(N * (C / 8)), 256, smem, (cudaStream_t)st>>>((const __nv_bfloat16*)x, ldx, H, W, C / 8,
                                                                              (__nv_bfloat16*)y, ldy, ystep);

@@ -17,6 +17,8 @@
 
 #include <cuda_fp16.h>
 
+#include <atomic>
+
 #include "ly_common.cuh"
 #include "ly_tc.cuh"
 
@@ -244,12 +246,12 @@ int stem_tc_u8(const uint8_t* img, int N, int H, int W, int Cout, const float* w
     if (r != CUDA_SUCCESS) return fail(LY_ECUDA, "cuTensorMapEncodeTiled(uint8 image) failed: %d", (int)r);
   }
   const size_t smem = 4 * (size_t)kStTile + 64 * 128 + (size_t)kStRawSlots * kStRaw + 1024;
-  static bool attr_done[64] = {false};
+  static std::atomic<bool> attr_done[64];   // zero-initialised; set only after the attribute call succeeded
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
-  if (!attr_done[dev & 63]) {
+  if (!attr_done[dev & 63].load()) {
     LY_CUDA(cudaFuncSetAttribute(stem_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done[dev & 63] = true;
+    attr_done[dev & 63].store(true);
   }
   const long cap = 2L * device_sm_count();
   stem_tc_kernel<<<(unsigned)(stages < cap ? stages : cap), kStThreads, smem, st>>>(p);

@@ -11,6 +11,8 @@
 
 #include <mutex>
 
+#include <atomic>
+
 #include "ly_common.cuh"
 #include "ly_tc.cuh"
 #include "ly_tmap.h"
@@ -274,15 +276,14 @@ extern "C" int ly_conv_wgrad(const ly_conv_desc* d, const void* dz, long dz_ld, 
   if (split > num_tiles) split = num_tiles;
   if (split < 1) split = 1;
 
-  static std::once_flag flags[64];
+  static std::atomic<bool> done[64];
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
   const size_t smem_bytes = (size_t)kWStages * 6 * kSlot + 1024;
-  cudaError_t err = cudaSuccess;
-  std::call_once(flags[dev & 63], [&] {
-    err = cudaFuncSetAttribute(wgrad_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-  });
-  if (err != cudaSuccess) return fail(LY_ECUDA, "cudaFuncSetAttribute(wgrad): %s", cudaGetErrorString(err));
+  if (!done[dev & 63].load()) {
+    LY_CUDA(cudaFuncSetAttribute(wgrad_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    done[dev & 63].store(true);
+  }
   dim3 grid((unsigned)split, (unsigned)cts, (unsigned)kgs);
   wgrad_gemm_kernel<<<grid, 192, smem_bytes, (cudaStream_t)stream>>>(p);
   LY_LAUNCH_CHECK();

@@ -248,9 +248,7 @@ class Upsample(nn.Module):
 # FasterNet — reference models/common.py:1411-1561
 # ------------------------------------------------------------------------------------------------------------
 # The partial conv runs on the implicit-GEMM kernel (tensor cores, 8-aligned channel slice, zero weight rows for the
-# untouched channels inside the slice); LY_PCONV_KERNEL=1 selects the FP32 CUDA-core kernel instead (A/B knob: it is
-# ~2.5x slower at C=80 since the GEMM kernel became persistent).
-_PCONV_KERNEL = bool(__import__('os').environ.get('LY_PCONV_KERNEL'))
+# untouched channels inside the slice).
 
 
 class Partial_conv3(nn.Module):
@@ -277,14 +275,6 @@ class Partial_conv3(nn.Module):
         w = self.partial_conv3.weight
         if x.shape[1] < cpp:
             raise LeadYoloError("Partial_conv3: channel count too small for the 8-aligned slice")
-        if fast and cpp in (8, 16, 24, 32, 40) and _PCONV_KERNEL:
-            wk = ops.cached([w], ("pconvk", cpp), lambda: nn.functional.pad(
-                w.detach().float(), (0, 0, 0, 0, 0, cpp - cp, 0, cpp - cp)).permute(2, 3, 1, 0).reshape(
-                    9, cpp, cpp).contiguous())
-            n, _, h, wd = x.shape
-            t1 = ll.empty_cl(n, cpp, h, wd, device=x.device)
-            ll.call("ly_pconv3x3_fwd", x, ll.pixel_ld(x), n, h, wd, cpp, wk, t1, cpp)
-            return t1
         if fast:
             wp = ops.cached([w], ("pconv", cpp), lambda: pack_conv_weight(
                 nn.functional.pad(w.detach().float(), (0, 0, 0, 0, 0, cpp - cp, 0, cpp - cp)), [cpp]))
