@@ -14,6 +14,7 @@ __global__ void __launch_bounds__(256) ca_mid_kernel(const __nv_bfloat16* __rest
                                                      const float* __restrict__ bh, const float* __restrict__ ww,
                                                      const float* __restrict__ bw, __nv_bfloat16* __restrict__ gates,
                                                      long ldg) {
+  pdl_enter();
   __shared__ float y[32];
   const long r = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -54,6 +55,7 @@ __global__ void __launch_bounds__(256) ca_mid_warp_kernel(const __nv_bfloat16* _
                                                           const float* __restrict__ wh, const float* __restrict__ bh,
                                                           const float* __restrict__ ww, const float* __restrict__ bw,
                                                           __nv_bfloat16* __restrict__ gates, long ldg) {
+  pdl_enter();
   constexpr int C = 32 * CPL;
   __shared__ __align__(16) float s_w1[8 * C], s_wx[8 * C], s_b[C], s_sc[8], s_sh[8];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -137,7 +139,7 @@ extern "C" int ly_ca_mid_infer(const void* pooled, long ldp, long rows, long nh,
     const int gh = (int)ceil_div(nh, per), gwb = (int)ceil_div(rows - nh, per);
     cudaStream_t s_ = (cudaStream_t)st;
 #define LY_CAMID(CPL)                                                                                                   \
-  ca_mid_warp_kernel<CPL><<<gh + gwb, 256, 0, s_>>>((const __nv_bfloat16*)pooled, ldp, rows, nh, gh, w1, scale, shift, wh, \
+  (void)launch(ca_mid_warp_kernel<CPL>, gh + gwb, 256, 0, s_, (const __nv_bfloat16*)pooled, ldp, rows, nh, gh, w1, scale, shift, wh, \
                                                     bh, ww, bw, (__nv_bfloat16*)gates, ldg)
     if (C == 64) LY_CAMID(2);
     else if (C == 128) LY_CAMID(4);
@@ -146,8 +148,8 @@ extern "C" int ly_ca_mid_infer(const void* pooled, long ldp, long rows, long nh,
     LY_LAUNCH_CHECK();
     return LY_OK;
   }
-  ca_mid_kernel<<<(unsigned)rows, 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)pooled, ldp, rows, nh, C, mip, w1,
-                                                             scale, shift, wh, bh, ww, bw, (__nv_bfloat16*)gates, ldg);
+  LY_CUDA(launch(ca_mid_kernel, (unsigned)rows, 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)pooled, ldp, rows, nh, C, mip, w1,
+                                                             scale, shift, wh, bh, ww, bw, (__nv_bfloat16*)gates, ldg));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

@@ -1,6 +1,7 @@
 // Library-wide plumbing of libleadyolo.so: error text, device check, TMA descriptor encoding.
 #include <cuda.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -25,6 +26,11 @@ int fail(int code, const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
   return code;
+}
+
+bool pdl_enabled() {
+  static const bool on = getenv("LY_NO_PDL") == nullptr;   // dev knob: plain stream-ordered launches
+  return on;
 }
 
 int device_sm_count() {

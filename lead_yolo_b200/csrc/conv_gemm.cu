@@ -421,6 +421,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
+  pdl_wait();   // everything above touched only this CTA's own state
   // folded BatchNorm / bias of every output channel, padded so that vector reads past Cout stay in bounds
   const int cpad = (p.Cout + 7) & ~7;
   for (int i = threadIdx.x; i < cpad; i += blockDim.x) {
@@ -431,6 +432,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_trigger();   // TMEM is ours: the next kernel's CTAs may come in behind the tail of this one
   const uint32_t tmem_base = tmem_base_s;
 
   const int tiles_m = p.tiles_w * p.tiles_h * p.n_img;
@@ -946,7 +948,7 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   const long num_tiles = (long)p.tiles_w * p.tiles_h * p.n_img * ny;
   const int sms = device_sm_count();
   dim3 grid((unsigned)(num_tiles < sms ? num_tiles : sms), 1, 1);
-  conv_gemm_kernel<<<grid, kThreads, smem_bytes, (cudaStream_t)stream>>>(p);
+  LY_CUDA(launch(conv_gemm_kernel, grid, kThreads, smem_bytes, (cudaStream_t)stream, p));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

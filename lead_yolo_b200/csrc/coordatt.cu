@@ -21,6 +21,7 @@ __global__ void __launch_bounds__(256) ca_reduce_kernel(const __nv_bfloat16* __r
                                                         const __nv_bfloat16* __restrict__ gate, long ldg, int N,
                                                         int H, int W, int V, int gw, int mode,
                                                         __nv_bfloat16* __restrict__ out, long ldo) {
+  pdl_enter();
   float acc[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
@@ -85,6 +86,7 @@ __global__ void __launch_bounds__(256) ca_reduce_kernel(const __nv_bfloat16* __r
 // loops are short dependent chains otherwise and the kernel runs at a third of the HBM rate.
 __global__ void __launch_bounds__(256) ca_pool_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int N, int H,
                                                       int W, int V, int gw, __nv_bfloat16* __restrict__ out, long ldo) {
+  pdl_enter();
   float acc[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
@@ -136,6 +138,7 @@ __global__ void __launch_bounds__(256) ca_pointwise_kernel(const __nv_bfloat16* 
                                                            const __nv_bfloat16* __restrict__ gate, long ldg, int N,
                                                            int H, int W, int V, int mode,
                                                            __nv_bfloat16* __restrict__ out, long ldo) {
+  pdl_enter();
   const IT total = (IT)N * (IT)H * (IT)W * (IT)V;
   const IT t = (IT)blockIdx.x * (IT)blockDim.x + (IT)threadIdx.x;
   if (t >= total) return;
@@ -174,13 +177,13 @@ static int launch_reduce(const void* x, long ldx, const void* dy, long lddy, con
   const int gw = ceil_div((long)N * W * V, 256);
   const int gh = ceil_div((long)N * H * V, 256);
   if (mode == 0) {
-    ca_pool_kernel<<<gw + gh, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, N, H, W, V, gw, (__nv_bfloat16*)out, ldo);
+    LY_CUDA(launch(ca_pool_kernel, gw + gh, 256, 0, st, (const __nv_bfloat16*)x, ldx, N, H, W, V, gw, (__nv_bfloat16*)out, ldo));
     LY_LAUNCH_CHECK();
     return LY_OK;
   }
-  ca_reduce_kernel<<<gw + gh, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy,
+  LY_CUDA(launch(ca_reduce_kernel, gw + gh, 256, 0, st, (const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy,
                                             (const __nv_bfloat16*)gate, ldg, N, H, W, V, gw, mode,
-                                            (__nv_bfloat16*)out, ldo);
+                                            (__nv_bfloat16*)out, ldo));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -209,11 +212,11 @@ extern "C" int ly_ca_apply(const void* x, long ldx, const void* gates, long ldg,
   const int V = C / 8;
   const long total = (long)N * H * W * V;
   if (total < (1L << 31))
-    ca_pointwise_kernel<unsigned><<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
-        (const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)gates, ldg, N, H, W, V, 0, (__nv_bfloat16*)out, ldo);
+    LY_CUDA(launch(ca_pointwise_kernel<unsigned>, ceil_div(total, 256), 256, 0, (cudaStream_t)st, 
+        (const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)gates, ldg, N, H, W, V, 0, (__nv_bfloat16*)out, ldo));
   else
-    ca_pointwise_kernel<long><<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
-        (const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)gates, ldg, N, H, W, V, 0, (__nv_bfloat16*)out, ldo);
+    LY_CUDA(launch(ca_pointwise_kernel<long>, ceil_div(total, 256), 256, 0, (cudaStream_t)st, 
+        (const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)gates, ldg, N, H, W, V, 0, (__nv_bfloat16*)out, ldo));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -240,11 +243,11 @@ extern "C" int ly_ca_pool_bwd(const void* dpooled, long ldp, int N, int H, int W
   const int V = C / 8;
   const long total = (long)N * H * W * V;
   if (total < (1L << 31))
-    ca_pointwise_kernel<unsigned><<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
-        nullptr, 0, (const __nv_bfloat16*)dpooled, ldp, N, H, W, V, 1, (__nv_bfloat16*)dx, ldx);
+    LY_CUDA(launch(ca_pointwise_kernel<unsigned>, ceil_div(total, 256), 256, 0, (cudaStream_t)st, 
+        nullptr, 0, (const __nv_bfloat16*)dpooled, ldp, N, H, W, V, 1, (__nv_bfloat16*)dx, ldx));
   else
-    ca_pointwise_kernel<long><<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
-        nullptr, 0, (const __nv_bfloat16*)dpooled, ldp, N, H, W, V, 1, (__nv_bfloat16*)dx, ldx);
+    LY_CUDA(launch(ca_pointwise_kernel<long>, ceil_div(total, 256), 256, 0, (cudaStream_t)st, 
+        nullptr, 0, (const __nv_bfloat16*)dpooled, ldp, N, H, W, V, 1, (__nv_bfloat16*)dx, ldx));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

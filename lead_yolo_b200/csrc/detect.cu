@@ -12,6 +12,7 @@ __global__ void __launch_bounds__(256) detect_decode_kernel(const float* __restr
                                                             const float* __restrict__ anchors /*[na][2], stride units*/,
                                                             float* __restrict__ raw, float* __restrict__ z,
                                                             long rows_total, long row_off) {
+  pdl_enter();
   const long total = (long)N * ny * nx * na;
   const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= total) return;
@@ -51,8 +52,8 @@ extern "C" int ly_detect_decode(const float* p, int N, int ny, int nx, int na, i
   LY_REQUIRE(z == nullptr || (row_off >= 0 && row_off + (long)na * ny * nx <= rows_total),
              "ly_detect_decode: rows out of range");
   const long total = (long)N * ny * nx * na;
-  detect_decode_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(p, N, ny, nx, na, no, stride, anchors, raw,
-                                                                          z, rows_total, row_off);
+  LY_CUDA(launch(detect_decode_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, p, N, ny, nx, na, no, stride, anchors, raw,
+                                                                          z, rows_total, row_off));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

@@ -74,6 +74,7 @@ __device__ __forceinline__ void block_channel_reduce(const float (&a)[8], const 
 // folded by a fixed shuffle tree — the same order on every run.
 __global__ void __launch_bounds__(256) ordered_finalize_kernel(const float* __restrict__ parts, int B, int C,
                                                                float* __restrict__ s1, float* __restrict__ s2) {
+  pdl_enter();
   const int i = (int)(((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
   if (i >= 2 * C) return;
@@ -121,6 +122,7 @@ __device__ __forceinline__ void st16(__nv_bfloat16* p, const uint4& u) { *reinte
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) col_stats_kernel(const __nv_bfloat16* __restrict__ x, long ld, long M, int V,
                                                         float* __restrict__ sum, float* __restrict__ sq) {
+  pdl_enter();
   LY_FLAT_SETUP(V)
   float s[8], q[8];
 #pragma unroll
@@ -163,6 +165,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
                                    const float* __restrict__ beta, float* running_mean, float* running_var,
                                    float* __restrict__ mean_out, float* __restrict__ rstd_out,
                                    float* __restrict__ scale_out, float* __restrict__ shift_out) {
+  pdl_enter();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float mean = sum[c] / n;
@@ -187,6 +190,7 @@ __global__ void bn_fold_kernel(int C, float eps, const float* __restrict__ gamma
                                const float* __restrict__ conv_bias, float* __restrict__ mean_out,
                                float* __restrict__ rstd_out, float* __restrict__ scale_out,
                                float* __restrict__ shift_out) {
+  pdl_enter();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float rstd = rsqrtf(rvar[c] + eps);
@@ -206,6 +210,7 @@ __global__ void __launch_bounds__(256) scale_shift_act_kernel(const __nv_bfloat1
                                                               int V, const float* __restrict__ scale,
                                                               const float* __restrict__ shift, int act,
                                                               __nv_bfloat16* __restrict__ y, long ldy) {
+  pdl_enter();
   LY_FLAT_SETUP(V)
   float sc[8], sh[8];
 #pragma unroll
@@ -232,6 +237,7 @@ __global__ void __launch_bounds__(256) bn_act_bwd_reduce_kernel(
     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
     const float* __restrict__ rstd, int act, float* __restrict__ s1, float* __restrict__ s2,
     float* __restrict__ parts) {
+  pdl_enter();
   LY_FLAT_SETUP(V)
   float sc[8], sh[8], mu[8], rs[8], a1[8], a2[8];
 #pragma unroll
@@ -271,6 +277,7 @@ __global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(
     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
     const float* __restrict__ rstd, int act, const float* __restrict__ s1, const float* __restrict__ s2,
     float inv_n, int training, __nv_bfloat16* __restrict__ dz, long lddz) {
+  pdl_enter();
   LY_FLAT_SETUP(V)
   float sc[8], sh[8], mu[8], rs[8], m1[8], m2[8];
 #pragma unroll
@@ -308,6 +315,7 @@ __global__ void __launch_bounds__(256) act_bwd_from_out_kernel(const __nv_bfloat
                                                                const __nv_bfloat16* __restrict__ y, long ldy, long M,
                                                                int V, int act, __nv_bfloat16* __restrict__ dz,
                                                                long lddz) {
+  pdl_enter();
   LY_FLAT_SETUP(V)
   for (long row = row0; row < M; row += rstep) {
     float g[8], f[8];
@@ -342,8 +350,8 @@ extern "C" int ly_col_stats(const void* x, long ld, long M, int C, float* sum, f
   if (rc) return rc;
   LY_REQUIRE(sum != nullptr, "ly_col_stats: null sum");
   const int V = C / 8;
-  col_stats_kernel<<<flat_grid_reduce(M, V, 256), 256, 0, (cudaStream_t)st>>>(
-      (const __nv_bfloat16*)x, ld, M, V, sum, sq);
+  LY_CUDA(launch(col_stats_kernel, flat_grid_reduce(M, V, 256), 256, 0, (cudaStream_t)st, 
+      (const __nv_bfloat16*)x, ld, M, V, sum, sq));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -353,9 +361,9 @@ extern "C" int ly_bn_finalize(const float* sum, const float* sq, int C, long n, 
                               float* mean_out, float* rstd_out, float* scale_out, float* shift_out,
                               ly_stream_t st) {
   LY_REQUIRE(sum && sq && mean_out && rstd_out && scale_out && shift_out && C > 0 && n > 0, "ly_bn_finalize: bad args");
-  bn_finalize_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)st>>>(sum, sq, C, (float)n, eps, momentum, gamma,
+  LY_CUDA(launch(bn_finalize_kernel, ceil_div(C, 128), 128, 0, (cudaStream_t)st, sum, sq, C, (float)n, eps, momentum, gamma,
                                                                       beta, running_mean, running_var, mean_out,
-                                                                      rstd_out, scale_out, shift_out);
+                                                                      rstd_out, scale_out, shift_out));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -364,8 +372,8 @@ extern "C" int ly_bn_fold(int C, float eps, const float* gamma, const float* bet
                           const float* running_var, const float* conv_bias, float* mean_out, float* rstd_out,
                           float* scale_out, float* shift_out, ly_stream_t st) {
   LY_REQUIRE(C > 0 && gamma && beta && running_mean && running_var && scale_out && shift_out, "ly_bn_fold: bad args");
-  bn_fold_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)st>>>(C, eps, gamma, beta, running_mean, running_var,
-                                                                  conv_bias, mean_out, rstd_out, scale_out, shift_out);
+  LY_CUDA(launch(bn_fold_kernel, ceil_div(C, 128), 128, 0, (cudaStream_t)st, C, eps, gamma, beta, running_mean, running_var,
+                                                                  conv_bias, mean_out, rstd_out, scale_out, shift_out));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -377,8 +385,8 @@ extern "C" int ly_scale_shift_act(const void* x, long ldx, long M, int C, const 
   rc = check_mat(y, ldy, M, C, "ly_scale_shift_act(y)");
   if (rc) return rc;
   const int V = C / 8;
-  scale_shift_act_kernel<<<flat_grid(M, V, 256), 256, 0, (cudaStream_t)st>>>(
-      (const __nv_bfloat16*)x, ldx, M, V, scale, shift, act, (__nv_bfloat16*)y, ldy);
+  LY_CUDA(launch(scale_shift_act_kernel, flat_grid(M, V, 256), 256, 0, (cudaStream_t)st, 
+      (const __nv_bfloat16*)x, ldx, M, V, scale, shift, act, (__nv_bfloat16*)y, ldy));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -401,16 +409,16 @@ extern "C" int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz,
   const int V = C / 8;
   const int grid = flat_grid(M, V, 256);
   const int rgrid = flat_grid_reduce(M, V, 256);
-  bn_act_bwd_reduce_kernel<<<rgrid, 256, 0, (cudaStream_t)st>>>(
-      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2, parts);
+  LY_CUDA(launch(bn_act_bwd_reduce_kernel, rgrid, 256, 0, (cudaStream_t)st, 
+      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2, parts));
   LY_LAUNCH_CHECK();
   if (parts != nullptr) {
-    ordered_finalize_kernel<<<ceil_div(2L * C * 32, 256), 256, 0, (cudaStream_t)st>>>(parts, rgrid, C, s1, s2);
+    LY_CUDA(launch(ordered_finalize_kernel, ceil_div(2L * C * 32, 256), 256, 0, (cudaStream_t)st, parts, rgrid, C, s1, s2));
     LY_LAUNCH_CHECK();
   }
-  bn_act_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(
+  LY_CUDA(launch(bn_act_bwd_apply_kernel, grid, 256, 0, (cudaStream_t)st, 
       (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2,
-      1.f / (float)M, training, (__nv_bfloat16*)dz, lddz);
+      1.f / (float)M, training, (__nv_bfloat16*)dz, lddz));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -426,8 +434,8 @@ extern "C" int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, lon
   LY_REQUIRE(act == LY_ACT_NONE || act == LY_ACT_RELU || act == LY_ACT_SIGMOID,
              "ly_act_bwd_from_out: activation %d has no output-only derivative", act);
   const int V = C / 8;
-  act_bwd_from_out_kernel<<<flat_grid(M, V, 256), 256, 0, (cudaStream_t)st>>>(
-      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)y, ldy, M, V, act, (__nv_bfloat16*)dz, lddz);
+  LY_CUDA(launch(act_bwd_from_out_kernel, flat_grid(M, V, 256), 256, 0, (cudaStream_t)st, 
+      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)y, ldy, M, V, act, (__nv_bfloat16*)dz, lddz));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -447,6 +455,7 @@ constexpr float kBnScale2 = 1048576.f;    // 2^20
 
 __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long ld, long M, int V,
                                                        float* __restrict__ acc) {
+  pdl_enter();
   const int C = V * 8;
   LY_FLAT_SETUP(V)
   float s[8], q[8], K[8];
@@ -501,6 +510,7 @@ __global__ void __launch_bounds__(256) bn_apply_train_kernel(
     const __nv_bfloat16* __restrict__ z, long ldz, long M, int V, const float* __restrict__ acc,
     const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum, float* running_mean,
     float* running_var, float* __restrict__ stats, int act, __nv_bfloat16* __restrict__ y, long ldy) {
+  pdl_enter();
   LY_FLAT_SETUP(V)
   const int C = V * 8;
   const float n = (float)M, inv_n = 1.f / n;
@@ -558,8 +568,8 @@ extern "C" int ly_bn_stats(const void* x, long ld, long M, int C, float* acc, ly
   if (rc) return rc;
   LY_REQUIRE(acc != nullptr, "ly_bn_stats: null accumulator");
   const int V = C / 8;
-  bn_stats_kernel<<<flat_grid_reduce(M, V, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)x, ld,
-                                                                                          M, V, acc);
+  LY_CUDA(launch(bn_stats_kernel, flat_grid_reduce(M, V, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)x, ld,
+                                                                                          M, V, acc));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -574,9 +584,9 @@ extern "C" int ly_bn_apply_train(const void* z, long ldz, long M, int C, const f
   LY_REQUIRE(acc && stats, "ly_bn_apply_train: null statistics");
   LY_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "ly_bn_apply_train: running statistics come in pairs");
   const int V = C / 8;
-  bn_apply_train_kernel<<<flat_grid(M, V, 256), 256, 0, (cudaStream_t)st>>>(
+  LY_CUDA(launch(bn_apply_train_kernel, flat_grid(M, V, 256), 256, 0, (cudaStream_t)st, 
       (const __nv_bfloat16*)z, ldz, M, V, acc, gamma, beta, eps, momentum, running_mean, running_var, stats, act,
-      (__nv_bfloat16*)y, ldy);
+      (__nv_bfloat16*)y, ldy));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(320) fasternet_block_kernel(const __grid_const
   }
   // the hidden tile's K padding (columns >= 2C of its last 64-wide chunk) is zeroed once and never written again
   for (int i = threadIdx.x; i < p.v_chunks * kXBytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(sV)[i] = make_uint4(0, 0, 0, 0);
+  pdl_wait();
   for (int i = threadIdx.x; i < 128; i += blockDim.x) {
     s_sc[i] = i < p.C2 ? p.scale[i] : 0.f;
     s_sh[i] = i < p.C2 ? p.shift[i] : 0.f;
@@ -122,6 +123,7 @@ __global__ void __launch_bounds__(320) fasternet_block_kernel(const __grid_const
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_trigger();
   const uint32_t tmem = tmem_base_s;
   // u is double buffered: phase A of tile i+1 runs while tile i is in its hidden epilogue / phase B / output epilogue
   const uint32_t tm_y = tmem + 2u * (uint32_t)p.C2;
@@ -400,12 +402,14 @@ __global__ void __launch_bounds__(320, 1) fasternet_block80_kernel(const __grid_
   // K padding of the hidden tile (columns 160..191 of chunk 2) and the halo overrun rows: zeroed once
   for (int i = threadIdx.x; i < 3 * kXBytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(sV)[i] = make_uint4(0, 0, 0, 0);
   for (int i = threadIdx.x; i < 2 * kHalo / 16; i += blockDim.x) reinterpret_cast<uint4*>(sHalo)[i] = make_uint4(0, 0, 0, 0);
+  pdl_wait();
   for (int i = threadIdx.x; i < C2; i += blockDim.x) { s_sc[i] = p.scale[i]; s_sh[i] = p.shift[i]; }
   fence_proxy_async_smem();
   if (warp == 2) tmem_alloc(&tmem_base_s, 512u);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_trigger();
   const uint32_t tmem = tmem_base_s;
   const uint32_t tm_y = tmem + 2u * C2;
 
@@ -621,7 +625,7 @@ static int launch_fnb80(const void* x, void* y, int N, int H, int W, const void*
   }
   const int sms = device_sm_count();
   const unsigned grid = (unsigned)(p.tiles < sms ? p.tiles : sms);
-  fasternet_block80_kernel<<<grid, 320, kSmem, (cudaStream_t)st>>>(p);
+  LY_CUDA(launch(fasternet_block80_kernel, grid, 320, kSmem, (cudaStream_t)st, p));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -701,7 +705,7 @@ extern "C" int ly_fasternet_block_infer(const void* x, void* y, int N, int H, in
   const int per_sm = smem <= 112 * 1024 ? 2 : 1;
   const long cap = (long)per_sm * device_sm_count();
   const unsigned grid = (unsigned)(p.tiles < cap ? p.tiles : cap);
-  fasternet_block_kernel<<<grid, 320, smem, (cudaStream_t)st>>>(p);
+  LY_CUDA(launch(fasternet_block_kernel, grid, 320, smem, (cudaStream_t)st, p));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

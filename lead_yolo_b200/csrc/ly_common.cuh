@@ -18,12 +18,12 @@ int fail(int code, const char* fmt, ...);
     if (!(cond)) return ::ly::fail(LY_EINVAL, __VA_ARGS__);     \
   } while (0)
 
-#define LY_CUDA(expr)                                                                             \
-  do {                                                                                            \
-    cudaError_t e__ = (expr);                                                                     \
-    if (e__ != cudaSuccess)                                                                       \
-      return ::ly::fail(LY_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, \
-                        __LINE__);                                                                \
+#define LY_CUDA(...)                                                                                     \
+  do {                                                                                                   \
+    cudaError_t e__ = (__VA_ARGS__);                                                                     \
+    if (e__ != cudaSuccess)                                                                              \
+      return ::ly::fail(LY_ECUDA, "%s failed: %s (%s:%d)", #__VA_ARGS__, cudaGetErrorString(e__), __FILE__, \
+                        __LINE__);                                                                       \
   } while (0)
 
 #define LY_LAUNCH_CHECK() LY_CUDA(cudaGetLastError())
@@ -34,7 +34,38 @@ int flat_grid(long M, int V, int block);
 
 static inline int ceil_div(long a, long b) { return (int)((a + b - 1) / b); }
 
+// Programmatic dependent launch.  A kernel started through ly::launch may become resident while the kernel before it
+// in the stream is still draining its last wave: its launch latency and its prologue (barrier init, TMEM allocation,
+// descriptor prefetch) then overlap that tail.  Contract for every kernel launched this way:
+//   * pdl_wait() before the first access to memory another kernel may have written (or may still read) — it returns
+//     when the preceding grid has completed and its writes are visible;
+//   * pdl_trigger() once the kernel holds its TMEM (a dependant that allocated first would starve it), else first thing.
+// Both are no-ops for a launch without the attribute (LY_NO_PDL=1, or <<<>>>).
+bool pdl_enabled();
+
 #if defined(__CUDACC__)
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() {
+  pdl_trigger();
+  pdl_wait();
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                          Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
+}
 // sigmoid through the hardware tanh: one MUFU op instead of ex2 + rcp (relative error ~2^-11, below bf16)
 __device__ __forceinline__ float fast_sigmoid(float v) {
   float t;

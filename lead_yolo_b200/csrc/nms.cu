@@ -18,6 +18,7 @@ namespace ly {
 __global__ void __launch_bounds__(256) nms_candidates_kernel(const float* __restrict__ pred, int bs, int rows, int no,
                                                              float conf_thres, unsigned long long* __restrict__ keys,
                                                              int* __restrict__ ncand, int cap) {
+  pdl_enter();
   const int img = blockIdx.y;
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= rows) return;
@@ -51,6 +52,7 @@ __global__ void __launch_bounds__(1024) nms_select_kernel(const float* __restric
                                                           const int* __restrict__ ncand, int cap, int cap2,
                                                           float iou_thres, float max_wh, int max_nms, int max_det,
                                                           float* __restrict__ det, int* __restrict__ det_count) {
+  pdl_enter();
   extern __shared__ __align__(16) unsigned char smraw[];
   unsigned long long* sk = reinterpret_cast<unsigned long long*>(smraw);
   Box* sb = reinterpret_cast<Box*>(smraw + (size_t)cap2 * 8);
@@ -193,10 +195,10 @@ extern "C" int ly_detect_nms(const float* pred, int bs, int rows, int no, float 
   LY_CUDA(cudaMemsetAsync(ncand, 0, (size_t)bs * 4, s));
   LY_CUDA(cudaMemsetAsync(det, 0, (size_t)bs * max_det * 6 * 4, s));
   dim3 g1((unsigned)ceil_div(rows, 256), (unsigned)bs);
-  nms_candidates_kernel<<<g1, 256, 0, s>>>(pred, bs, rows, no, conf_thres, keys, ncand, max_candidates);
+  LY_CUDA(launch(nms_candidates_kernel, g1, 256, 0, s, pred, bs, rows, no, conf_thres, keys, ncand, max_candidates));
   LY_LAUNCH_CHECK();
-  nms_select_kernel<<<bs, 1024, smem, s>>>(pred, rows, no, keys, ncand, max_candidates, cap2, iou_thres,
-                                           agnostic ? 0.f : 7680.f, 30000, max_det, det, det_count);
+  LY_CUDA(launch(nms_select_kernel, bs, 1024, smem, s, pred, rows, no, keys, ncand, max_candidates, cap2, iou_thres,
+                                           agnostic ? 0.f : 7680.f, 30000, max_det, det, det_count));
   LY_LAUNCH_CHECK();
   if (n_candidates != nullptr)
     LY_CUDA(cudaMemcpyAsync(n_candidates, ncand, (size_t)bs * 4, cudaMemcpyDeviceToDevice, s));

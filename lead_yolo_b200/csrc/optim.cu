@@ -14,6 +14,7 @@
 namespace ly {
 
 __global__ void __launch_bounds__(256) sq_sum_kernel(const float* __restrict__ g, long n, float* __restrict__ out) {
+  pdl_enter();
   __shared__ float sm[8];
   float a = 0.f;
   const long stride = (long)gridDim.x * blockDim.x * 4;
@@ -38,6 +39,7 @@ __global__ void __launch_bounds__(256) sgd_ema_kernel(float* __restrict__ p, con
                                                       float* __restrict__ mom, float* __restrict__ ema, long n, long n0,
                                                       long n1, const float* __restrict__ hp,
                                                       const float* __restrict__ grad_sq) {
+  pdl_enter();
   const float momentum = hp[3], wd = hp[4], max_norm = hp[5], d = hp[6], gs = hp[7];
   float clip = 1.f;
   if (max_norm > 0.f && grad_sq != nullptr) {
@@ -63,6 +65,7 @@ __global__ void __launch_bounds__(256) sgd_ema_kernel(float* __restrict__ p, con
 
 __global__ void __launch_bounds__(256) ema_kernel(float* __restrict__ ema, const float* __restrict__ src, long n,
                                                   const float* __restrict__ hp) {
+  pdl_enter();
   const float d = hp[6];
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
     ema[i] = fmaf(d, ema[i] - src[i], src[i]);
@@ -76,7 +79,7 @@ extern "C" int ly_sq_sum(const float* g, long n, float* out, ly_stream_t st) {
   LY_REQUIRE(g && out && n > 0, "ly_sq_sum: bad arguments");
   LY_REQUIRE(reinterpret_cast<uintptr_t>(g) % 16 == 0, "ly_sq_sum: pointer not 16-byte aligned");
   const int grid = (int)((n / 4 + 255) / 256 < device_sm_count() * 4 ? (n / 4 + 255) / 256 + 1 : device_sm_count() * 4);
-  sq_sum_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(g, n, out);
+  LY_CUDA(launch(sq_sum_kernel, grid, 256, 0, (cudaStream_t)st, g, n, out));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -86,7 +89,7 @@ extern "C" int ly_sgd_ema_step(float* params, const float* grads, float* momentu
   LY_REQUIRE(params && grads && momentum_buf && hp && n > 0, "ly_sgd_ema_step: null pointer");
   LY_REQUIRE(0 <= n0 && n0 <= n1 && n1 <= n, "ly_sgd_ema_step: group boundaries %ld, %ld outside [0, %ld]", n0, n1, n);
   const int grid = (int)((n + 255) / 256 < device_sm_count() * 8 ? (n + 255) / 256 : device_sm_count() * 8);
-  sgd_ema_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(params, grads, momentum_buf, ema, n, n0, n1, hp, grad_sq);
+  LY_CUDA(launch(sgd_ema_kernel, grid, 256, 0, (cudaStream_t)st, params, grads, momentum_buf, ema, n, n0, n1, hp, grad_sq));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -94,7 +97,7 @@ extern "C" int ly_sgd_ema_step(float* params, const float* grads, float* momentu
 extern "C" int ly_ema_update(float* ema, const float* src, long n, const float* hp, ly_stream_t st) {
   LY_REQUIRE(ema && src && hp && n > 0, "ly_ema_update: bad arguments");
   const int grid = (int)((n + 255) / 256 < device_sm_count() * 8 ? (n + 255) / 256 : device_sm_count() * 8);
-  ema_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(ema, src, n, hp);
+  LY_CUDA(launch(ema_kernel, grid, 256, 0, (cudaStream_t)st, ema, src, n, hp));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

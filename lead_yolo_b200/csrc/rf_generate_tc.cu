@@ -146,6 +146,8 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_trigger();
+  pdl_wait();
   const uint32_t tmem = tmem_base_s;
 
   const int first = (int)blockIdx.x * p.per_cta;
@@ -451,6 +453,8 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_fused_kernel(const __grid_co
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_trigger();
+  pdl_wait();
   const uint32_t tmem = tmem_base_s;
 
   const int tile0 = (int)blockIdx.x * p.per_cta;
@@ -809,9 +813,9 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   }
   if (mode == 0) {
     LY_CUDA(cudaMemsetAsync(maps, 0, sizeof(float) * 2 * (size_t)N * ho * 3 * wo * 3, stream));
-    rf_tc_kernel<0><<<grid, kRtThreads, smem0, stream>>>(p);
+    LY_CUDA(launch(rf_tc_kernel<0>, grid, kRtThreads, smem0, stream, p));
   } else {
-    rf_tc_kernel<1><<<grid, kRtThreads, smem1, stream>>>(p);
+    LY_CUDA(launch(rf_tc_kernel<1>, grid, kRtThreads, smem1, stream, p));
   }
   LY_LAUNCH_CHECK();
   return LY_OK;
@@ -878,7 +882,7 @@ static int rf_fused_launch(const void* x, long ldx, int N, int H, int W, int C, 
     LY_CUDA(cudaFuncSetAttribute(rf_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set[dev & 63].store(smem);
   }
-  rf_fused_kernel<<<grid, kRtThreads, smem, stream>>>(p);
+  LY_CUDA(launch(rf_fused_kernel, grid, kRtThreads, smem, stream, p));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

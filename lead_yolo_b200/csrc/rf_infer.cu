@@ -129,6 +129,7 @@ __global__ void __launch_bounds__(512, 1) rf_stats_kernel(const __nv_bfloat16* _
                                                           const float* __restrict__ shift, float* __restrict__ maps,
                                                           float* __restrict__ gap_sum, int use_atomics,
                                                           __nv_bfloat16* __restrict__ G) {
+  pdl_enter();
   constexpr int KK = K * K;
   extern __shared__ float dsm[];
   __shared__ int smax[KK][32];
@@ -230,6 +231,7 @@ __global__ void __launch_bounds__(256) rf_se_att_kernel(const float* __restrict_
                                                         float* __restrict__ se, const float* __restrict__ maps,
                                                         int HK, int WK, const float* __restrict__ wa,
                                                         float* __restrict__ att) {
+  pdl_enter();
   if ((int)blockIdx.x < N) {
     __shared__ float mean[512];
     __shared__ float hid[64];
@@ -290,6 +292,7 @@ __global__ void __launch_bounds__(256) rf_apply_kernel(const __nv_bfloat16* __re
                                                        const float* __restrict__ shift,
                                                        const float* __restrict__ se, const float* __restrict__ att,
                                                        __nv_bfloat16* __restrict__ A) {
+  pdl_enter();
   constexpr int KK = K * K;
   constexpr int VB = 8;
   extern __shared__ float dsm[];
@@ -345,6 +348,7 @@ __global__ void __launch_bounds__(256) rf_apply_kernel(const __nv_bfloat16* __re
 __global__ void __launch_bounds__(256) rf_gate2_kernel(const __nv_bfloat16* __restrict__ G, long M, int KK, int K,
                                                        int V, int ho, int wo, const float* __restrict__ se,
                                                        const float* __restrict__ att, __nv_bfloat16* __restrict__ A) {
+  pdl_enter();
   const long total = M * KK * V;
   const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= total) return;
@@ -371,6 +375,7 @@ __global__ void __launch_bounds__(256) rf1_stats_kernel(const __nv_bfloat16* __r
                                                         const float* __restrict__ wgk, const float* __restrict__ scale,
                                                         const float* __restrict__ shift, float* __restrict__ maps,
                                                         float* __restrict__ gap_sum) {
+  pdl_enter();
   const int C = V * 8;
   const int n = blockIdx.y;
   const int lane = threadIdx.x & 31;
@@ -455,6 +460,7 @@ __global__ void __launch_bounds__(256) rf1_apply_kernel(const __nv_bfloat16* __r
                                                         const float* __restrict__ wgk, const float* __restrict__ scale,
                                                         const float* __restrict__ shift, const float* __restrict__ se,
                                                         const float* __restrict__ att, __nv_bfloat16* __restrict__ A) {
+  pdl_enter();
   const int n = blockIdx.y;
   const int rows = 256 / V;
   const int v = threadIdx.x % V, row = threadIdx.x / V;
@@ -537,11 +543,11 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
       if (bx1 > ceil_div(H * W, 32)) bx1 = ceil_div(H * W, 32);
       if (bx1 < 1) bx1 = 1;
       if (V > 32)
-        rf1_stats_kernel<true><<<dim3((unsigned)bx1, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W,
-                                                                                    V, wgk, scale, shift, maps, gap_sum);
+        LY_CUDA(launch(rf1_stats_kernel<true>, dim3((unsigned)bx1, (unsigned)N), 256, 0, stream, (const __nv_bfloat16*)x, ldx, H * W,
+                                                                                    V, wgk, scale, shift, maps, gap_sum));
       else
-        rf1_stats_kernel<false><<<dim3((unsigned)bx1, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W,
-                                                                                     V, wgk, scale, shift, maps, gap_sum);
+        LY_CUDA(launch(rf1_stats_kernel<false>, dim3((unsigned)bx1, (unsigned)N), 256, 0, stream, (const __nv_bfloat16*)x, ldx, H * W,
+                                                                                     V, wgk, scale, shift, maps, gap_sum));
     } else {
       static std::atomic<bool> attr_done[64];   // zero-initialised; set only after the attribute call succeeded
       int dev = 0;
@@ -552,15 +558,15 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
         attr_done[dev & 63].store(true);
       }
       // k = 3: the features cost k^4 = 81 MACs per channel; store them once (in A) instead of recomputing in pass 2
-      rf_stats_kernel<3><<<grid1, WPB * 32, sm1, stream>>>((const __nv_bfloat16*)x, ldx, M, H, W, V, WPB, s, ho, wo,
+      LY_CUDA(launch(rf_stats_kernel<3>, grid1, WPB * 32, sm1, stream, (const __nv_bfloat16*)x, ldx, M, H, W, V, WPB, s, ho, wo,
                                                           wgk, scale, shift, maps, gap_sum, vgroups > 1,
-                                                          (__nv_bfloat16*)A);
+                                                          (__nv_bfloat16*)A));
     }
     LY_LAUNCH_CHECK();
   }
   const long tot_att = (long)N * ho * k * wo * k;
-  rf_se_att_kernel<<<N + ceil_div(tot_att, 256), 256, 0, stream>>>(gap_sum, N, C, 1.f / (float)(H * W), w1, w2, R, se,
-                                                                  maps, ho * k, wo * k, wa, att);
+  LY_CUDA(launch(rf_se_att_kernel, N + ceil_div(tot_att, 256), 256, 0, stream, gap_sum, N, C, 1.f / (float)(H * W), w1, w2, R, se,
+                                                                  maps, ho * k, wo * k, wa, att));
   LY_LAUNCH_CHECK();
   {
     const int vg8 = ceil_div(V, 8);
@@ -576,12 +582,12 @@ extern "C" int ly_rfcbam_front_infer(const void* x, long ldx, int N, int H, int 
       const long cap = ceil_div((long)sms * 16, (long)N);
       if (bxa > cap) bxa = cap;
       if (bxa < 1) bxa = 1;
-      rf1_apply_kernel<<<dim3((unsigned)bxa, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, H * W, V, wgk,
-                                                                            scale, shift, se, att, (__nv_bfloat16*)A);
+      LY_CUDA(launch(rf1_apply_kernel, dim3((unsigned)bxa, (unsigned)N), 256, 0, stream, (const __nv_bfloat16*)x, ldx, H * W, V, wgk,
+                                                                            scale, shift, se, att, (__nv_bfloat16*)A));
     }
     else
-      rf_gate2_kernel<<<ceil_div(M * KK * V, 256), 256, 0, stream>>>((const __nv_bfloat16*)A, M, KK, k, V, ho, wo, se,
-                                                                    att, (__nv_bfloat16*)A);
+      LY_CUDA(launch(rf_gate2_kernel, ceil_div(M * KK * V, 256), 256, 0, stream, (const __nv_bfloat16*)A, M, KK, k, V, ho, wo, se,
+                                                                    att, (__nv_bfloat16*)A));
   }
   LY_LAUNCH_CHECK();
   return LY_OK;
@@ -594,6 +600,7 @@ namespace ly {
 template <bool PARTS>
 __global__ void __launch_bounds__(256) rf_gap_sum_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int HW, int V,
                                                          int Vp, float* __restrict__ gap_sum) {
+  pdl_enter();
   __shared__ float red[256 * 8];
   const int n = blockIdx.y;
   const int v = threadIdx.x % Vp, row = threadIdx.x / Vp, rows = 256 / Vp;
@@ -638,6 +645,7 @@ __global__ void __launch_bounds__(256) rf_gap_sum_kernel(const __nv_bfloat16* __
 
 // out[n][c] = bf16( (Σ_b parts[b][n][c]) / HW ), the partials added in index order
 __global__ void gap_finish_kernel(const float* __restrict__ parts, int B, long NC, float inv, __nv_bfloat16* __restrict__ out) {
+  pdl_enter();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= NC) return;
   float a = 0.f;
@@ -659,8 +667,8 @@ extern "C" int ly_rf_gap_sum(const void* x, long ldx, int N, int HW, int C, floa
   const long cap = ceil_div(8L * device_sm_count(), (long)N);
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
-  rf_gap_sum_kernel<false><<<dim3((unsigned)bx, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, HW, V, Vp,
-                                                                               gap_sum);
+  LY_CUDA(launch(rf_gap_sum_kernel<false>, dim3((unsigned)bx, (unsigned)N), 256, 0, stream, (const __nv_bfloat16*)x, ldx, HW, V, Vp,
+                                                                               gap_sum));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -674,12 +682,12 @@ extern "C" int ly_gap_mean(const void* x, long ldx, int N, int HW, int C, float*
   const int V = C / 8;
   int Vp = 1;
   while (Vp < V) Vp *= 2;
-  rf_gap_sum_kernel<true><<<dim3(LY_GAP_PARTS, (unsigned)N), 256, 0, stream>>>((const __nv_bfloat16*)x, ldx, HW, V, Vp,
-                                                                              parts);
+  LY_CUDA(launch(rf_gap_sum_kernel<true>, dim3(LY_GAP_PARTS, (unsigned)N), 256, 0, stream, (const __nv_bfloat16*)x, ldx, HW, V, Vp,
+                                                                              parts));
   LY_LAUNCH_CHECK();
   const long NC = (long)N * C;
-  gap_finish_kernel<<<ceil_div(NC, 256), 256, 0, stream>>>(parts, LY_GAP_PARTS, NC, 1.f / (float)HW,
-                                                           (__nv_bfloat16*)out);
+  LY_CUDA(launch(gap_finish_kernel, ceil_div(NC, 256), 256, 0, stream, parts, LY_GAP_PARTS, NC, 1.f / (float)HW,
+                                                           (__nv_bfloat16*)out));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -690,8 +698,8 @@ extern "C" int ly_rf_se_att(const float* gap_sum, int N, int C, int HW, const fl
                             ly_stream_t st) {
   LY_REQUIRE(gap_sum && w1 && w2 && maps && wa && se && att && R > 0 && R <= 64 && C <= 512, "ly_rf_se_att: bad args");
   const long tot = (long)N * HK * WK;
-  rf_se_att_kernel<<<N + ceil_div(tot, 256), 256, 0, (cudaStream_t)st>>>(gap_sum, N, C, 1.f / (float)HW, w1, w2, R, se,
-                                                                        maps, HK, WK, wa, att);
+  LY_CUDA(launch(rf_se_att_kernel, N + ceil_div(tot, 256), 256, 0, (cudaStream_t)st, gap_sum, N, C, 1.f / (float)HW, w1, w2, R, se,
+                                                                        maps, HK, WK, wa, att));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(128) rf_generate_kernel(const __nv_bfloat16* _
                                                           const float* __restrict__ scale,
                                                           const float* __restrict__ shift, int act,
                                                           __nv_bfloat16* __restrict__ G) {
+  pdl_enter();
   constexpr int KK = K * K;
   const int C = V * 8;
   const long total = (long)N * ho * wo * V;
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(128) rf_generate_kernel(const __nv_bfloat16* _
 __global__ void __launch_bounds__(256) rf_poolc_kernel(const __nv_bfloat16* __restrict__ G, long M, int KK, int K,
                                                        int V, int ho, int wo, float* __restrict__ maps,
                                                        int16_t* __restrict__ amax) {
+  pdl_enter();
   const int lane = threadIdx.x & 31;
   const long wid = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (wid >= M * KK) return;
@@ -117,6 +119,7 @@ __global__ void __launch_bounds__(256) rf_poolc_kernel(const __nv_bfloat16* __re
 __global__ void __launch_bounds__(256) rf_att_kernel(const float* __restrict__ maps, int N, int HK, int WK,
                                                      const float* __restrict__ wa /*[2][3][3]*/,
                                                      float* __restrict__ att) {
+  pdl_enter();
   const long total = (long)N * HK * WK;
   const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= total) return;
@@ -141,6 +144,7 @@ __global__ void __launch_bounds__(256) rf_gate_kernel(const __nv_bfloat16* __res
                                                       int V, int ho, int wo, const __nv_bfloat16* __restrict__ se,
                                                       long ldse, const float* __restrict__ att,
                                                       __nv_bfloat16* __restrict__ A) {
+  pdl_enter();
   const long total = M * KK * V;
   const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= total) return;
@@ -170,6 +174,7 @@ __global__ void __launch_bounds__(256) rf_gate_bwd_kernel(const __nv_bfloat16* _
                                                           long ldse, const float* __restrict__ att,
                                                           __nv_bfloat16* __restrict__ dG, float* __restrict__ dse,
                                                           float* __restrict__ datt) {
+  pdl_enter();
   const int lane = threadIdx.x & 31;
   const int n = blockIdx.y;
   const int C = V * 8;
@@ -242,6 +247,7 @@ __global__ void __launch_bounds__(256) rf_att_bwd_kernel(const float* __restrict
                                                          const float* __restrict__ maps, int N, int HK, int WK,
                                                          const float* __restrict__ wa, float* __restrict__ dmaps,
                                                          float* __restrict__ dwa) {
+  pdl_enter();
   __shared__ float sw[18];
   if (threadIdx.x < 18) sw[threadIdx.x] = 0.f;
   __syncthreads();
@@ -294,6 +300,7 @@ __global__ void __launch_bounds__(256) rf_att_bwd_kernel(const float* __restrict
 __global__ void __launch_bounds__(256) rf_poolc_bwd_kernel(__nv_bfloat16* __restrict__ dG, long M, int KK, int K,
                                                            int V, int ho, int wo, const float* __restrict__ dmaps,
                                                            const int16_t* __restrict__ amax) {
+  pdl_enter();
   const long total = M * KK * V;
   const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= total) return;
@@ -325,6 +332,7 @@ __global__ void __launch_bounds__(128) rf_generate_dx_kernel(const __nv_bfloat16
                                                              const float* __restrict__ wgk,
                                                              const float* __restrict__ extra,
                                                              __nv_bfloat16* __restrict__ dx, long lddx) {
+  pdl_enter();
   constexpr int KK = K * K;
   const int C = V * 8;
   const long total = (long)N * H * W * V;
@@ -378,6 +386,7 @@ __global__ void __launch_bounds__(288, 3) rf_generate_wgrad_kernel(const __nv_bf
                                                                    const __nv_bfloat16* __restrict__ x, long ldx, int N,
                                                                    int H, int W, int V, int s, int ho, int wo,
                                                                    float* __restrict__ dwgk, float* __restrict__ parts) {
+  pdl_enter();
   // A thread owns (vector v, feature t, kernel ROW i): K x 8 sums.  Splitting the k*k taps over K threads keeps the
   // register count low enough for three blocks per SM — the loop is bound by memory latency (ncu: 14 % warps active and
   // 15 stalled-on-scoreboard warps per issue with one 115-register block per SM), and two pixels are in flight per thread.
@@ -458,6 +467,7 @@ __global__ void __launch_bounds__(288, 3) rf_generate_wgrad_kernel(const __nv_bf
 // dwgk[o] += Σ_rows parts[row][o]: one warp per output, lane l adds rows l, l+32, ... in order, fixed shuffle tree
 __global__ void __launch_bounds__(256) rf_wgrad_finalize_kernel(const float* __restrict__ parts, int rows, long outs,
                                                                 float* __restrict__ dwgk) {
+  pdl_enter();
   const long o = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (o >= outs) return;
@@ -499,11 +509,11 @@ extern "C" int ly_rf_generate(const void* x, long ldx, int N, int H, int W, int 
   const int V = C / 8;
   const long total = (long)N * ho * wo * V;
   if (k == 1)
-    rf_generate_kernel<1><<<ceil_div(total, 128), 128, 0, (cudaStream_t)st>>>(
-        (const __nv_bfloat16*)x, ldx, N, H, W, V, s, ho, wo, wgk, scale, shift, act, (__nv_bfloat16*)G);
+    LY_CUDA(launch(rf_generate_kernel<1>, ceil_div(total, 128), 128, 0, (cudaStream_t)st, 
+        (const __nv_bfloat16*)x, ldx, N, H, W, V, s, ho, wo, wgk, scale, shift, act, (__nv_bfloat16*)G));
   else
-    rf_generate_kernel<3><<<ceil_div(total, 128), 128, 0, (cudaStream_t)st>>>(
-        (const __nv_bfloat16*)x, ldx, N, H, W, V, s, ho, wo, wgk, scale, shift, act, (__nv_bfloat16*)G);
+    LY_CUDA(launch(rf_generate_kernel<3>, ceil_div(total, 128), 128, 0, (cudaStream_t)st, 
+        (const __nv_bfloat16*)x, ldx, N, H, W, V, s, ho, wo, wgk, scale, shift, act, (__nv_bfloat16*)G));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -513,11 +523,11 @@ extern "C" int ly_rf_attention(const void* G, int N, int ho, int wo, int C, int 
   LY_REQUIRE(G && wa && maps && att && LY_ALIGNED16(G) && C % 8 == 0 && C > 0, "ly_rf_attention: bad args");
   const int V = C / 8, KK = k * k;
   const long M = (long)N * ho * wo;
-  rf_poolc_kernel<<<ceil_div(M * KK * 32, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)G, M, KK, k, V, ho,
-                                                                          wo, maps, amax);
+  LY_CUDA(launch(rf_poolc_kernel, ceil_div(M * KK * 32, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)G, M, KK, k, V, ho,
+                                                                          wo, maps, amax));
   LY_LAUNCH_CHECK();
   const long total = (long)N * ho * k * wo * k;
-  rf_att_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(maps, N, ho * k, wo * k, wa, att);
+  LY_CUDA(launch(rf_att_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, maps, N, ho * k, wo * k, wa, att));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -529,8 +539,8 @@ extern "C" int ly_rf_gate(const void* G, int N, int ho, int wo, int C, int k, co
              "ly_rf_gate: bad args");
   const int V = C / 8, KK = k * k;
   const long M = (long)N * ho * wo;
-  rf_gate_kernel<<<ceil_div(M * KK * V, 256), 256, 0, (cudaStream_t)st>>>(
-      (const __nv_bfloat16*)G, M, KK, k, V, ho, wo, (const __nv_bfloat16*)se, ldse, att, (__nv_bfloat16*)A);
+  LY_CUDA(launch(rf_gate_kernel, ceil_div(M * KK * V, 256), 256, 0, (cudaStream_t)st, 
+      (const __nv_bfloat16*)G, M, KK, k, V, ho, wo, (const __nv_bfloat16*)se, ldse, att, (__nv_bfloat16*)A));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -542,9 +552,9 @@ extern "C" int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int 
   const long per_img = (long)ho * wo * KK;
   (void)per_img;
   dim3 grid(LY_RF_GATE_PARTS, N);   // fixed: the caller sizes dse as [LY_RF_GATE_PARTS][N][C]
-  rf_gate_bwd_kernel<<<grid, 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)dA, (const __nv_bfloat16*)G, KK, k, V,
+  LY_CUDA(launch(rf_gate_bwd_kernel, grid, 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)dA, (const __nv_bfloat16*)G, KK, k, V,
                                                         ho, wo, (const __nv_bfloat16*)se, ldse, att,
-                                                        (__nv_bfloat16*)dG, dse, datt);
+                                                        (__nv_bfloat16*)dG, dse, datt));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -556,11 +566,11 @@ extern "C" int ly_rf_attention_bwd(const float* datt, const float* att, const fl
   const int V = C / 8, KK = k * k;
   const long M = (long)N * ho * wo;
   const long total = (long)N * ho * k * wo * k;
-  rf_att_bwd_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(datt, att, maps, N, ho * k, wo * k, wa, dmaps,
-                                                                       dwa);
+  LY_CUDA(launch(rf_att_bwd_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, datt, att, maps, N, ho * k, wo * k, wa, dmaps,
+                                                                       dwa));
   LY_LAUNCH_CHECK();
-  rf_poolc_bwd_kernel<<<ceil_div(M * KK * V, 256), 256, 0, (cudaStream_t)st>>>((__nv_bfloat16*)dG, M, KK, k, V, ho, wo,
-                                                                              dmaps, amax);
+  LY_CUDA(launch(rf_poolc_bwd_kernel, ceil_div(M * KK * V, 256), 256, 0, (cudaStream_t)st, (__nv_bfloat16*)dG, M, KK, k, V, ho, wo,
+                                                                              dmaps, amax));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -585,11 +595,11 @@ extern "C" int ly_rf_generate_bwd(const void* dZ, const void* x, long ldx, int N
     LY_REQUIRE(LY_ALIGNED16(dx) && lddx % 8 == 0 && lddx >= C, "ly_rf_generate_bwd: bad dx");
     const long total = (long)N * H * W * V;
     if (k == 1)
-      rf_generate_dx_kernel<1><<<ceil_div(total, 128), 128, 0, (cudaStream_t)st>>>(
-          (const __nv_bfloat16*)dZ, N, H, W, V, s, ho, wo, wgk, extra, (__nv_bfloat16*)dx, lddx);
+      LY_CUDA(launch(rf_generate_dx_kernel<1>, ceil_div(total, 128), 128, 0, (cudaStream_t)st, 
+          (const __nv_bfloat16*)dZ, N, H, W, V, s, ho, wo, wgk, extra, (__nv_bfloat16*)dx, lddx));
     else
-      rf_generate_dx_kernel<3><<<ceil_div(total, 128), 128, 0, (cudaStream_t)st>>>(
-          (const __nv_bfloat16*)dZ, N, H, W, V, s, ho, wo, wgk, extra, (__nv_bfloat16*)dx, lddx);
+      LY_CUDA(launch(rf_generate_dx_kernel<3>, ceil_div(total, 128), 128, 0, (cudaStream_t)st, 
+          (const __nv_bfloat16*)dZ, N, H, W, V, s, ho, wo, wgk, extra, (__nv_bfloat16*)dx, lddx));
     LY_LAUNCH_CHECK();
   }
   if (dwgk != nullptr) {
@@ -606,22 +616,22 @@ extern "C" int ly_rf_generate_bwd(const void* dZ, const void* x, long ldx, int N
     const bool use_parts = wscratch != nullptr && wscratch_floats >= lanes * outs;
     if (k == 1) {
       if (use_parts)
-        rf_generate_wgrad_kernel<1, true><<<grid, 288, 0, stream>>>((const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x, ldx,
-                                                                    N, H, W, V, s, ho, wo, dwgk, wscratch);
+        LY_CUDA(launch(rf_generate_wgrad_kernel<1, true>, grid, 288, 0, stream, (const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x, ldx,
+                                                                    N, H, W, V, s, ho, wo, dwgk, wscratch));
       else
-        rf_generate_wgrad_kernel<1, false><<<grid, 288, 0, stream>>>((const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x, ldx,
-                                                                     N, H, W, V, s, ho, wo, dwgk, nullptr);
+        LY_CUDA(launch(rf_generate_wgrad_kernel<1, false>, grid, 288, 0, stream, (const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x, ldx,
+                                                                     N, H, W, V, s, ho, wo, dwgk, nullptr));
     } else {
       if (use_parts)
-        rf_generate_wgrad_kernel<3, true><<<grid, 288, 0, stream>>>((const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x, ldx,
-                                                                    N, H, W, V, s, ho, wo, dwgk, wscratch);
+        LY_CUDA(launch(rf_generate_wgrad_kernel<3, true>, grid, 288, 0, stream, (const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x, ldx,
+                                                                    N, H, W, V, s, ho, wo, dwgk, wscratch));
       else
-        rf_generate_wgrad_kernel<3, false><<<grid, 288, 0, stream>>>((const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x, ldx,
-                                                                     N, H, W, V, s, ho, wo, dwgk, nullptr);
+        LY_CUDA(launch(rf_generate_wgrad_kernel<3, false>, grid, 288, 0, stream, (const __nv_bfloat16*)dZ, (const __nv_bfloat16*)x, ldx,
+                                                                     N, H, W, V, s, ho, wo, dwgk, nullptr));
     }
     LY_LAUNCH_CHECK();
     if (use_parts) {
-      rf_wgrad_finalize_kernel<<<ceil_div(outs * 32, 256), 256, 0, stream>>>(wscratch, (int)lanes, outs, dwgk);
+      LY_CUDA(launch(rf_wgrad_finalize_kernel, ceil_div(outs * 32, 256), 256, 0, stream, wscratch, (int)lanes, outs, dwgk));
       LY_LAUNCH_CHECK();
     }
   }
@@ -687,11 +697,11 @@ extern "C" int ly_rf_attention_noalloc(const void* G, int N, int ho, int wo, int
   if (rc != LY_OK) return rc;
   const int V = C / 8, KK = k * k;
   const long M = (long)N * ho * wo;
-  rf_poolc_kernel<<<ceil_div(M * KK * 32, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)G, M, KK, k, V, ho,
-                                                                          wo, maps, amax);
+  LY_CUDA(launch(rf_poolc_kernel, ceil_div(M * KK * 32, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)G, M, KK, k, V, ho,
+                                                                          wo, maps, amax));
   LY_LAUNCH_CHECK();
   const long total = (long)N * ho * k * wo * k;
-  rf_att_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(maps, N, ho * k, wo * k, wa, att);
+  LY_CUDA(launch(rf_att_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, maps, N, ho * k, wo * k, wa, att));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

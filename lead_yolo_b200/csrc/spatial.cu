@@ -19,6 +19,7 @@ __global__ void __launch_bounds__(128) stem_kernel(const Tin* __restrict__ img, 
                                                    const float* __restrict__ wk /*[48][COUT]*/,
                                                    const float* __restrict__ scale, const float* __restrict__ shift,
                                                    float in_scale, __nv_bfloat16* __restrict__ out, long ld_out) {
+  pdl_enter();
   __shared__ float sw[48 * COUT];
   for (int i = threadIdx.x; i < 48 * COUT; i += blockDim.x) sw[i] = wk[i] * in_scale;
   __syncthreads();
@@ -79,6 +80,7 @@ template <int COUT, typename Tin>
 __global__ void __launch_bounds__(192) stem_wgrad_kernel(const Tin* __restrict__ img, int N, int H, int W,
                                                          const __nv_bfloat16* __restrict__ dz, long ld_dz,
                                                          float in_scale, float* __restrict__ dwk /*[48][COUT]*/) {
+  pdl_enter();
   constexpr int P = 64;
   constexpr int CG = COUT / 4;
   __shared__ float sx[P][49];
@@ -137,6 +139,7 @@ __global__ void __launch_bounds__(192) stem_wgrad_kernel(const Tin* __restrict__
 __global__ void __launch_bounds__(256) maxpool5_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int N, int H,
                                                        int W, int V, __nv_bfloat16* __restrict__ y, long ldy,
                                                        uint8_t* __restrict__ idx) {
+  pdl_enter();
   const long total = (long)N * H * W * V;
   const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= total) return;
@@ -190,6 +193,7 @@ __device__ __forceinline__ uint4 max8(const uint4& a, const uint4& b) {
 
 __global__ void __launch_bounds__(256) sppf_pool3_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int H, int W,
                                                          int V, __nv_bfloat16* __restrict__ y, long ldy, long ystep) {
+  pdl_enter();
   extern __shared__ uint4 sp[];                 // [4][H*W]: input, row-max 5, 9, 13
   const int HW = H * W;
   uint4* sIn = sp;
@@ -243,6 +247,7 @@ __global__ void __launch_bounds__(256) maxpool5_bwd_kernel(const __nv_bfloat16* 
                                                            const uint8_t* __restrict__ idx, int N, int H, int W,
                                                            int V, __nv_bfloat16* __restrict__ dx, long lddx,
                                                            int accumulate) {
+  pdl_enter();
   const long total = (long)N * H * W * V;
   const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= total) return;
@@ -285,6 +290,7 @@ __global__ void __launch_bounds__(256) maxpool5_bwd_kernel(const __nv_bfloat16* 
 __global__ void __launch_bounds__(256) copy_up_kernel(const __nv_bfloat16* __restrict__ src, long lds, int N, int Hs,
                                                       int Ws, int V, int up, __nv_bfloat16* __restrict__ dst,
                                                       long ldd) {
+  pdl_enter();
   const int H = Hs * up, W = Ws * up;
   const long total = (long)N * H * W * V;
   const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -299,6 +305,7 @@ __global__ void __launch_bounds__(256) copy_up_kernel(const __nv_bfloat16* __res
 // up == 2: one thread per SOURCE vector, two of them in flight: one load feeds four stores
 __global__ void __launch_bounds__(256) copy_up2_kernel(const __nv_bfloat16* __restrict__ src, long lds, int N, int Hs,
                                                        int Ws, int V, __nv_bfloat16* __restrict__ dst, long ldd) {
+  pdl_enter();
   const long total = (long)N * Hs * Ws * V;
   const long t0 = ((long)blockIdx.x * blockDim.x + threadIdx.x);
   const long stride = (long)gridDim.x * blockDim.x;
@@ -330,6 +337,7 @@ __global__ void __launch_bounds__(256) copy_up2_kernel(const __nv_bfloat16* __re
 // Backward of the 2x nearest upsample: dst[n,h,w] = Σ_{a,b<2} src[n,2h+a,2w+b]
 __global__ void __launch_bounds__(256) downsum2_kernel(const __nv_bfloat16* __restrict__ src, long lds, int N, int H,
                                                        int W, int V, __nv_bfloat16* __restrict__ dst, long ldd) {
+  pdl_enter();
   const long total = (long)N * H * W * V;
   const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= total) return;
@@ -357,6 +365,7 @@ __global__ void __launch_bounds__(256) downsum2_kernel(const __nv_bfloat16* __re
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(512) gap_kernel(const __nv_bfloat16* __restrict__ x, long ldx, int HW, int V,
                                                   __nv_bfloat16* __restrict__ out, long ldo) {
+  pdl_enter();
   __shared__ float red[16][32][9];
   const int vl = threadIdx.x & 31, pl = threadIdx.x >> 5;
   const int v = blockIdx.x * 32 + vl;
@@ -404,7 +413,7 @@ static int stem_dispatch(const Tin* img, int N, int H, int W, int Cout, const fl
   const int grid = ceil_div(total, 128);
 #define LY_STEM(CO)                                                                                          \
   case CO:                                                                                                   \
-    stem_kernel<CO, Tin><<<grid, 128, 0, st>>>(img, N, H, W, wk, scale, shift, in_scale, out, ld_out);       \
+    LY_CUDA(launch(stem_kernel<CO, Tin>, grid, 128, 0, st, img, N, H, W, wk, scale, shift, in_scale, out, ld_out));       \
     break;
   switch (Cout) {
     LY_STEM(8) LY_STEM(16) LY_STEM(24) LY_STEM(32) LY_STEM(40) LY_STEM(48) LY_STEM(64)
@@ -421,7 +430,7 @@ static int stem_wgrad_dispatch(const Tin* img, int N, int H, int W, int Cout, co
   const int grid = device_sm_count() * 4;
 #define LY_STEMW(CO)                                                                               \
   case CO:                                                                                         \
-    stem_wgrad_kernel<CO, Tin><<<grid, 192, 0, st>>>(img, N, H, W, dz, ld_dz, in_scale, dwk);      \
+    LY_CUDA(launch(stem_wgrad_kernel<CO, Tin>, grid, 192, 0, st, img, N, H, W, dz, ld_dz, in_scale, dwk));      \
     break;
   switch (Cout) {
     LY_STEMW(8) LY_STEMW(16) LY_STEMW(24) LY_STEMW(32) LY_STEMW(40) LY_STEMW(48) LY_STEMW(64)
@@ -479,8 +488,8 @@ extern "C" int ly_maxpool5_fwd(const void* x, long ldx, int N, int H, int W, int
   if (rc) return rc;
   const int V = C / 8;
   const long total = (long)N * H * W * V;
-  maxpool5_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)x, ldx, N, H, W, V,
-                                                                      (__nv_bfloat16*)y, ldy, idx);
+  LY_CUDA(launch(maxpool5_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)x, ldx, N, H, W, V,
+                                                                      (__nv_bfloat16*)y, ldy, idx));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -503,8 +512,8 @@ extern "C" int ly_sppf_pool3(const void* x, long ldx, int N, int H, int W, int C
     LY_CUDA(cudaFuncSetAttribute(sppf_pool3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 1600 * 16));
     attr_done[dev & 63].store(true);
   }
-  sppf_pool3_kernel<<<(unsigned)(N * (C / 8)), 256, smem, (cudaStream_t)st>>>((const __nv_bfloat16*)x, ldx, H, W, C / 8,
-                                                                             (__nv_bfloat16*)y, ldy, ystep);
+  LY_CUDA(launch(sppf_pool3_kernel, (unsigned)(N * (C / 8)), 256, smem, (cudaStream_t)st, (const __nv_bfloat16*)x, ldx, H, W, C / 8,
+                                                                             (__nv_bfloat16*)y, ldy, ystep));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -518,8 +527,8 @@ extern "C" int ly_maxpool5_bwd(const void* dy, long lddy, const uint8_t* idx, in
   LY_REQUIRE(idx != nullptr, "ly_maxpool5_bwd: null idx");
   const int V = C / 8;
   const long total = (long)N * H * W * V;
-  maxpool5_bwd_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(
-      (const __nv_bfloat16*)dy, lddy, idx, N, H, W, V, (__nv_bfloat16*)dx, lddx, accumulate);
+  LY_CUDA(launch(maxpool5_bwd_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, 
+      (const __nv_bfloat16*)dy, lddy, idx, N, H, W, V, (__nv_bfloat16*)dx, lddx, accumulate));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -535,13 +544,13 @@ extern "C" int ly_copy_upsample(const void* src, long lds, int N, int Hs, int Ws
   const long total = (long)N * Hs * up * Ws * up * V;
   if (up == 2) {
     const long src_total = (long)N * Hs * Ws * V;
-    copy_up2_kernel<<<ceil_div(src_total, 512), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)src, lds, N, Hs, Ws, V,
-                                                                           (__nv_bfloat16*)dst, ldd);
+    LY_CUDA(launch(copy_up2_kernel, ceil_div(src_total, 512), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)src, lds, N, Hs, Ws, V,
+                                                                           (__nv_bfloat16*)dst, ldd));
     LY_LAUNCH_CHECK();
     return LY_OK;
   }
-  copy_up_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)src, lds, N, Hs, Ws, V,
-                                                                     up, (__nv_bfloat16*)dst, ldd);
+  LY_CUDA(launch(copy_up_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)src, lds, N, Hs, Ws, V,
+                                                                     up, (__nv_bfloat16*)dst, ldd));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -554,8 +563,8 @@ extern "C" int ly_downsum2(const void* src, long lds, int N, int H, int W, int C
   if (rc) return rc;
   const int V = C / 8;
   const long total = (long)N * H * W * V;
-  downsum2_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)src, lds, N, H, W, V,
-                                                                      (__nv_bfloat16*)dst, ldd);
+  LY_CUDA(launch(downsum2_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)src, lds, N, H, W, V,
+                                                                      (__nv_bfloat16*)dst, ldd));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -567,7 +576,7 @@ extern "C" int ly_gap(const void* x, long ldx, int N, int HW, int C, void* out, 
   if (rc) return rc;
   const int V = C / 8;
   dim3 grid(ceil_div(V, 32), N);
-  gap_kernel<<<grid, 512, 0, (cudaStream_t)st>>>((const __nv_bfloat16*)x, ldx, HW, V, (__nv_bfloat16*)out, ldo);
+  LY_CUDA(launch(gap_kernel, grid, 512, 0, (cudaStream_t)st, (const __nv_bfloat16*)x, ldx, HW, V, (__nv_bfloat16*)out, ldo));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

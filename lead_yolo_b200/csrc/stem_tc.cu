@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(kStThreads, 2) stem_tc_kernel(const __grid_con
 
   // zero A once (the K padding chunks 6,7 are never written again) and build the weight tile
   for (int i = threadIdx.x; i < 4 * kStTile / 16; i += kStThreads) reinterpret_cast<uint4*>(sA)[i] = make_uint4(0, 0, 0, 0);
+  pdl_wait();
   for (int i = threadIdx.x; i < p.Npad * 64; i += kStThreads) {
     const int n = i >> 6, k = i & 63;
     float w = 0.f;
@@ -81,6 +82,7 @@ __global__ void __launch_bounds__(kStThreads, 2) stem_tc_kernel(const __grid_con
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_trigger();
   const uint32_t tmem = tmem_base_s;
 
   const int mine = ((int)blockIdx.x < p.stages) ? (p.stages - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
@@ -254,7 +256,7 @@ int stem_tc_u8(const uint8_t* img, int N, int H, int W, int Cout, const float* w
     attr_done[dev & 63].store(true);
   }
   const long cap = 2L * device_sm_count();
-  stem_tc_kernel<<<(unsigned)(stages < cap ? stages : cap), kStThreads, smem, st>>>(p);
+  LY_CUDA(launch(stem_tc_kernel, (unsigned)(stages < cap ? stages : cap), kStThreads, smem, st, p));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

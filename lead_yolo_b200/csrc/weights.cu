@@ -35,6 +35,7 @@ __device__ __forceinline__ int packed_col(const SrcSplit& sp, int kh, int kw, in
 // forward pack: wp[o][Kp] bf16 <- w[o][ci][ky][kx]; one thread per packed element (zero padding included)
 __global__ void pack_fwd_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw, int patch, SrcSplit sp,
                                 int Kp, __nv_bfloat16* __restrict__ wp) {
+  pdl_enter();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long)Cout * Kp) return;
   const int o = (int)(i / Kp);
@@ -65,6 +66,7 @@ __global__ void pack_fwd_kernel(const float* __restrict__ w, int Cout, int Cin, 
 //   patch conv   : rows (ky, kx, c) (kh*kw*cs), K = pad64(cpad):  wd[(ky*kw+kx)*cs + c][co] = w[co][coff+c][ky][kx]
 __global__ void pack_dgrad_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw, int patch, int coff,
                                   int cs, int P, __nv_bfloat16* __restrict__ wd) {
+  pdl_enter();
   const int rows = patch ? kh * kw * cs : cs;
   const int Kp = patch ? P : kh * kw * P;
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -90,6 +92,7 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ w, int Cout, int Cin
 // weight gradient back to OIHW: dw[o][ci][ky][kx] (+)= dwp[o][packed_col]
 __global__ void unpack_wgrad_kernel(const float* __restrict__ dwp, int Cout, int Cin, int kh, int kw, int patch,
                                     SrcSplit sp, int Kp, float* __restrict__ dw, int accumulate) {
+  pdl_enter();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long)Cout * Cin * kh * kw) return;
   const int kx = (int)(i % kw);
@@ -135,8 +138,8 @@ extern "C" int ly_pack_weight(const float* w, int Cout, int kh, int kw, int patc
   LY_REQUIRE(split_of(c0, c1, c2, c3, &sp, &cin) == 0, "ly_pack_weight: bad source split (%d,%d,%d,%d)", c0, c1, c2, c3);
   const int Kp = packed_k_of(sp, kh, kw, patch);
   const long total = (long)Cout * Kp;
-  pack_fwd_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(w, Cout, cin, kh, kw, patch, sp, Kp,
-                                                                       (__nv_bfloat16*)wp);
+  LY_CUDA(launch(pack_fwd_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, w, Cout, cin, kh, kw, patch, sp, Kp,
+                                                                       (__nv_bfloat16*)wp));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -147,8 +150,8 @@ extern "C" int ly_pack_weight_dgrad(const float* w, int Cout, int Cin, int kh, i
              "ly_pack_weight_dgrad: bad arguments");
   const int P = pad64((Cout + 7) / 8 * 8);
   const long total = patch ? (long)kh * kw * cs * P : (long)cs * kh * kw * P;
-  pack_dgrad_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(w, Cout, Cin, kh, kw, patch, coff, cs, P,
-                                                                         (__nv_bfloat16*)wd);
+  LY_CUDA(launch(pack_dgrad_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, w, Cout, Cin, kh, kw, patch, coff, cs, P,
+                                                                         (__nv_bfloat16*)wd));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -162,8 +165,8 @@ extern "C" int ly_unpack_wgrad(const float* dwp, int Cout, int kh, int kw, int p
              c3);
   const int Kp = packed_k_of(sp, kh, kw, patch);
   const long total = (long)Cout * cin * kh * kw;
-  unpack_wgrad_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)st>>>(dwp, Cout, cin, kh, kw, patch, sp, Kp, dw,
-                                                                           accumulate);
+  LY_CUDA(launch(unpack_wgrad_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, dwp, Cout, cin, kh, kw, patch, sp, Kp, dw,
+                                                                           accumulate));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

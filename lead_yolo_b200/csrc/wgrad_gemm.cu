@@ -75,6 +75,8 @@ __global__ void __launch_bounds__(192) wgrad_gemm_kernel(const __grid_constant__
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_trigger();
+  pdl_wait();
   const uint32_t tmem_base = tmem_base_s;
   const uint32_t box_bytes = (uint32_t)p.P * 128u;
 
@@ -285,7 +287,7 @@ extern "C" int ly_conv_wgrad(const ly_conv_desc* d, const void* dz, long dz_ld, 
     done[dev & 63].store(true);
   }
   dim3 grid((unsigned)split, (unsigned)cts, (unsigned)kgs);
-  wgrad_gemm_kernel<<<grid, 192, smem_bytes, (cudaStream_t)stream>>>(p);
+  LY_CUDA(launch(wgrad_gemm_kernel, grid, 192, smem_bytes, (cudaStream_t)stream, p));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

@@ -135,6 +135,7 @@ __device__ __forceinline__ float block_sum(float v, float* sm) {
 // ---- K1: target assignment (build_targets, loss.py:195-268) ----------------------------------------------------
 __global__ void loss_assign_kernel(LossGeom g, const float* __restrict__ targets, const float* __restrict__ anchors,
                                    int* __restrict__ winner, float* __restrict__ rec, int* __restrict__ counts) {
+  pdl_enter();
   const long per = 5L * g.na * g.nt;
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= per * g.nl) return;
@@ -204,6 +205,7 @@ __device__ __forceinline__ EntryEval eval_entry(const LossGeom& g, int lvl, int 
 // acc: [nl][4] = Σ(1 - eiou) | Σ softplus(x_obj) over all cells | Σ objectness correction | Σ class BCE
 __global__ void __launch_bounds__(256) loss_entry_fwd_kernel(LossGeom g, const int* __restrict__ winner,
                                                              const float* __restrict__ rec, float* __restrict__ acc) {
+  pdl_enter();
   __shared__ float sm[8];
   const long per = 5L * g.na * g.nt;
   const int lvl = blockIdx.y;
@@ -237,6 +239,7 @@ __global__ void __launch_bounds__(256) loss_entry_fwd_kernel(LossGeom g, const i
 
 // ---- K3: dense objectness, target 0 on every cell ---------------------------------------------------------------
 __global__ void __launch_bounds__(256) loss_dense_fwd_kernel(LossGeom g, float* __restrict__ acc) {
+  pdl_enter();
   __shared__ float sm[8];
   const int lvl = blockIdx.y;
   const int nx = g.nx[lvl], ny = g.ny[lvl];
@@ -255,6 +258,7 @@ __global__ void __launch_bounds__(256) loss_dense_fwd_kernel(LossGeom g, float* 
 // ---- K4: (lbox + lobj + lcls) * bs and the three weighted terms (loss.py:183-191) ------------------------------
 __global__ void loss_finalize_kernel(LossGeom g, const float* __restrict__ acc, const int* __restrict__ counts,
                                      float* __restrict__ out) {
+  pdl_enter();
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   float lbox = 0.f, lobj = 0.f, lcls = 0.f;
   for (int l = 0; l < g.nl; ++l) {
@@ -277,6 +281,7 @@ __global__ void loss_finalize_kernel(LossGeom g, const float* __restrict__ acc, 
 
 // ---- B1: dense gradient: zero everywhere except the objectness logit ----------------------------------------------
 __global__ void __launch_bounds__(256) loss_dense_bwd_kernel(LossGeom g, const float* __restrict__ gscale) {
+  pdl_enter();
   const int lvl = blockIdx.y;
   const int nx = g.nx[lvl], ny = g.ny[lvl];
   const long cells = (long)g.bs * g.na * ny * nx;
@@ -297,6 +302,7 @@ __global__ void __launch_bounds__(256) loss_entry_bwd_kernel(LossGeom g, const i
                                                              const float* __restrict__ rec,
                                                              const int* __restrict__ counts,
                                                              const float* __restrict__ gscale) {
+  pdl_enter();
   const long per = 5L * g.na * g.nt;
   const int lvl = blockIdx.y;
   const float n = (float)counts[lvl];
@@ -390,15 +396,15 @@ extern "C" int ly_yolo_loss_fwd(const ly_loss_desc* d, void* workspace, float* o
   LY_CUDA(cudaMemsetAsync(winner, 0xFF, cells * 4, s));
   LY_CUDA(cudaMemsetAsync(counts, 0, 16 + kMaxLevels * 16, s));
   const long per = 5L * g.na * g.nt;
-  loss_assign_kernel<<<ceil_div(per * g.nl, 256), 256, 0, s>>>(g, d->targets, d->anchors, winner, rec, counts);
+  LY_CUDA(launch(loss_assign_kernel, ceil_div(per * g.nl, 256), 256, 0, s, g, d->targets, d->anchors, winner, rec, counts));
   LY_LAUNCH_CHECK();
   dim3 ge((unsigned)min(ceil_div(per, 256), 64), (unsigned)g.nl);
-  loss_entry_fwd_kernel<<<ge, 256, 0, s>>>(g, winner, rec, acc);
+  LY_CUDA(launch(loss_entry_fwd_kernel, ge, 256, 0, s, g, winner, rec, acc));
   LY_LAUNCH_CHECK();
   dim3 gd((unsigned)(device_sm_count() * 2), (unsigned)g.nl);
-  loss_dense_fwd_kernel<<<gd, 256, 0, s>>>(g, acc);
+  LY_CUDA(launch(loss_dense_fwd_kernel, gd, 256, 0, s, g, acc));
   LY_LAUNCH_CHECK();
-  loss_finalize_kernel<<<1, 32, 0, s>>>(g, acc, counts, out);
+  LY_CUDA(launch(loss_finalize_kernel, 1, 32, 0, s, g, acc, counts, out));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -415,11 +421,11 @@ extern "C" int ly_yolo_loss_bwd(const ly_loss_desc* d, const void* workspace, co
   ws_split(g, const_cast<void*>(workspace), &winner, &rec, &counts, &acc, &cells);
   cudaStream_t s = (cudaStream_t)st;
   dim3 gd((unsigned)(device_sm_count() * 4), (unsigned)g.nl);
-  loss_dense_bwd_kernel<<<gd, 256, 0, s>>>(g, grad_scale);
+  LY_CUDA(launch(loss_dense_bwd_kernel, gd, 256, 0, s, g, grad_scale));
   LY_LAUNCH_CHECK();
   const long per = 5L * g.na * g.nt;
   dim3 ge((unsigned)min(ceil_div(per, 256), 64), (unsigned)g.nl);
-  loss_entry_bwd_kernel<<<ge, 256, 0, s>>>(g, winner, rec, counts, grad_scale);
+  LY_CUDA(launch(loss_entry_bwd_kernel, ge, 256, 0, s, g, winner, rec, counts, grad_scale));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
