@@ -611,6 +611,241 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   if (warp == 2) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// 3x3 convolutions whose weights do not fit in one SM's shared memory (128 -> 128): CTA PAIRS, cta_group::2.
+// With one box per tap these layers move 590 KB from L2 per 128-pixel tile through a two-stage ring and the issuing
+// lane waits on the ring most of the time (tensor pipe 40 % active, ncu).  Here two CTAs of a cluster (one TPC) share
+// one accumulation M = 256 x N = Cout: each CTA keeps HALF of the weight matrix resident (Cout/2 rows x 9·Cin, 147 KB
+// for 128 -> 128) and feeds its own 128 pixels from one halo box per 64-channel chunk (row-shifted descriptors, as in the
+// resident-weight mode above), so a tile costs 2 barrier waits, 72 MMAs and 3 commits on ONE lane for both SMs and no
+// weight traffic at all.
+//   both CTAs   warp 0: TMA lane (own halo boxes; completes on the LEADER's barrier), warps 2..17: epilogue of own rows
+//   leader      warp 1: MMA lane, tcgen05.mma.cta_group::2; commits are multicast to both CTAs' barriers
+// Every load here reads this GPU's memory; none is a multicast load.
+constexpr int kC2Threads = 64 + kEpiGroups * 128;
+constexpr int kC2MaxCout = 256;
+constexpr int kC2Slots = 4;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2cta(uint32_t* dst_smem, uint32_t ncols) {   // same warp id in both CTAs
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2cta(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2cta(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this offset in BOTH CTAs once the MMAs issued so far have completed
+__device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3)
+               : "memory");
+}
+// TMA loads into this CTA's shared memory whose bytes complete on the barrier at the same offset in the LEADER
+// (bit 24 of a shared::cluster address is the CTA's rank inside the pair)
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+__device__ __forceinline__ void tma_load_2d_2cta(void* smem, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_5d_2cta(void* smem, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                                 int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, "
+      "%6, %7}], [%2];"
+      ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1),
+      "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta) {   // barrier at this offset in CTA `cta`
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(smem_u32(bar)), "r"(cta)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {   // arrivals may come from the peer CTA
+  const long long t0 = clock64();
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (ok) return;
+    if (clock64() - t0 > 4000000000LL) __trap();
+  }
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
+    conv_cta2_kernel(const __grid_constant__ ConvGemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t a_full[kC2Slots], a_empty[kC2Slots], b_ready_bar;
+  __shared__ uint64_t tmem_full_bar[4], tmem_empty_bar[4];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float s_scale[kC2MaxCout];
+  __shared__ __align__(16) float s_shift[kC2MaxCout];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sA = smem;                                  // `stages` halo boxes
+  uint8_t* sB = smem + p.stages * p.a_stage;           // num_kb x [BN/2][64] weight tiles: this CTA's half of the rows
+  const int b_half = (p.BN >> 1) * 128;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.b_map);
+    tma_prefetch_desc(&p.a_map[0]);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+    mbar_init(&b_ready_bar, 1);
+    for (int b = 0; b < 4; ++b) { mbar_init(&tmem_full_bar[b], 1); mbar_init(&tmem_empty_bar[b], 8); }   // 4 warps x 2 CTAs
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc_2cta(&tmem_base_s, (uint32_t)p.tmem_cols);
+  pdl_wait();
+  const int cpad = (p.Cout + 7) & ~7;
+  for (int i = threadIdx.x; i < cpad; i += blockDim.x) {
+    const float half = p.act == LY_ACT_SILU ? 0.5f : 1.f;   // see ssa<>
+    s_scale[i] = half * ((p.scale != nullptr && i < p.Cout) ? p.scale[i] : 1.f);
+    s_shift[i] = half * ((p.shift != nullptr && i < p.Cout) ? p.shift[i] : 0.f);
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();   // the peer's barriers exist before anything is sent to them
+  tc_fence_after_sync();
+  pdl_trigger();
+  const uint32_t tmem_base = tmem_base_s;
+
+  const int tiles_img = p.tiles_w * p.tiles_h;
+  const int tiles_m = tiles_img * p.n_img;
+  const int units = (tiles_m + 1) >> 1;                 // unit u = tiles 2u (leader) and 2u + 1 (peer)
+  const int cid = (int)blockIdx.x >> 1, ncl = (int)gridDim.x >> 1;
+  const int mine = cid < units ? (units - cid + ncl - 1) / ncl : 0;
+
+  if (warp == 0) {
+    // ---------------- TMA producer (both CTAs) ----------------
+    if (lane == 0 && mine > 0) {
+      if (rank == 0) mbar_arrive_expect_tx(&b_ready_bar, (uint32_t)(2 * p.num_kb * b_half));
+      for (int k = 0; k < p.num_kb; ++k)
+        tma_load_2d_2cta(sB + k * b_half, &p.b_map, &b_ready_bar, k * 64, (int)rank * (p.BN >> 1));
+      int s = 0;
+      uint32_t ph = 1;
+      int u = cid;
+      for (int i = 0; i < mine; ++i, u += ncl) {
+        const int m = 2 * u + (int)rank;
+        int n = p.n_img, h0 = 0, w0 = 0;                // a unit's missing second tile: out of bounds = zero fill
+        if (m < tiles_m) {
+          n = m / tiles_img;
+          const int tr = m - n * tiles_img, th = tr / p.tiles_w;
+          h0 = th * p.Ht;
+          w0 = (tr - th * p.tiles_w) * p.Wt;
+        }
+        for (int k = 0; k < p.num_k; ++k) {
+          const KEntry e = p.sched[k];
+          mbar_wait(&a_empty[s], ph);
+          if (rank == 0) mbar_arrive_expect_tx(&a_full[s], 2u * p.a_bytes);
+          tma_load_5d_2cta(sA + s * p.a_stage, &p.a_map[e.src], &a_full[s], e.c0, w0 - 1, 0, h0 - 1, n);
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer (leader only) ----------------
+    if (lane == 0 && rank == 0 && mine > 0) {
+      const uint32_t idesc = umma_idesc_bf16_f32(256, p.BN, 0, 0);
+      const uint64_t a_desc0 = umma_smem_desc_sw128(smem_u32(sA), 16, 1024);
+      const uint64_t b_desc0 = umma_smem_desc_sw128(smem_u32(sB), 16, 1024);
+      const uint32_t a_step = (uint32_t)(p.a_stage >> 4), b_step = (uint32_t)(b_half >> 4);
+      mbar_wait_cluster(&b_ready_bar, 0);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int i = 0; i < mine; ++i) {
+        const int buf = i & 3;
+        mbar_wait_cluster(&tmem_empty_bar[buf], (((uint32_t)i >> 2) & 1u) ^ 1u);
+        tc_fence_after_sync();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * p.BN);
+        for (int k = 0; k < p.num_k; ++k) {
+          const KEntry e = p.sched[k];
+          mbar_wait_cluster(&a_full[s], ph);
+          tc_fence_after_sync();
+          const uint64_t ahalo = a_desc0 + (uint64_t)((uint32_t)s * a_step);
+          for (int t = 0; t < 9; ++t) {
+            const int ty = t / 3, tx = t - ty * 3;
+            const uint64_t adesc = ahalo + (uint64_t)((uint32_t)(ty * p.halo + tx) * 8u);   // 128-byte rows
+            const uint64_t bdesc = b_desc0 + (uint64_t)((uint32_t)(e.kb + t * e.kstep) * b_step);
+            umma_bf16_2cta(tmem_d, adesc, bdesc, idesc, (uint32_t)((k | t) != 0));
+            if (e.nk16 > 1) umma_bf16_2cta(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
+            if (e.nk16 > 2) umma_bf16_2cta(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+            if (e.nk16 > 3) umma_bf16_2cta(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+          }
+          umma_commit_2cta(&a_empty[s]);
+          if (++s == p.stages) { s = 0; ph ^= 1u; }
+        }
+        umma_commit_2cta(&tmem_full_bar[buf]);
+      }
+    }
+  } else {
+    // ---------------- epilogue (both CTAs, own 128 rows) ----------------
+    const int q = warp & 3;
+    const int grp = (warp - 2) >> 2;       // = TMEM buffer
+    const int r = q * 32 + lane;
+    const int hh = r / p.halo, ww = r - hh * p.halo;
+    for (int i = grp; i < mine; i += 4) {
+      const int m = 2 * (cid + i * ncl) + (int)rank;
+      const int n = m / tiles_img, tr = m - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+      const int h = th * p.Ht + hh, w = tw * p.Wt + ww;
+      const bool valid = (m < tiles_m) && (ww < p.Wt) && (hh < p.Ht) && (h < p.Hout) && (w < p.Wout);
+      const long pix = ((long)n * p.Hout + h) * p.Wout + w;
+      mbar_wait(&tmem_full_bar[grp], ((uint32_t)i >> 2) & 1u);
+      tc_fence_after_sync();
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * p.BN);
+      switch (p.act) {
+        case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
+        case LY_ACT_SILU: epilogue_cols<LY_ACT_SILU>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
+        case LY_ACT_HSWISH: epilogue_cols<LY_ACT_HSWISH>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
+        case LY_ACT_SIGMOID: epilogue_cols<LY_ACT_SIGMOID>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
+        default: epilogue_cols<LY_ACT_NONE>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[grp], 0u);   // the leader's lane waits for both CTAs
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();   // no CTA of the pair leaves while the other may still signal it or read its shared memory
+  if (warp == 2) tmem_dealloc_2cta(tmem_base, (uint32_t)p.tmem_cols);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Host side
 // ---------------------------------------------------------------------------------------------
@@ -763,6 +998,8 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   // (row-shifted descriptors), which cuts the L2 -> SM activation traffic ~6x.  The tile keeps the halo's pitch.
   p.a_stage = kAStage;
   p.num_kb = num_k;
+  bool cta2 = false;
+  constexpr long kC2Budget = 224 * 1024 - 1024;   // dynamic shared memory of conv_cta2_kernel after alignment
   {
     static const int no_halo = getenv("LY_CONV_NO_HALO") ? 1 : 0;   // dev knob
     const int cr = (d->Cout + 15) / 16 * 16;
@@ -777,6 +1014,27 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
       p.Wt = p.halo - 2;
       p.Ht = 128 / p.halo;
       p.a_stage = ((130 + 2 * p.halo) * 128 + 1023) / 1024 * 1024;   // box rows + what a shifted 128-row read runs past
+    }
+    // weights too large for one SM but half of them fit: CTA pairs (conv_cta2_kernel), each CTA keeps Cout/2 rows
+    static const int no_cta2 = getenv("LY_CONV_NO_CTA2") ? 1 : 0;   // dev knob
+    const long b_half_all = (long)num_k * (cr / 2) * 128;
+    if (!p.halo && !no_cta2 && g.taps == 9 && !g.patch && det == nullptr && d->patch_k == 0 && cr >= 32 && cr <= 128 &&
+        d->Cout <= kC2MaxCout) {
+      double best = -1;
+      const int pitches[3] = {16, 32, 64};
+      for (int i = 0; i < 3; ++i) {
+        const int wt = pitches[i] - 2, ht = 128 / pitches[i];
+        const long a_st = ((130 + 2 * pitches[i]) * 128 + 1023) / 1024 * 1024;
+        if (b_half_all + 2 * a_st > kC2Budget) continue;
+        const double eff = (double)p.Hout * p.Wout / ((double)ceil_div(p.Wout, wt) * ceil_div(p.Hout, ht) * 128.0);
+        if (eff > best + 1e-9) { best = eff; p.halo = pitches[i]; }
+      }
+      if (p.halo) {
+        p.Wt = p.halo - 2;
+        p.Ht = 128 / p.halo;
+        p.a_stage = ((130 + 2 * p.halo) * 128 + 1023) / 1024 * 1024;
+        cta2 = true;
+      }
     }
   }
   p.tiles_w = ceil_div(p.Wout, p.Wt);
@@ -858,7 +1116,7 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   {
     uint64_t dims[2] = {(uint64_t)num_k * 64, (uint64_t)d->Cout};
     uint64_t str[1] = {(uint64_t)num_k * 64 * 2};
-    uint32_t box[2] = {64, (uint32_t)p.BN};
+    uint32_t box[2] = {64, (uint32_t)(cta2 ? p.BN / 2 : p.BN)};   // CTA pairs: each CTA loads its half of the rows
     rc = tmap_encode_bf16(&p.b_map, d->w_packed, 2, dims, str, box);
     if (rc != LY_OK) return rc;
   }
@@ -896,6 +1154,38 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
   p.b_resident = (ny == 1 && b_all <= 100 * 1024) ? 1 : 0;
   // K chunks per ring stage: the largest divisor of num_k (<= 4) that still leaves a ring of >= 3 stages (>= 2 when
   // one chunk alone is big).  Fewer, larger stages amortise the commit / mbarrier round trips of the single-lane roles.
+  if (cta2) {
+    const long b_half_all = (long)num_k * (p.BN / 2) * 128;
+    p.b_resident = 1;
+    p.tma_store = 0;
+    p.slab_bytes = 0;
+    p.stages = (int)((kC2Budget - b_half_all) / p.a_stage);
+    if (p.stages > kC2Slots) p.stages = kC2Slots;
+    LY_REQUIRE(p.stages >= 2 && p.nbuf == 4 && ny == 1, "CTA-pair mode: bad configuration (BN=%d)", p.BN);
+    p.kgroup = 1;
+    p.issuers = 1;
+    p.act = d->act; p.scale = d->scale; p.shift = d->shift;
+    p.residual = reinterpret_cast<const __nv_bfloat16*>(d->residual);
+    p.res_ld = d->res_ld; p.out = d->out; p.out_ld = d->out_ld; p.out_fp32 = d->out_fp32;
+    const long tiles_c = (long)p.tiles_w * p.tiles_h * p.n_img;
+    static const bool verbose_c = getenv("LY_CONV_VERBOSE") != nullptr;
+    if (verbose_c)
+      fprintf(stderr, "[conv cta2] BN=%d chunks=%d weight chunks=%d slots=%d halo=%d a_stage=%d tiles=%ld\n", p.BN, p.num_k,
+              p.num_kb, p.stages, p.halo, p.a_stage, tiles_c);
+    static std::atomic<bool> c2_attr[64];
+    int dev = 0;
+    LY_CUDA(cudaGetDevice(&dev));
+    if (!c2_attr[dev & 63].load()) {
+      LY_CUDA(cudaFuncSetAttribute(conv_cta2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+      c2_attr[dev & 63].store(true);
+    }
+    const size_t smem_c = (size_t)p.stages * p.a_stage + (size_t)b_half_all + 1024;
+    const long units = (tiles_c + 1) / 2;
+    const long ncl = units < device_sm_count() / 2 ? units : device_sm_count() / 2;
+    conv_cta2_kernel<<<dim3((unsigned)(2 * ncl)), dim3(kC2Threads), smem_c, (cudaStream_t)stream>>>(p);   // cluster (2,1,1)
+    LY_LAUNCH_CHECK();
+    return LY_OK;
+  }
   LY_REQUIRE(!p.halo || p.b_resident, "halo tiles need resident weights");
   const long chunk_bytes = p.a_stage + (p.b_resident ? 0 : p.BN * 128);
   const long ring_budget = budget - (p.b_resident ? b_all : 0);
