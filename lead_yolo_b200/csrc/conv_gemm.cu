@@ -613,19 +613,21 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
 
 
 // ---------------------------------------------------------------------------------------------
-// 3x3 convolutions whose weights do not fit in one SM's shared memory (128 -> 128): CTA PAIRS, cta_group::2.
+// 3x3 convolutions whose weights do not fit in one SM's shared memory but whose HALF does (128 -> 128, 64 -> 256 ...):
+// CTA PAIRS, cta_group::2.
 // With one box per tap these layers move 590 KB from L2 per 128-pixel tile through a two-stage ring and the issuing
 // lane waits on the ring most of the time (tensor pipe 40 % active, ncu).  Here two CTAs of a cluster (one TPC) share
 // one accumulation M = 256 x N = Cout: each CTA keeps HALF of the weight matrix resident (Cout/2 rows x 9·Cin, 147 KB
 // for 128 -> 128) and feeds its own 128 pixels from one halo box per 64-channel chunk (row-shifted descriptors, as in the
-// resident-weight mode above), so a tile costs 2 barrier waits, 72 MMAs and 3 commits on ONE lane for both SMs and no
-// weight traffic at all.
+// resident-weight mode above), so a tile pair costs 2 barrier waits, 72 MMAs and 3 commits on ONE lane for both SMs and
+// no weight traffic at all: 50 -> 38 us on the 40x40 layers.  (Measured and not kept: the same scheme for 1x1 layers
+// with N = 256 — 256 -> 256 at 40x40 runs 34 us either way; those are bound by the fill and drain of six tiles per SM.)
 //   both CTAs   warp 0: TMA lane (own halo boxes; completes on the LEADER's barrier), warps 2..17: epilogue of own rows
 //   leader      warp 1: MMA lane, tcgen05.mma.cta_group::2; commits are multicast to both CTAs' barriers
 // Every load here reads this GPU's memory; none is a multicast load.
 constexpr int kC2Threads = 64 + kEpiGroups * 128;
 constexpr int kC2MaxCout = 256;
-constexpr int kC2Slots = 4;
+constexpr int kC2Slots = 8;
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -726,7 +728,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
     mbar_init(&b_ready_bar, 1);
-    for (int b = 0; b < 4; ++b) { mbar_init(&tmem_full_bar[b], 1); mbar_init(&tmem_empty_bar[b], 8); }   // 4 warps x 2 CTAs
+    for (int b = 0; b < 4; ++b) {   // drained by (4 warps per group) x (groups per accumulator) x (2 CTAs)
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], 8 * (kEpiGroups / p.nbuf));
+    }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc_2cta(&tmem_base_s, (uint32_t)p.tmem_cols);
@@ -772,7 +777,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
           const KEntry e = p.sched[k];
           mbar_wait(&a_empty[s], ph);
           if (rank == 0) mbar_arrive_expect_tx(&a_full[s], 2u * p.a_bytes);
-          tma_load_5d_2cta(sA + s * p.a_stage, &p.a_map[e.src], &a_full[s], e.c0, w0 - 1, 0, h0 - 1, n);
+          tma_load_5d_2cta(sA + s * p.a_stage, &p.a_map[e.src], &a_full[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
       }
@@ -787,15 +792,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
       mbar_wait_cluster(&b_ready_bar, 0);
       int s = 0;
       uint32_t ph = 0;
+      int buf = 0;
+      uint32_t use_par = 1;   // parity to wait for on tmem_empty_bar[buf]
       for (int i = 0; i < mine; ++i) {
-        const int buf = i & 3;
-        mbar_wait_cluster(&tmem_empty_bar[buf], (((uint32_t)i >> 2) & 1u) ^ 1u);
+        mbar_wait_cluster(&tmem_empty_bar[buf], use_par);
         tc_fence_after_sync();
         const uint32_t tmem_d = tmem_base + (uint32_t)(buf * p.BN);
         for (int k = 0; k < p.num_k; ++k) {
-          const KEntry e = p.sched[k];
           mbar_wait_cluster(&a_full[s], ph);
           tc_fence_after_sync();
+          // nine taps from the one halo box of this chunk: tap (dy, dx) starts (dy+1)*P + (dx+1) rows further in
+          const KEntry e = p.sched[k];
           const uint64_t ahalo = a_desc0 + (uint64_t)((uint32_t)s * a_step);
           for (int t = 0; t < 9; ++t) {
             const int ty = t / 3, tx = t - ty * 3;
@@ -810,33 +817,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
           if (++s == p.stages) { s = 0; ph ^= 1u; }
         }
         umma_commit_2cta(&tmem_full_bar[buf]);
+        if (++buf == p.nbuf) { buf = 0; use_par ^= 1u; }
       }
     }
   } else {
     // ---------------- epilogue (both CTAs, own 128 rows) ----------------
     const int q = warp & 3;
-    const int grp = (warp - 2) >> 2;       // = TMEM buffer
+    const int grp = (warp - 2) >> 2;
+    const int slot = grp % p.nbuf;         // TMEM buffer this group drains; groups that share one split its columns
+    const int part = grp / p.nbuf, nparts = kEpiGroups / p.nbuf;
     const int r = q * 32 + lane;
     const int hh = r / p.halo, ww = r - hh * p.halo;
-    for (int i = grp; i < mine; i += 4) {
+    for (int i = slot; i < mine; i += p.nbuf) {
       const int m = 2 * (cid + i * ncl) + (int)rank;
       const int n = m / tiles_img, tr = m - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
       const int h = th * p.Ht + hh, w = tw * p.Wt + ww;
       const bool valid = (m < tiles_m) && (ww < p.Wt) && (hh < p.Ht) && (h < p.Hout) && (w < p.Wout);
       const long pix = ((long)n * p.Hout + h) * p.Wout + w;
-      mbar_wait(&tmem_full_bar[grp], ((uint32_t)i >> 2) & 1u);
+      mbar_wait(&tmem_full_bar[slot], (uint32_t)(i / p.nbuf) & 1u);
       tc_fence_after_sync();
-      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * p.BN);
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * p.BN);
+      const int cb = part * 16, cs = nparts * 16;
       switch (p.act) {
-        case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
-        case LY_ACT_SILU: epilogue_cols<LY_ACT_SILU>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
-        case LY_ACT_HSWISH: epilogue_cols<LY_ACT_HSWISH>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
-        case LY_ACT_SIGMOID: epilogue_cols<LY_ACT_SIGMOID>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
-        default: epilogue_cols<LY_ACT_NONE>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, 0, 16); break;
+        case LY_ACT_RELU: epilogue_cols<LY_ACT_RELU>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, cb, cs); break;
+        case LY_ACT_SILU: epilogue_cols<LY_ACT_SILU>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, cb, cs); break;
+        case LY_ACT_HSWISH: epilogue_cols<LY_ACT_HSWISH>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, cb, cs); break;
+        case LY_ACT_SIGMOID: epilogue_cols<LY_ACT_SIGMOID>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, cb, cs); break;
+        default: epilogue_cols<LY_ACT_NONE>(p, trow, valid, n, h, w, pix, 0, s_scale, s_shift, cb, cs); break;
       }
       tc_fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[grp], 0u);   // the leader's lane waits for both CTAs
+      if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[slot], 0u);   // the leader's lane waits for both CTAs
     }
   }
 
@@ -1018,22 +1029,24 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
     // weights too large for one SM but half of them fit: CTA pairs (conv_cta2_kernel), each CTA keeps Cout/2 rows
     static const int no_cta2 = getenv("LY_CONV_NO_CTA2") ? 1 : 0;   // dev knob
     const long b_half_all = (long)num_k * (cr / 2) * 128;
-    if (!p.halo && !no_cta2 && g.taps == 9 && !g.patch && det == nullptr && d->patch_k == 0 && cr >= 32 && cr <= 128 &&
-        d->Cout <= kC2MaxCout) {
-      double best = -1;
-      const int pitches[3] = {16, 32, 64};
-      for (int i = 0; i < 3; ++i) {
-        const int wt = pitches[i] - 2, ht = 128 / pitches[i];
-        const long a_st = ((130 + 2 * pitches[i]) * 128 + 1023) / 1024 * 1024;
-        if (b_half_all + 2 * a_st > kC2Budget) continue;
-        const double eff = (double)p.Hout * p.Wout / ((double)ceil_div(p.Wout, wt) * ceil_div(p.Hout, ht) * 128.0);
-        if (eff > best + 1e-9) { best = eff; p.halo = pitches[i]; }
-      }
-      if (p.halo) {
-        p.Wt = p.halo - 2;
-        p.Ht = 128 / p.halo;
-        p.a_stage = ((130 + 2 * p.halo) * 128 + 1023) / 1024 * 1024;
-        cta2 = true;
+    if (!p.halo && !no_cta2 && !g.patch && det == nullptr && d->patch_k == 0 && cr >= 32 && cr <= kC2MaxCout &&
+        d->Cout <= kC2MaxCout && (long)num_k * cr * 128 > 100 * 1024) {
+      if (g.taps == 9) {
+        double best = -1;
+        const int pitches[3] = {16, 32, 64};
+        for (int i = 0; i < 3; ++i) {
+          const int wt = pitches[i] - 2, ht = 128 / pitches[i];
+          const long a_st = ((130 + 2 * pitches[i]) * 128 + 1023) / 1024 * 1024;
+          if (b_half_all + 2 * a_st > kC2Budget) continue;
+          const double eff = (double)p.Hout * p.Wout / ((double)ceil_div(p.Wout, wt) * ceil_div(p.Hout, ht) * 128.0);
+          if (eff > best + 1e-9) { best = eff; p.halo = pitches[i]; }
+        }
+        if (p.halo) {
+          p.Wt = p.halo - 2;
+          p.Ht = 128 / p.halo;
+          p.a_stage = ((130 + 2 * p.halo) * 128 + 1023) / 1024 * 1024;
+          cta2 = true;
+        }
       }
     }
   }
@@ -1161,8 +1174,8 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
     p.slab_bytes = 0;
     p.stages = (int)((kC2Budget - b_half_all) / p.a_stage);
     if (p.stages > kC2Slots) p.stages = kC2Slots;
-    LY_REQUIRE(p.stages >= 2 && p.nbuf == 4 && ny == 1, "CTA-pair mode: bad configuration (BN=%d)", p.BN);
     p.kgroup = 1;
+    LY_REQUIRE(p.stages >= 2 && ny == 1 && p.nbuf * p.BN <= 512, "CTA-pair mode: bad configuration (BN=%d)", p.BN);
     p.issuers = 1;
     p.act = d->act; p.scale = d->scale; p.shift = d->shift;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(d->residual);
@@ -1170,8 +1183,8 @@ static int conv_launch(const ly_conv_desc* d, const ly::DetectArgs* det, ly_stre
     const long tiles_c = (long)p.tiles_w * p.tiles_h * p.n_img;
     static const bool verbose_c = getenv("LY_CONV_VERBOSE") != nullptr;
     if (verbose_c)
-      fprintf(stderr, "[conv cta2] BN=%d chunks=%d weight chunks=%d slots=%d halo=%d a_stage=%d tiles=%ld\n", p.BN, p.num_k,
-              p.num_kb, p.stages, p.halo, p.a_stage, tiles_c);
+      fprintf(stderr, "[conv cta2] BN=%d chunks=%d weight chunks=%d stages=%d halo=%d a_stage=%d tiles=%ld\n", p.BN,
+              p.num_k, p.num_kb, p.stages, p.halo, p.a_stage, tiles_c);
     static std::atomic<bool> c2_attr[64];
     int dev = 0;
     LY_CUDA(cudaGetDevice(&dev));

@@ -201,10 +201,18 @@ __device__ __forceinline__ EntryEval eval_entry(const LossGeom& g, int lvl, int 
   return e;
 }
 
+// Block partials meet in 64-bit fixed point (2^-28 units): integer addition is associative, so the loss value does not
+// depend on the order in which blocks finish (fp32 atomics made the first loss of two identical runs differ by an ulp).
+constexpr double kAccScale = 268435456.0;
+__device__ __forceinline__ void acc_add(long long* acc, float v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(acc), (unsigned long long)__double2ll_rn((double)v * kAccScale));
+}
+__device__ __forceinline__ float acc_get(const long long* acc) { return (float)((double)acc[0] * (1.0 / kAccScale)); }
+
 // ---- K2: per-entry forward: box term, objectness correction on the winning entry, class term -------------------
 // acc: [nl][4] = Σ(1 - eiou) | Σ softplus(x_obj) over all cells | Σ objectness correction | Σ class BCE
 __global__ void __launch_bounds__(256) loss_entry_fwd_kernel(LossGeom g, const int* __restrict__ winner,
-                                                             const float* __restrict__ rec, float* __restrict__ acc) {
+                                                             const float* __restrict__ rec, long long* __restrict__ acc) {
   pdl_enter();
   __shared__ float sm[8];
   const long per = 5L * g.na * g.nt;
@@ -231,14 +239,14 @@ __global__ void __launch_bounds__(256) loss_entry_fwd_kernel(LossGeom g, const i
   aobj = block_sum(aobj, sm);
   acls = block_sum(acls, sm);
   if (threadIdx.x == 0) {
-    atomicAdd(&acc[lvl * 4 + 0], abox);
-    atomicAdd(&acc[lvl * 4 + 2], aobj);
-    atomicAdd(&acc[lvl * 4 + 3], acls);
+    acc_add(&acc[lvl * 4 + 0], abox);
+    acc_add(&acc[lvl * 4 + 2], aobj);
+    acc_add(&acc[lvl * 4 + 3], acls);
   }
 }
 
 // ---- K3: dense objectness, target 0 on every cell ---------------------------------------------------------------
-__global__ void __launch_bounds__(256) loss_dense_fwd_kernel(LossGeom g, float* __restrict__ acc) {
+__global__ void __launch_bounds__(256) loss_dense_fwd_kernel(LossGeom g, long long* __restrict__ acc) {
   pdl_enter();
   __shared__ float sm[8];
   const int lvl = blockIdx.y;
@@ -252,11 +260,11 @@ __global__ void __launch_bounds__(256) loss_dense_fwd_kernel(LossGeom g, float* 
     a += softplus(p[b * g.sb[lvl] + an * g.sa[lvl] + gj * g.sy[lvl] + gi * g.sx[lvl]]);
   }
   a = block_sum(a, sm);
-  if (threadIdx.x == 0) atomicAdd(&acc[lvl * 4 + 1], a);
+  if (threadIdx.x == 0) acc_add(&acc[lvl * 4 + 1], a);
 }
 
 // ---- K4: (lbox + lobj + lcls) * bs and the three weighted terms (loss.py:183-191) ------------------------------
-__global__ void loss_finalize_kernel(LossGeom g, const float* __restrict__ acc, const int* __restrict__ counts,
+__global__ void loss_finalize_kernel(LossGeom g, const long long* __restrict__ acc, const int* __restrict__ counts,
                                      float* __restrict__ out) {
   pdl_enter();
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -265,10 +273,10 @@ __global__ void loss_finalize_kernel(LossGeom g, const float* __restrict__ acc, 
     const float n = (float)counts[l];
     const float cells = (float)g.bs * g.na * g.ny[l] * g.nx[l];
     if (n > 0.f) {
-      lbox += acc[l * 4 + 0] / n;
-      if (g.nc > 1) lcls += acc[l * 4 + 3] / (n * g.nc);
+      lbox += acc_get(&acc[l * 4 + 0]) / n;
+      if (g.nc > 1) lcls += acc_get(&acc[l * 4 + 3]) / (n * g.nc);
     }
-    lobj += g.balance[l] * (acc[l * 4 + 1] + acc[l * 4 + 2]) / cells;
+    lobj += g.balance[l] * (acc_get(&acc[l * 4 + 1]) + acc_get(&acc[l * 4 + 2])) / cells;
   }
   lbox *= g.box;
   lobj *= g.obj;
@@ -368,11 +376,11 @@ extern "C" long ly_yolo_loss_workspace_bytes(const ly_loss_desc* d) {
   long cells = 0;
   for (int l = 0; l < g.nl; ++l) cells += (long)g.bs * g.na * g.ny[l] * g.nx[l];
   const long entries = 5L * g.na * g.nt * g.nl;
-  // winner map | entry records | counts [4] | acc [nl][4]
-  return cells * 4 + entries * kRec * 4 + 16 + kMaxLevels * 16;
+  // winner map | entry records | counts [4] | pad to 8 | acc [nl][4] int64
+  return cells * 4 + entries * kRec * 4 + 16 + 8 + kMaxLevels * 32;
 }
 
-static void ws_split(const LossGeom& g, void* ws, int** winner, float** rec, int** counts, float** acc, long* cells) {
+static void ws_split(const LossGeom& g, void* ws, int** winner, float** rec, int** counts, long long** acc, long* cells) {
   long c = 0;
   for (int l = 0; l < g.nl; ++l) c += (long)g.bs * g.na * g.ny[l] * g.nx[l];
   const long entries = 5L * g.na * g.nt * g.nl;
@@ -380,7 +388,7 @@ static void ws_split(const LossGeom& g, void* ws, int** winner, float** rec, int
   *winner = (int*)ws;
   *rec = (float*)((char*)ws + c * 4);
   *counts = (int*)((char*)ws + c * 4 + entries * kRec * 4);
-  *acc = (float*)((char*)ws + c * 4 + entries * kRec * 4 + 16);
+  *acc = (long long*)((char*)ws + ((c * 4 + entries * kRec * 4 + 16 + 7) & ~7L));
 }
 
 extern "C" int ly_yolo_loss_fwd(const ly_loss_desc* d, void* workspace, float* out, ly_stream_t st) {
@@ -389,12 +397,13 @@ extern "C" int ly_yolo_loss_fwd(const ly_loss_desc* d, void* workspace, float* o
   if (rc) return rc;
   LY_REQUIRE(workspace && out && d->targets && d->anchors, "ly_yolo_loss_fwd: null pointer");
   int *winner, *counts;
-  float *rec, *acc;
+  float* rec;
+  long long* acc;
   long cells;
   ws_split(g, workspace, &winner, &rec, &counts, &acc, &cells);
   cudaStream_t s = (cudaStream_t)st;
   LY_CUDA(cudaMemsetAsync(winner, 0xFF, cells * 4, s));
-  LY_CUDA(cudaMemsetAsync(counts, 0, 16 + kMaxLevels * 16, s));
+  LY_CUDA(cudaMemsetAsync(counts, 0, 16 + 8 + kMaxLevels * 32, s));
   const long per = 5L * g.na * g.nt;
   LY_CUDA(launch(loss_assign_kernel, ceil_div(per * g.nl, 256), 256, 0, s, g, d->targets, d->anchors, winner, rec, counts));
   LY_LAUNCH_CHECK();
@@ -416,7 +425,8 @@ extern "C" int ly_yolo_loss_bwd(const ly_loss_desc* d, const void* workspace, co
   LY_REQUIRE(workspace && grad_scale, "ly_yolo_loss_bwd: null pointer");
   for (int l = 0; l < g.nl; ++l) LY_REQUIRE(g.dp[l] != nullptr, "ly_yolo_loss_bwd: level %d has no gradient map", l);
   int *winner, *counts;
-  float *rec, *acc;
+  float* rec;
+  long long* acc;
   long cells;
   ws_split(g, const_cast<void*>(workspace), &winner, &rec, &counts, &acc, &cells);
   cudaStream_t s = (cudaStream_t)st;

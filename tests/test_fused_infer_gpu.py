@@ -32,24 +32,25 @@ def test_conv3x3_halo_ragged(shape):
     assert rel_l2(y.float(), ref) < TOL_BF16
 
 
-@pytest.mark.parametrize("case", [(2, 128, 128, 40, 40), (1, 128, 128, 37, 45), (1, 128, 128, 5, 3), (3, 128, 128, 15, 14),
-                                  (5, 160, 96, 20, 20), (2, 72, 112, 33, 30), (64, 128, 128, 40, 40),
-                                  (1, 256, 256, 33, 30), (5, 136, 200, 20, 20), (1, 64, 320, 5, 3)])
-def test_conv3x3_cta2_ragged(case):
-    """3x3 Conv whose weights fit in shared memory only when split over a CTA pair: conv_cta2_kernel (cta_group::2, M = 256,
-    each CTA keeps Cout/2 weight rows resident, halo boxes).  Single tiles and odd tile counts (the peer CTA of the last
-    unit has no tile), ragged channel chunks, the bench geometry; the last three cases are too large even for a pair and
-    stay on the streaming path.  Forward in eval mode and input gradient (the dgrad convolution takes the same kernel)
-    against the oracle."""
+@pytest.mark.parametrize("case", [(2, 128, 128, 40, 40, 3), (1, 128, 128, 37, 45, 3), (1, 128, 128, 5, 3, 3),
+                                  (3, 128, 128, 15, 14, 3), (5, 160, 96, 20, 20, 3), (2, 72, 112, 33, 30, 3),
+                                  (64, 128, 128, 40, 40, 3), (2, 64, 256, 20, 20, 3), (3, 48, 208, 9, 31, 3),
+                                  (1, 256, 256, 33, 30, 3), (5, 136, 200, 20, 20, 3), (1, 64, 320, 5, 3, 3)])
+def test_conv_cta2_ragged(case):
+    """3x3 convolutions whose weights fit in shared memory only when split over a CTA pair: conv_cta2_kernel (cta_group::2,
+    M = 256, each CTA keeps Cout/2 weight rows resident, halo boxes).  Single tiles and odd tile counts (the peer CTA of
+    the last unit has no tile), ragged channel chunks, four and two accumulators (Cout <= 128 / <= 256), the bench
+    geometry; the last three cases are too large even for a pair and stay on the streaming path.  Forward in eval mode
+    and input gradient (the dgrad convolution takes the same kernels) against the oracle."""
     M = _mods()
-    n, c1, c2, h, w = case
+    n, c1, c2, h, w, k = case
     torch.manual_seed(3)
-    mod = M.Conv(c1, c2, 3, 1).cuda().eval()
+    mod = M.Conv(c1, c2, k, 1).cuda().eval()
     randomise_bn(mod, 5)
     x = half_normal((n, c1, h, w), 11, signed=True)
     with torch.no_grad():
         y = mod(x)
-        ref = R.conv_block(oracle_params(mod), "m", x.float(), R.Ctx(False), k=3)
+        ref = R.conv_block(oracle_params(mod), "m", x.float(), R.Ctx(False), k=k)
     assert y.shape == ref.shape
     assert rel_l2(y.float(), ref) < TOL_BF16
     # gradient with respect to the input (eval-mode BN: a fixed affine map, so the oracle's autograd is the reference)
@@ -57,7 +58,7 @@ def test_conv3x3_cta2_ragged(case):
     g = half_normal(tuple(ref.shape), 12, signed=True)
     (mod(xg).float() * g.float()).sum().backward()
     xr = x.float().clone().requires_grad_(True)
-    (R.conv_block(oracle_params(mod), "m", xr, R.Ctx(False), k=3) * g.float()).sum().backward()
+    (R.conv_block(oracle_params(mod), "m", xr, R.Ctx(False), k=k) * g.float()).sum().backward()
     assert rel_l2(xg.grad.float(), xr.grad) < TOL_BF16
 
 
