@@ -253,6 +253,12 @@ int ly_rf_tc_stats(const void* x, long ldx, int N, int H, int W, int C, int s, i
                    const void* shift, float* maps, ly_stream_t stream);
 int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
                    const void* shift, const float* se, const float* att, void* A, ly_stream_t stream);
+/* Training forward of the receptive-field generation on the same kernel (models/rfa.py:95-100, the grouped 3x3 alone):
+ * Z bf16 [N*ho*wo][9][C], Z[m][t*C+c] = generate + shift — the layout and the meaning of ly_rf_generate's output; pass a
+ * zero shift for the raw convolution that feeds the batch-statistics BatchNorm.  wc as above with scale 1 (bf16 weights:
+ * the difference to ly_rf_generate's fp32 weights is below the bf16 rounding of Z).  Z 32-byte aligned. */
+int ly_rf_tc_generate(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
+                      const void* shift, void* Z, ly_stream_t stream);
 /* ly_rf_tc_apply fused with RFCBAMConv.conv + its BatchNorm + ReLU (models/rfa.py:121-129): the gated receptive-field
  * matrix (9*C wide) never reaches HBM — each [128 pixels][144] tile goes from the gating epilogue through shared memory
  * straight into a second tcgen05 accumulation over the channel groups.  out: bf16 NHWC [N][ho][wo][Cout] (pixel stride

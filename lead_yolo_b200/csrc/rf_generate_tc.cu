@@ -111,9 +111,9 @@ __device__ __forceinline__ uint32_t relu_bf16x2(uint64_t v) {   // bf16(relu(lo)
   return r;
 }
 
-template <int MODE>  // 0 = STATS, 1 = APPLY
+template <int MODE>  // 0 = STATS, 1 = APPLY, 2 = RAW (training forward: generate + shift as bf16 [M][9][C], no gate)
 __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_constant__ RfTcParams p) {
-  constexpr int kRtStages = MODE == 0 ? 6 : 4;   // APPLY trades two ring stages for the output staging buffers
+  constexpr int kRtStages = MODE == 1 ? 4 : 6;   // APPLY trades two ring stages for the output staging buffers
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[kRtStages], empty_bar[kRtStages], tfull[2], tempty[2], b1_full[2], b1_empty[2];
   __shared__ uint32_t tmem_base_s;
@@ -333,6 +333,15 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
             float s_lo, s_hi;
             f2_unpack(s2, s_lo, s_hi);
             va[tt] = mx; vb[tt] += s_lo + s_hi;
+          } else if (MODE == 2) {   // one full 32-byte sector per lane: Z[m][t][cg*16 .. +16]
+            if (valid) {
+              uint32_t wds[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                wds[j] = pack_bf16x2(__uint_as_float(acc[tt][2 * j]), __uint_as_float(acc[tt][2 * j + 1]));
+              const long m = ((long)n * p.ho + h) * p.wo + w;
+              st_global_256(p.A + (m * 9 + (t0 + tt)) * (long)p.C + cg * 16, wds);
+            }
           } else {           // relu(acc) * se * att = relu(acc * (se * att)): both gates are sigmoids (> 0)
             const uint64_t att2 = f2_pack(va[tt], va[tt]);
             uint32_t wds[8];
@@ -809,13 +818,16 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   if (!attr_done[dev & 63].load()) {
     LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem0));
     LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem0));
     attr_done[dev & 63].store(true);
   }
   if (mode == 0) {
     LY_CUDA(cudaMemsetAsync(maps, 0, sizeof(float) * 2 * (size_t)N * ho * 3 * wo * 3, stream));
     LY_CUDA(launch(rf_tc_kernel<0>, grid, kRtThreads, smem0, stream, p));
-  } else {
+  } else if (mode == 1) {
     LY_CUDA(launch(rf_tc_kernel<1>, grid, kRtThreads, smem1, stream, p));
+  } else {
+    LY_CUDA(launch(rf_tc_kernel<2>, grid, kRtThreads, smem0, stream, p));
   }
   LY_LAUNCH_CHECK();
   return LY_OK;
@@ -908,6 +920,15 @@ extern "C" int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int 
   LY_REQUIRE(se && att && A && reinterpret_cast<uintptr_t>(A) % 16 == 0 && reinterpret_cast<uintptr_t>(se) % 16 == 0,
              "ly_rf_tc_apply: null or misaligned pointer");
   return rf_tc_launch(1, x, ldx, N, H, W, C, s, ho, wo, wc, shift, se, att, A, nullptr, (cudaStream_t)st);
+}
+
+// Training forward of the receptive-field generation (models/rfa.py:95-100, the grouped 3x3 convolution alone):
+// Z bf16 [N*ho*wo][9][C], Z[m][t][c] = generate (+ shift; pass zeros for the raw convolution), the layout ly_rf_generate
+// writes.  The diagonal weights are bf16 here (fp32 in ly_rf_generate): the difference is below the bf16 rounding of Z.
+extern "C" int ly_rf_tc_generate(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
+                                 const void* shift, void* Z, ly_stream_t st) {
+  LY_REQUIRE(Z && reinterpret_cast<uintptr_t>(Z) % 32 == 0, "ly_rf_tc_generate: null or misaligned pointer");
+  return rf_tc_launch(2, x, ldx, N, H, W, C, s, ho, wo, wc, shift, nullptr, nullptr, Z, nullptr, (cudaStream_t)st);
 }
 
 // Pass 2 fused with RFCBAMConv.conv (models/rfa.py:121-129): out bf16 NHWC [N][ho][wo][Cout] = relu(scale2 * (gated

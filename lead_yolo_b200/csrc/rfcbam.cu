@@ -73,38 +73,51 @@ __global__ void __launch_bounds__(128) rf_generate_kernel(const __nv_bfloat16* _
 }
 
 // ------------------------------------------------------------------------------------------------
-// channel max / mean of G per (pixel, tap): one warp per (m, t)
+// channel max / mean of G per (pixel, tap).  LPR lanes share one (m, t) row of C channels, each lane takes every
+// LPR-th 16-byte vector (four per lane for C = 128 / 256, all loads issued before the first use), so a warp covers
+// 32 / LPR rows at once.  (One warp per row left half the lanes idle at C = 128 and ran at 12 % of the HBM rate.)
 // ------------------------------------------------------------------------------------------------
+template <int LPR>
 __global__ void __launch_bounds__(256) rf_poolc_kernel(const __nv_bfloat16* __restrict__ G, long M, int KK, int K,
                                                        int V, int ho, int wo, float* __restrict__ maps,
                                                        int16_t* __restrict__ amax) {
   pdl_enter();
-  const int lane = threadIdx.x & 31;
-  const long wid = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (wid >= M * KK) return;
-  const int t = (int)(wid % KK);
-  const long m = wid / KK;
+  const int sub = threadIdx.x % LPR;
+  const long row = ((long)blockIdx.x * blockDim.x + threadIdx.x) / LPR;
+  const bool live = row < M * KK;
   const int C = V * 8;
-  const __nv_bfloat16* row = G + (m * KK + t) * (long)C;
+  const __nv_bfloat16* rp = G + (live ? row : 0) * (long)C;
   float mx = -INFINITY, sum = 0.f;
   int mi = 0;
-  for (int v = lane; v < V; v += 32) {
-    float f[8];
-    unpack8(ldg16(row + v * 8), f);
+  for (int v0 = sub; v0 < V; v0 += 4 * LPR) {
+    uint4 u[4];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      sum += f[e];
-      if (f[e] > mx) { mx = f[e]; mi = v * 8 + e; }
+    for (int q = 0; q < 4; ++q)
+      if (v0 + q * LPR < V) u[q] = ldg16(rp + (v0 + q * LPR) * 8);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int v = v0 + q * LPR;
+      if (v < V) {
+        float f[8];
+        unpack8(u[q], f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          sum += f[e];
+          if (f[e] > mx) { mx = f[e]; mi = v * 8 + e; }
+        }
+      }
     }
   }
-  sum = warp_sum(sum);
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
+  for (int o = LPR / 2; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(0xffffffffu, sum, o);
     const float om = __shfl_xor_sync(0xffffffffu, mx, o);
     const int oi = __shfl_xor_sync(0xffffffffu, mi, o);
     if (om > mx || (om == mx && oi < mi)) { mx = om; mi = oi; }
   }
-  if (lane == 0) {
+  if (live && sub == 0) {
+    const int t = (int)(row % KK);
+    const long m = row / KK;
     const int w = (int)(m % wo), h = (int)((m / wo) % ho);
     const long n = m / ((long)wo * ho);
     const int n1 = t / K, n2 = t % K;
@@ -113,6 +126,20 @@ __global__ void __launch_bounds__(256) rf_poolc_kernel(const __nv_bfloat16* __re
     maps[pos * 2 + 1] = sum / (float)C;
     if (amax != nullptr) amax[pos] = (int16_t)mi;
   }
+}
+
+static int poolc_launch(const void* G, long M, int KK, int k, int V, int ho, int wo, float* maps, int16_t* amax,
+                        cudaStream_t st) {
+  const long rows = M * KK;
+  const __nv_bfloat16* g = (const __nv_bfloat16*)G;
+  if (V <= 16)
+    LY_CUDA(launch(rf_poolc_kernel<4>, ceil_div(rows * 4, 256), 256, 0, st, g, M, KK, k, V, ho, wo, maps, amax));
+  else if (V <= 32)
+    LY_CUDA(launch(rf_poolc_kernel<8>, ceil_div(rows * 8, 256), 256, 0, st, g, M, KK, k, V, ho, wo, maps, amax));
+  else
+    LY_CUDA(launch(rf_poolc_kernel<32>, ceil_div(rows * 32, 256), 256, 0, st, g, M, KK, k, V, ho, wo, maps, amax));
+  LY_LAUNCH_CHECK();
+  return LY_OK;
 }
 
 // att = sigmoid(conv3x3_{2->1, pad 1}(maps))   (get_weight, rfa.py:106,127)
@@ -166,8 +193,11 @@ __global__ void __launch_bounds__(256) rf_gate_kernel(const __nv_bfloat16* __res
 // ------------------------------------------------------------------------------------------------
 // Backward of the gating: given dA, G, se, att ->
 //   dG1 = dA*se*att (written to dG), dse[part][n,c] = this block's share of Σ dA*G*att, datt[pos] = Σ_c dA*G*se.
-// grid = (blocks per image, N); each warp strides over the (m, t) pairs of its image.
+// grid = (blocks per image, N).  LPR lanes share one (m, t) row (each lane up to four 16-byte channel vectors of dA and of
+// G, all eight loads in flight before the first use); the 256 / LPR row groups of a block stride over the rows of its
+// image.  (One warp per row: half the lanes idle at C = 128, one row in flight per warp, 31 % of the HBM rate.)
 // ------------------------------------------------------------------------------------------------
+template <int LPR>
 __global__ void __launch_bounds__(256) rf_gate_bwd_kernel(const __nv_bfloat16* __restrict__ dA,
                                                           const __nv_bfloat16* __restrict__ G, int KK, int K, int V,
                                                           int ho, int wo, const __nv_bfloat16* __restrict__ se,
@@ -175,37 +205,51 @@ __global__ void __launch_bounds__(256) rf_gate_bwd_kernel(const __nv_bfloat16* _
                                                           __nv_bfloat16* __restrict__ dG, float* __restrict__ dse,
                                                           float* __restrict__ datt) {
   pdl_enter();
+  constexpr int QV = 4;                       // channel vectors per lane: C <= LPR * 32
+  constexpr int GPB = 256 / LPR;              // row groups per block
   const int lane = threadIdx.x & 31;
+  const int sub = threadIdx.x % LPR;
+  const int grp = threadIdx.x / LPR;
   const int n = blockIdx.y;
   const int C = V * 8;
   const long per_img = (long)ho * wo * KK;
-  const long warps = ((long)gridDim.x * blockDim.x) >> 5;
-  const long w0 = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  // each lane owns up to 2 channel vectors (C <= 512)
-  float s8[2][8], ds[2][8];
+  const long step = (long)gridDim.x * GPB;
+  float s8[QV][8], ds[QV][8];
 #pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const int v = lane + q * 32;
+  for (int q = 0; q < QV; ++q) {
+    const int v = sub + q * LPR;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { s8[q][e] = 0.f; ds[q][e] = 0.f; }
     if (v < V) unpack8(ldg16(se + (long)n * ldse + v * 8), s8[q]);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) ds[q][e] = 0.f;
   }
-  for (long i = w0; i < per_img; i += warps) {
+  // every thread of the block runs the same number of iterations (the shuffles below need whole warps)
+  for (long base = (long)blockIdx.x * GPB; base < per_img; base += step) {
+    const long i = base + grp;
+    const bool live = i < per_img;
     const int t = (int)(i % KK);
     const long ml = i / KK;  // pixel within image
     const int w = (int)(ml % wo), h = (int)(ml / wo);
     const int n1 = t / K, n2 = t % K;
     const long pos = ((long)n * (ho * K) + (h * K + n1)) * (long)(wo * K) + (w * K + n2);
-    const float a = __ldg(att + pos);
     const long rowoff = (((long)n * ho * wo + ml) * KK + t) * (long)C;
+    uint4 ud[QV], ug[QV];
+#pragma unroll
+    for (int q = 0; q < QV; ++q) {
+      const int v = sub + q * LPR;
+      if (live && v < V) {
+        ud[q] = ldg16(dA + rowoff + v * 8);
+        ug[q] = ldg16(G + rowoff + v * 8);
+      }
+    }
+    const float a = live ? __ldg(att + pos) : 0.f;
     float da_att = 0.f;
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const int v = lane + q * 32;
-      if (v < V) {
+    for (int q = 0; q < QV; ++q) {
+      const int v = sub + q * LPR;
+      if (live && v < V) {
         float d[8], g[8];
-        unpack8(ldg16(dA + rowoff + v * 8), d);
-        unpack8(ldg16(G + rowoff + v * 8), g);
+        unpack8(ud[q], d);
+        unpack8(ug[q], g);
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           const float dg = d[e] * g[e];
@@ -216,21 +260,30 @@ __global__ void __launch_bounds__(256) rf_gate_bwd_kernel(const __nv_bfloat16* _
         *reinterpret_cast<uint4*>(dG + rowoff + v * 8) = pack8(d);
       }
     }
-    da_att = warp_sum(da_att);
-    if (lane == 0) datt[pos] = da_att;
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) da_att += __shfl_xor_sync(0xffffffffu, da_att, o);
+    if (live && sub == 0) datt[pos] = da_att;
   }
-  // Deterministic reduction: the eight warps of the block are summed in warp order through shared memory and the block
-  // STORES its partial at dse[blockIdx.x][n][c]; the caller adds the gridDim.x partials in order.  (dse is broadcast back
-  // over all pixels of the image after a bf16 rounding: with order-dependent float atomics a rounding flip of one value
-  // shifted a whole channel's input gradient from run to run.)
+  // Deterministic reduction: the row groups of a warp are folded by shuffles, the eight warps of the block are summed in
+  // warp order through shared memory and the block STORES its partial at dse[blockIdx.x][n][c]; the caller adds the
+  // gridDim.x partials in order.  (dse is broadcast back over all pixels of the image after a bf16 rounding: with
+  // order-dependent float atomics a rounding flip of one value shifted a whole channel's input gradient from run to run.)
+#pragma unroll
+  for (int q = 0; q < QV; ++q)
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+#pragma unroll
+      for (int o = LPR; o < 32; o <<= 1) ds[q][e] += __shfl_xor_sync(0xffffffffu, ds[q][e], o);
   __shared__ float red[8][512];
   const int warp = threadIdx.x >> 5;
+  if (lane < LPR) {
 #pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const int v = lane + q * 32;
-    if (v < V) {
+    for (int q = 0; q < QV; ++q) {
+      const int v = sub + q * LPR;
+      if (v < V) {
 #pragma unroll
-      for (int e = 0; e < 8; ++e) red[warp][v * 8 + e] = ds[q][e];
+        for (int e = 0; e < 8; ++e) red[warp][v * 8 + e] = ds[q][e];
+      }
     }
   }
   __syncthreads();
@@ -523,9 +576,10 @@ extern "C" int ly_rf_attention(const void* G, int N, int ho, int wo, int C, int 
   LY_REQUIRE(G && wa && maps && att && LY_ALIGNED16(G) && C % 8 == 0 && C > 0, "ly_rf_attention: bad args");
   const int V = C / 8, KK = k * k;
   const long M = (long)N * ho * wo;
-  LY_CUDA(launch(rf_poolc_kernel, ceil_div(M * KK * 32, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)G, M, KK, k, V, ho,
-                                                                          wo, maps, amax));
-  LY_LAUNCH_CHECK();
+  {
+    const int prc = poolc_launch(G, M, KK, k, V, ho, wo, maps, amax, (cudaStream_t)st);
+    if (prc != LY_OK) return prc;
+  }
   const long total = (long)N * ho * k * wo * k;
   LY_CUDA(launch(rf_att_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, maps, N, ho * k, wo * k, wa, att));
   LY_LAUNCH_CHECK();
@@ -552,9 +606,12 @@ extern "C" int ly_rf_gate_bwd(const void* dA, const void* G, int N, int ho, int 
   const long per_img = (long)ho * wo * KK;
   (void)per_img;
   dim3 grid(LY_RF_GATE_PARTS, N);   // fixed: the caller sizes dse as [LY_RF_GATE_PARTS][N][C]
-  LY_CUDA(launch(rf_gate_bwd_kernel, grid, 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)dA, (const __nv_bfloat16*)G, KK, k, V,
-                                                        ho, wo, (const __nv_bfloat16*)se, ldse, att,
-                                                        (__nv_bfloat16*)dG, dse, datt));
+  const __nv_bfloat16 *da_ = (const __nv_bfloat16*)dA, *g_ = (const __nv_bfloat16*)G, *se_ = (const __nv_bfloat16*)se;
+  __nv_bfloat16* dg_ = (__nv_bfloat16*)dG;
+  cudaStream_t s_ = (cudaStream_t)st;
+  if (V <= 16) LY_CUDA(launch(rf_gate_bwd_kernel<4>, grid, 256, 0, s_, da_, g_, KK, k, V, ho, wo, se_, ldse, att, dg_, dse, datt));
+  else if (V <= 32) LY_CUDA(launch(rf_gate_bwd_kernel<8>, grid, 256, 0, s_, da_, g_, KK, k, V, ho, wo, se_, ldse, att, dg_, dse, datt));
+  else LY_CUDA(launch(rf_gate_bwd_kernel<16>, grid, 256, 0, s_, da_, g_, KK, k, V, ho, wo, se_, ldse, att, dg_, dse, datt));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -697,9 +754,10 @@ extern "C" int ly_rf_attention_noalloc(const void* G, int N, int ho, int wo, int
   if (rc != LY_OK) return rc;
   const int V = C / 8, KK = k * k;
   const long M = (long)N * ho * wo;
-  LY_CUDA(launch(rf_poolc_kernel, ceil_div(M * KK * 32, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)G, M, KK, k, V, ho,
-                                                                          wo, maps, amax));
-  LY_LAUNCH_CHECK();
+  {
+    const int prc = poolc_launch(G, M, KK, k, V, ho, wo, maps, amax, (cudaStream_t)st);
+    if (prc != LY_OK) return prc;
+  }
   const long total = (long)N * ho * k * wo * k;
   LY_CUDA(launch(rf_att_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, maps, N, ho * k, wo * k, wa, att));
   LY_LAUNCH_CHECK();

@@ -182,6 +182,7 @@ _SIGS = {
     "ly_rfcbam_front_infer": "pliiiiiiiipppppipppppp",
     "ly_rf_tc_stats": "pliiiiiiippp",
     "ly_rf_tc_apply": "pliiiiiiippppp",
+    "ly_rf_tc_generate": "pliiiiiiippp",
     "ly_rfcbam_fused_infer": "pliiiiiiipppppppipl",
     "ly_rf_gap_sum": "pliiip",
     "ly_gap_mean": "pliiipp",

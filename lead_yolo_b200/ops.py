@@ -8,6 +8,8 @@ from __future__ import annotations
 
 import weakref
 
+import os
+
 import torch
 
 from . import lowlevel as ll
@@ -524,6 +526,27 @@ def rf_channel_perm(c, k, device):
     return hit
 
 
+RF_GENERATE_CUDA_CORES = bool(os.environ.get("LY_RF_GENERATE_CUDA"))   # dev knob: fp32 CUDA-core feature generation
+
+
+def _rf_generate_raw(x, wgk, k, s, ho, wo):
+    """z = the grouped k x k convolution of rfa.py:95-100 alone, (N, k*k*C, ho, wo), channel t*C + c.  k = 3 with
+    C % 16 == 0 runs on the tensor cores (ly_rf_tc_generate, one tcgen05.mma per tap and 16-channel group, bf16 weights);
+    everything else on ly_rf_generate (fp32 weights)."""
+    n, c, h, w = x.shape
+    g = ll.empty_cl(n, k * k * c, ho, wo, device=x.device)
+    if k == 3 and c % 16 == 0 and not RF_GENERATE_CUDA_CORES:
+        wc = wgk.view(9, 9, c // 16, 16).permute(2, 1, 0, 3).reshape(c // 16, 1296).to(BF16).contiguous()
+        key = ("rfzero", c, x.device)
+        zero = _cache.get(key)
+        if zero is None:
+            zero = _cache[key] = torch.zeros((c // 16, 144), dtype=torch.int32, device=x.device)
+        ll.call("ly_rf_tc_generate", x, ll.pixel_ld(x), n, h, w, c, s, ho, wo, wc, zero, g)
+    else:
+        ll.call("ly_rf_generate", x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, None, ll.ACT["none"], g)
+    return g
+
+
 class RfGenerateFn(torch.autograd.Function):
     """Depthwise receptive-field features z (N, k*k*C, ho, wo), channel t*C+c; optional fused affine+act."""
 
@@ -533,8 +556,11 @@ class RfGenerateFn(torch.autograd.Function):
         n, c, h, w = x.shape
         ho, wo = rf_out_size(h, w, k, s)
         wgk = rf_pack_generate_weight(wg, c, k)
-        g = ll.empty_cl(n, k * k * c, ho, wo, device=x.device)
-        ll.call("ly_rf_generate", x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, scale, shift, ll.ACT[act], g)
+        if scale is None:
+            g = _rf_generate_raw(x, wgk, k, s, ho, wo)
+        else:
+            g = ll.empty_cl(n, k * k * c, ho, wo, device=x.device)
+            ll.call("ly_rf_generate", x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, scale, shift, ll.ACT[act], g)
         ctx.save_for_backward(x, wgk)
         ctx.cfg = (k, s, ho, wo, wg.dtype, scale is not None)
         return g
@@ -568,8 +594,7 @@ class RfFrontFn(torch.autograd.Function):
         n, c, h, w = x.shape
         ho, wo = rf_out_size(h, w, k, s)
         wgk = rf_pack_generate_weight(wg, c, k)
-        g = ll.empty_cl(n, k * k * c, ho, wo, device=x.device)
-        ll.call("ly_rf_generate", x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, None, ll.ACT["none"], g)
+        g = _rf_generate_raw(x, wgk, k, s, ho, wo)
         gap = _gap_mean(x)
         ctx.save_for_backward(x, wgk)
         ctx.cfg = (k, s, ho, wo, wg.dtype)
