@@ -167,27 +167,49 @@ __global__ void __launch_bounds__(256) rf_att_kernel(const float* __restrict__ m
 }
 
 // A = G * se[n, c] * att[n, h*k+n1, w*k+n2]     (also used for dG1 = dA * se * att)
+// LPR lanes share one (m, t) row, four 16-byte vectors per lane: the row's index arithmetic (three divisions) and its
+// attention value are paid once per four vectors and the four loads are in flight together.
+template <int LPR>
 __global__ void __launch_bounds__(256) rf_gate_kernel(const __nv_bfloat16* __restrict__ G, long M, int KK, int K,
                                                       int V, int ho, int wo, const __nv_bfloat16* __restrict__ se,
                                                       long ldse, const float* __restrict__ att,
                                                       __nv_bfloat16* __restrict__ A) {
   pdl_enter();
-  const long total = M * KK * V;
-  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (tid >= total) return;
-  const int v = (int)(tid % V);
-  const int t = (int)((tid / V) % KK);
-  const long m = tid / ((long)V * KK);
+  const int sub = threadIdx.x % LPR;
+  const long row = ((long)blockIdx.x * blockDim.x + threadIdx.x) / LPR;
+  if (row >= M * KK) return;
+  const int t = (int)(row % KK);
+  const long m = row / KK;
   const int w = (int)(m % wo), h = (int)((m / wo) % ho);
   const long n = m / ((long)wo * ho);
   const int n1 = t / K, n2 = t % K;
   const float a = __ldg(att + (n * (ho * K) + (h * K + n1)) * (long)(wo * K) + (w * K + n2));
-  float g[8], s8[8];
-  unpack8(ldg16(G + tid * 8), g);
-  unpack8(ldg16(se + n * ldse + v * 8), s8);
+  const __nv_bfloat16* grow = G + row * (long)(V * 8);
+  __nv_bfloat16* arow = A + row * (long)(V * 8);
+  const __nv_bfloat16* srow = se + n * ldse;
+  for (int v0 = sub; v0 < V; v0 += 4 * LPR) {
+    uint4 ug[4], us[4];
 #pragma unroll
-  for (int e = 0; e < 8; ++e) g[e] *= s8[e] * a;
-  *reinterpret_cast<uint4*>(A + tid * 8) = pack8(g);
+    for (int q = 0; q < 4; ++q) {
+      const int v = v0 + q * LPR;
+      if (v < V) {
+        ug[q] = ldg16(grow + v * 8);
+        us[q] = ldg16(srow + v * 8);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int v = v0 + q * LPR;
+      if (v < V) {
+        float g[8], s8[8];
+        unpack8(ug[q], g);
+        unpack8(us[q], s8);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] *= s8[e] * a;
+        *reinterpret_cast<uint4*>(arow + v * 8) = pack8(g);
+      }
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -349,17 +371,17 @@ __global__ void __launch_bounds__(256) rf_att_bwd_kernel(const float* __restrict
   if (threadIdx.x < 18) atomicAdd(&dwa[threadIdx.x], sw[threadIdx.x]);
 }
 
-// dG += dmean/C + [c == argmax] * dmax       (in place on dG)
+// dG += dmean/C + [c == argmax] * dmax       (in place on dG); LPR lanes per (m, t) row as in rf_gate_kernel
+template <int LPR>
 __global__ void __launch_bounds__(256) rf_poolc_bwd_kernel(__nv_bfloat16* __restrict__ dG, long M, int KK, int K,
                                                            int V, int ho, int wo, const float* __restrict__ dmaps,
                                                            const int16_t* __restrict__ amax) {
   pdl_enter();
-  const long total = M * KK * V;
-  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (tid >= total) return;
-  const int v = (int)(tid % V);
-  const int t = (int)((tid / V) % KK);
-  const long m = tid / ((long)V * KK);
+  const int sub = threadIdx.x % LPR;
+  const long row = ((long)blockIdx.x * blockDim.x + threadIdx.x) / LPR;
+  if (row >= M * KK) return;
+  const int t = (int)(row % KK);
+  const long m = row / KK;
   const int w = (int)(m % wo), h = (int)((m / wo) % ho);
   const long n = m / ((long)wo * ho);
   const int n1 = t / K, n2 = t % K;
@@ -367,11 +389,24 @@ __global__ void __launch_bounds__(256) rf_poolc_bwd_kernel(__nv_bfloat16* __rest
   const float2 dm = __ldg(reinterpret_cast<const float2*>(dmaps + pos * 2));
   const int am = amax[pos];
   const float dmean = dm.y / (float)(V * 8);
-  float d[8];
-  unpack8(*reinterpret_cast<const uint4*>(dG + tid * 8), d);
+  __nv_bfloat16* drow = dG + row * (long)(V * 8);
+  for (int v0 = sub; v0 < V; v0 += 4 * LPR) {
+    uint4 u[4];
 #pragma unroll
-  for (int e = 0; e < 8; ++e) d[e] += dmean + ((v * 8 + e) == am ? dm.x : 0.f);
-  *reinterpret_cast<uint4*>(dG + tid * 8) = pack8(d);
+    for (int q = 0; q < 4; ++q)
+      if (v0 + q * LPR < V) u[q] = *reinterpret_cast<const uint4*>(drow + (v0 + q * LPR) * 8);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int v = v0 + q * LPR;
+      if (v < V) {
+        float d[8];
+        unpack8(u[q], d);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) d[e] += dmean + ((v * 8 + e) == am ? dm.x : 0.f);
+        *reinterpret_cast<uint4*>(drow + v * 8) = pack8(d);
+      }
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -593,8 +628,15 @@ extern "C" int ly_rf_gate(const void* G, int N, int ho, int wo, int C, int k, co
              "ly_rf_gate: bad args");
   const int V = C / 8, KK = k * k;
   const long M = (long)N * ho * wo;
-  LY_CUDA(launch(rf_gate_kernel, ceil_div(M * KK * V, 256), 256, 0, (cudaStream_t)st, 
-      (const __nv_bfloat16*)G, M, KK, k, V, ho, wo, (const __nv_bfloat16*)se, ldse, att, (__nv_bfloat16*)A));
+  {
+    const __nv_bfloat16 *g_ = (const __nv_bfloat16*)G, *se_ = (const __nv_bfloat16*)se;
+    __nv_bfloat16* a_ = (__nv_bfloat16*)A;
+    cudaStream_t s_ = (cudaStream_t)st;
+    const long rows = M * KK;
+    if (V <= 16) LY_CUDA(launch(rf_gate_kernel<4>, ceil_div(rows * 4, 256), 256, 0, s_, g_, M, KK, k, V, ho, wo, se_, ldse, att, a_));
+    else if (V <= 32) LY_CUDA(launch(rf_gate_kernel<8>, ceil_div(rows * 8, 256), 256, 0, s_, g_, M, KK, k, V, ho, wo, se_, ldse, att, a_));
+    else LY_CUDA(launch(rf_gate_kernel<32>, ceil_div(rows * 32, 256), 256, 0, s_, g_, M, KK, k, V, ho, wo, se_, ldse, att, a_));
+  }
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
@@ -626,8 +668,14 @@ extern "C" int ly_rf_attention_bwd(const float* datt, const float* att, const fl
   LY_CUDA(launch(rf_att_bwd_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, datt, att, maps, N, ho * k, wo * k, wa, dmaps,
                                                                        dwa));
   LY_LAUNCH_CHECK();
-  LY_CUDA(launch(rf_poolc_bwd_kernel, ceil_div(M * KK * V, 256), 256, 0, (cudaStream_t)st, (__nv_bfloat16*)dG, M, KK, k, V, ho, wo,
-                                                                              dmaps, amax));
+  {
+    __nv_bfloat16* dg_ = (__nv_bfloat16*)dG;
+    cudaStream_t s_ = (cudaStream_t)st;
+    const long rows = M * KK;
+    if (V <= 16) LY_CUDA(launch(rf_poolc_bwd_kernel<4>, ceil_div(rows * 4, 256), 256, 0, s_, dg_, M, KK, k, V, ho, wo, dmaps, amax));
+    else if (V <= 32) LY_CUDA(launch(rf_poolc_bwd_kernel<8>, ceil_div(rows * 8, 256), 256, 0, s_, dg_, M, KK, k, V, ho, wo, dmaps, amax));
+    else LY_CUDA(launch(rf_poolc_bwd_kernel<32>, ceil_div(rows * 32, 256), 256, 0, s_, dg_, M, KK, k, V, ho, wo, dmaps, amax));
+  }
   LY_LAUNCH_CHECK();
   return LY_OK;
 }
