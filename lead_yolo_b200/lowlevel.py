@@ -235,9 +235,10 @@ def reduce_blocks(m, c):
     return int(fn(m, c))
 
 
-def conv_wgrad(srcs, dz, cout, k=1, stride=1, pad=0, zeros=None):
+def conv_wgrad(srcs, dz, cout, k=1, stride=1, pad=0, zeros=None, out=None):
     """fp32 [Cout, Kp] packed weight gradient of conv(cat(srcs)) given the output gradient dz (bf16 NHWC).
-    `zeros(n)` supplies the zero-initialised accumulator (the training arena); default torch.zeros."""
+    `zeros(n)` supplies the zero-initialised accumulator (the training arena); default torch.zeros.  `out`: an already
+    ZEROED fp32 buffer of Cout*Kp elements to accumulate into instead."""
     from .packing import packed_k
     d = ConvDesc()
     keep = []
@@ -255,7 +256,10 @@ def conv_wgrad(srcs, dz, cout, k=1, stride=1, pad=0, zeros=None):
     d.Cout = cout
     dz, dld = as_nhwc(dz)
     kp = packed_k([s.shape[1] for s in srcs], k, k, patch=(stride == k and k > 1))
-    if zeros is None:
+    if out is not None:
+        assert out.numel() == cout * kp and out.dtype == torch.float32 and out.is_contiguous()
+        dw = out.view(cout, kp)
+    elif zeros is None:
         dw = torch.zeros((cout, kp), dtype=torch.float32, device=dz.device)
     else:
         dw = zeros(cout * kp, dz.device).view(cout, kp)

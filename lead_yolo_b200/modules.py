@@ -349,19 +349,18 @@ class MLPBlock(nn.Module):
             wp2 = ops.cached([w2.weight], ("wp", (w2.in_channels,)), lambda: pack_conv_weight(w2.weight, None))
             return ops.conv_infer([v], wp2, c, residual=x)
         w = w1.weight
+        if isinstance(bn, nn.BatchNorm2d) and bn.training and bn.running_mean is not None and act == "relu" and \
+                bn.momentum is not None and pc.partial_conv3.weight.dtype == torch.float32:
+            # training: the whole block as ONE autograd node (ops.MlpBlockFn)
+            y = ops.MlpBlockFn.apply(x, pc.partial_conv3.weight, w, w2.weight, bn.weight, bn.bias, bn.running_mean,
+                                     bn.running_var, float(bn.eps), float(bn.momentum), cp, cpp)
+            if bn.num_batches_tracked is not None and not ops.NBT_EXTERNAL:
+                bn.num_batches_tracked += 1
+            return y
         wa = nn.functional.pad(w[:, :cp], (0, 0, 0, 0, 0, cpp - cp))
         mask = torch.ones(c, device=w.device, dtype=w.dtype)
         mask[:cp] = 0
         wcat = torch.cat([wa, w * mask.view(1, -1, 1, 1)], 1)
-        if isinstance(bn, nn.BatchNorm2d) and bn.training and bn.running_mean is not None and act == "relu" and \
-                bn.momentum is not None and pc.partial_conv3.weight.dtype == torch.float32:
-            # training: the whole activation path as ONE autograd node (ops.MlpBlockFn)
-            wpad = nn.functional.pad(pc.partial_conv3.weight, (0, 0, 0, 0, 0, cpp - cp, 0, cpp - cp))
-            y = ops.MlpBlockFn.apply(x, wpad, wcat, w2.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var,
-                                     float(bn.eps), float(bn.momentum), cpp)
-            if bn.num_batches_tracked is not None:
-                bn.num_batches_tracked += 1
-            return y
         t1 = pc._t1(x, fast)
         u = ops.conv([t1, x], wcat, None)
         v = ops.bn_act(u, bn, act)
@@ -626,8 +625,10 @@ class RFCBAMConv(nn.Module):
         if perm is None:
             g = ops.bn_act(z, gbn, "relu")
         else:
-            rm_p, rv_p = gbn.running_mean[perm].contiguous(), gbn.running_var[perm].contiguous()
-            g = ops.bn_act(z, gbn, "relu", gamma=gbn.weight[perm], beta=gbn.bias[perm], rmean=rm_p, rvar=rv_p)
+            inv = ops.rf_channel_perm_inv(c, k, x.device)
+            rm_p, rv_p = gbn.running_mean.index_select(0, perm), gbn.running_var.index_select(0, perm)
+            g = ops.bn_act(z, gbn, "relu", gamma=ops.PermuteFn.apply(gbn.weight, perm, inv),
+                           beta=ops.PermuteFn.apply(gbn.bias, perm, inv), rmean=rm_p, rvar=rv_p)
             if gbn.training:
                 with torch.no_grad():
                     gbn.running_mean.index_copy_(0, perm, rm_p)

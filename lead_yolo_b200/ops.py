@@ -22,6 +22,26 @@ CL = torch.channels_last
 # small caches (never stored on nn.Module instances: modules stay picklable / deepcopy-able)
 # ---------------------------------------------------------------------------------------------------------
 _cache = {}
+
+# Gradient sink (set by train.TrainEngine while a step runs): data_ptr of a parameter -> its slice of the engine's flat
+# gradient buffer, ZEROED at the start of the step.  A backward that owns the whole gradient of a leaf parameter writes
+# it there and returns that tensor, so the engine has nothing to copy (one small copy kernel per parameter otherwise).
+GRAD_SINK = {}
+_SINK_USED = set()
+NBT_EXTERNAL = False   # True: the caller advances every BatchNorm's num_batches_tracked itself (one add for all of them)
+
+
+def grad_sink(param):
+    """The flat-gradient slice of `param` if this backward may write there (leaf fp32 parameter of the running
+    TrainEngine step, first and only use), else None."""
+    if not GRAD_SINK or param is None:
+        return None
+    key = param.data_ptr()
+    v = GRAD_SINK.get(key)
+    if v is None or key in _SINK_USED or not param.is_leaf or param.dtype != torch.float32 or v.shape != param.shape:
+        return None
+    _SINK_USED.add(key)
+    return v
 # A captured training step replays the SAME launches while the parameters change underneath through raw pointers, so
 # everything derived from a parameter has to be recomputed inside the step: train.TrainEngine sets this flag around
 # its forward/backward and `cached` then rebuilds whatever is keyed on a tensor that requires grad.
@@ -158,6 +178,7 @@ class ConvFn(torch.autograd.Function):
         y = ll.conv_gemm(srcs, wp, cout, k=k, stride=s, pad=pad, shift=shift, act=act, residual=res,
                          out_fp32=out_fp32)
         ctx.cfg = (k, s, act, patch, pad, chans, out_fp32, bias is not None, residual is not None)
+        ctx.bias_ref = bias
         need_y = act != "none"
         ctx.save_for_backward(weight, y if need_y else None, *srcs)
         return y
@@ -184,9 +205,10 @@ class ConvFn(torch.autograd.Function):
             dz = dzp
         d_bias = None
         if has_bias and ctx.needs_input_grad[1]:
-            sums = zeros_f32(cpad, dz.device)
+            sink = grad_sink(ctx.bias_ref) if cpad == cout else None
+            sums = sink if sink is not None else zeros_f32(cpad, dz.device)
             ll.call("ly_col_stats", dz, ll.pixel_ld(dz), _rows(dz), cpad, sums, None)
-            d_bias = sums[:cout]
+            d_bias = sums[:cout] if sink is None else sink
         cin = sum(chans)
         d_srcs = []
         off = 0
@@ -204,14 +226,7 @@ class ConvFn(torch.autograd.Function):
             off += cs
         d_w = None
         if ctx.needs_input_grad[0]:
-            dwp = ll.conv_wgrad(srcs, dz, cpad, k=k, stride=s, pad=pad, zeros=zeros_f32)
-            if weight.dtype == torch.float32 and len(chans) == 1 and k == 1 and chans[0] % 64 == 0 and cpad == cout:
-                d_w = dwp.view(weight.shape)                     # packed == OIHW: nothing to unpack
-            else:
-                d_w = torch.empty(weight.shape, dtype=torch.float32, device=dz.device)
-                c4 = list(chans) + [0] * (4 - len(chans))
-                ll.call("ly_unpack_wgrad", dwp, cout, k, k, 1 if patch else 0, c4[0], c4[1], c4[2], c4[3], d_w, 0)
-                d_w = d_w.to(weight.dtype)
+            d_w = _wgrad_oihw(srcs, dz, weight, chans, k, s, pad, patch)
         return (d_w, d_bias, d_res, None, None, None, None, *d_srcs)
 
 
@@ -260,6 +275,7 @@ class BnActFn(torch.autograd.Function):
             ll.call("ly_scale_shift_act", z, ll.pixel_ld(z), m, c, stats[2], stats[3], ll.ACT[act], y,
                     ll.pixel_ld(y))
         ctx.cfg = (act, training)
+        ctx.affine = (gamma, beta)
         ctx.save_for_backward(z, stats)
         return y
 
@@ -270,12 +286,22 @@ class BnActFn(torch.autograd.Function):
         dy = to_act(dy)
         c = z.shape[1]
         m = _rows(z)
-        s12 = torch.empty((2, c), dtype=torch.float32, device=z.device)
+        d_beta, d_gamma = _bn_grad_buffers(ctx.affine[0], ctx.affine[1], c, z.device)
         parts = torch.empty(ll.reduce_blocks(m, c) * 2 * c, dtype=torch.float32, device=z.device)
         dz = torch.empty_like(z, memory_format=CL)
         ll.call("ly_bn_act_bwd", dy, ll.pixel_ld(dy), z, ll.pixel_ld(z), m, c, stats[2], stats[3], stats[0],
-                stats[1], ll.ACT[act], 1 if training else 0, s12[0], s12[1], parts, dz, ll.pixel_ld(dz))
-        return dz, s12[1], s12[0], None, None, None, None, None, None
+                stats[1], ll.ACT[act], 1 if training else 0, d_beta, d_gamma, parts, dz, ll.pixel_ld(dz))
+        return dz, d_gamma, d_beta, None, None, None, None, None, None
+
+
+def _bn_grad_buffers(gamma, beta, c, device):
+    """(d_beta, d_gamma) fp32 [c] for ly_bn_act_bwd: the parameters' gradient sinks when there are any."""
+    sb, sg = grad_sink(beta), grad_sink(gamma)
+    if sb is None or sg is None:
+        s12 = torch.empty((2, c), dtype=torch.float32, device=device)
+        sb = s12[0] if sb is None else sb
+        sg = s12[1] if sg is None else sg
+    return sb, sg
 
 
 def bn_act(z, bn, act="none", gamma=None, beta=None, rmean=None, rvar=None):
@@ -291,7 +317,7 @@ def bn_act(z, bn, act="none", gamma=None, beta=None, rmean=None, rvar=None):
         raise ll.LeadYoloError("BatchNorm2d(momentum=None) (cumulative average) has no kernel in lead_yolo_b200")
     mom = bn.momentum
     y = BnActFn.apply(z, gamma, beta, rmean, rvar, float(bn.eps), float(mom), act, training)
-    if training and bn.num_batches_tracked is not None:
+    if training and bn.num_batches_tracked is not None and not NBT_EXTERNAL:
         bn.num_batches_tracked += 1
     return y
 
@@ -526,6 +552,29 @@ def rf_channel_perm(c, k, device):
     return hit
 
 
+def rf_channel_perm_inv(c, k, device):
+    """inverse of rf_channel_perm: reference channel (ch*k*k + t) <- G-column (t*c + ch)."""
+    key = ("rfperminv", c, k, str(device))
+    hit = _cache.get(key)
+    if hit is None:
+        hit = _cache[key] = torch.argsort(rf_channel_perm(c, k, device))
+    return hit
+
+
+class PermuteFn(torch.autograd.Function):
+    """y = x[perm] for a PERMUTATION of dim 0; the gradient is a gather with the inverse permutation (torch's index
+    backward is an index_put with accumulation: a sort and an atomic scatter per call)."""
+
+    @staticmethod
+    def forward(ctx, x, perm, inv):
+        ctx.inv = inv
+        return x.index_select(0, perm)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return dy.index_select(0, ctx.inv), None, None
+
+
 RF_GENERATE_CUDA_CORES = bool(os.environ.get("LY_RF_GENERATE_CUDA"))   # dev knob: fp32 CUDA-core feature generation
 
 
@@ -621,19 +670,25 @@ class RfFrontFn(torch.autograd.Function):
 
 
 class MlpBlockFn(torch.autograd.Function):
-    """FasterNet block body on the activation path (models/common.py:1432-1437, 1478-1482):
-        t1 = conv3x3(x[:, :cpp], Wp);  u = W1 [t1 | x];  v = relu(BN(u));  y = x + W2 v
-    with every weight-side tensor prepared by the caller under autograd (wp = partial conv padded to the 8-aligned
-    slice, wcat = [W1[:, :cp] padded | W1 with its first cp columns zeroed]).  One node instead of a chain: x gets ONE
-    gradient, written in NHWC — the slice, the two convolutions reading x and the residual would otherwise be summed by
-    autograd through a zero-filled NCHW tensor and two extra adds."""
+    """FasterNet block body (models/common.py:1432-1437, 1478-1482) as ONE autograd node:
+        t1 = conv3x3(x[:, :cpp], Wp);  u = W1cat [t1 | x];  v = relu(BN(u));  y = x + W2 v
+    Wp = the partial conv's weight zero-padded to the 8-aligned slice (cp -> cpp channels), W1cat = [W1[:, :cp] padded |
+    W1 with its first cp columns zeroed]; both are built here from the raw parameters and their gradients are folded
+    back here, so autograd sees neither the padding nor the slicing (a zero fill, a copy and an add per slice otherwise).
+    x gets ONE gradient, written in NHWC — the slice, the two convolutions reading x and the residual would otherwise be
+    summed by autograd through a zero-filled NCHW tensor and two extra adds."""
 
     @staticmethod
-    def forward(ctx, x, wp, wcat, w2, gamma, beta, rmean, rvar, eps, momentum, cpp):
+    def forward(ctx, x, wpc, w1, w2, gamma, beta, rmean, rvar, eps, momentum, cp, cpp):
         x = to_act(x)
         n, c, h, w = x.shape
         m = n * h * w
-        hid = wcat.shape[0]
+        hid = w1.shape[0]
+        with torch.no_grad():
+            wp = torch.nn.functional.pad(wpc, (0, 0, 0, 0, 0, cpp - cp, 0, cpp - cp))
+            wcat = torch.zeros((hid, cpp + c, 1, 1), dtype=w1.dtype, device=w1.device)
+            wcat[:, :cp] = w1[:, :cp]
+            wcat[:, cpp + cp:] = w1[:, cp:]
         xs = x[:, :cpp]
         t1 = ll.conv_gemm([xs], packed_weight(wp, [cpp], 3, False), cpp, k=3, stride=1, pad=1)
         u = ll.conv_gemm([t1, x], packed_weight(wcat, [cpp, c], 1, False), hid)
@@ -647,13 +702,15 @@ class MlpBlockFn(torch.autograd.Function):
             torch.autograd.graph.increment_version(t)
         y = ll.conv_gemm([v], packed_weight(w2, [hid], 1, False), c, residual=x)
         ctx.save_for_backward(x, t1, u, v, stats, wp, wcat, w2)
-        ctx.cpp = cpp
+        ctx.cfg = (cp, cpp)
+        ctx.params = (wpc, w1, gamma, beta)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, t1, u, v, stats, wp, wcat, w2 = ctx.saved_tensors
-        cpp = ctx.cpp
+        cp, cpp = ctx.cfg
+        wpc, w1, gamma, beta = ctx.params
         dy = to_act(dy)
         n, c, h, w = x.shape
         m = n * h * w
@@ -663,34 +720,48 @@ class MlpBlockFn(torch.autograd.Function):
         dv = ll.conv_gemm([dy], packed_weight_dgrad(w2, c, hid, 1, False, 0, hid), hid)
         d_w2 = _wgrad_oihw([v], dy, w2, [hid], 1, 1, 0, False)
         # BatchNorm + ReLU
-        s12 = torch.empty((2, hid), dtype=torch.float32, device=dev)
+        d_beta, d_gamma = _bn_grad_buffers(gamma, beta, hid, dev)
         parts = torch.empty(ll.reduce_blocks(m, hid) * 2 * hid, dtype=torch.float32, device=dev)
         du = torch.empty_like(u, memory_format=CL)
         ll.call("ly_bn_act_bwd", dv, ll.pixel_ld(dv), u, ll.pixel_ld(u), m, hid, stats[2], stats[3], stats[0], stats[1],
-                ll.ACT["relu"], 1, s12[0], s12[1], parts, du, ll.pixel_ld(du))
+                ll.ACT["relu"], 1, d_beta, d_gamma, parts, du, ll.pixel_ld(du))
         # mlp.0: gradient of the x source lands on top of the residual gradient; t1 source separately
         dx = ll.conv_gemm([du], packed_weight_dgrad(wcat, hid, cpp + c, 1, False, cpp, c), c, residual=dy)
         dt1 = ll.conv_gemm([du], packed_weight_dgrad(wcat, hid, cpp + c, 1, False, 0, cpp), cpp)
         d_wcat = _wgrad_oihw([t1, x], du, wcat, [cpp, c], 1, 1, 0, False)
+        # W1 = [columns 0..cp of the t1 half | columns cp.. of the x half]
+        d_w1 = grad_sink(w1)
+        if d_w1 is None:
+            d_w1 = torch.empty(w1.shape, dtype=d_wcat.dtype, device=dev)
+        torch.cat([d_wcat[:, :cp], d_wcat[:, cpp + cp:]], 1, out=d_w1)
         # partial conv: accumulate into the first cpp channels of dx in place
         dxs = dx[:, :cpp]
         ll.conv_gemm([dt1], packed_weight_dgrad(wp, cpp, cpp, 3, False, 0, cpp), cpp, k=3, stride=1, pad=1, residual=dxs,
                      out=dxs)
         d_wp = _wgrad_oihw([x[:, :cpp]], dt1, wp, [cpp], 3, 1, 1, False)
-        return dx, d_wp, d_wcat, d_w2, s12[1], s12[0], None, None, None, None, None
+        d_wpc = grad_sink(wpc)
+        if d_wpc is None:
+            d_wpc = d_wp[:cp, :cp].contiguous()
+        else:
+            d_wpc.copy_(d_wp[:cp, :cp])
+        return dx, d_wpc, d_w1, d_w2, d_gamma, d_beta, None, None, None, None, None, None
 
 
 def _wgrad_oihw(srcs, dz, weight, chans, k, s, pad, patch):
-    """fp32 OIHW weight gradient of conv(cat(srcs), weight) given dz (the tail of ConvFn.backward)."""
+    """fp32 OIHW weight gradient of conv(cat(srcs), weight) given dz (the tail of ConvFn.backward); lands in the
+    gradient sink of `weight` when there is one."""
     cout = weight.shape[0]
     cpad = (cout + 7) // 8 * 8
-    dwp = ll.conv_wgrad(srcs, dz, cpad, k=k, stride=s, pad=pad, zeros=zeros_f32)
+    sink = grad_sink(weight)
     if len(chans) == 1 and k == 1 and chans[0] % 64 == 0 and cpad == cout:
-        return dwp.view(weight.shape).to(weight.dtype)
-    d_w = torch.empty(weight.shape, dtype=torch.float32, device=dz.device)
+        # packed == OIHW: the kernel accumulates straight into the (zeroed) sink, nothing to unpack
+        dwp = ll.conv_wgrad(srcs, dz, cpad, k=k, stride=s, pad=pad, zeros=zeros_f32, out=sink)
+        return dwp.view(weight.shape) if sink is not None else dwp.view(weight.shape).to(weight.dtype)
+    dwp = ll.conv_wgrad(srcs, dz, cpad, k=k, stride=s, pad=pad, zeros=zeros_f32)
+    d_w = sink if sink is not None else torch.empty(weight.shape, dtype=torch.float32, device=dz.device)
     c4 = list(chans) + [0] * (4 - len(chans))
     ll.call("ly_unpack_wgrad", dwp, cout, k, k, 1 if patch else 0, c4[0], c4[1], c4[2], c4[3], d_w, 0)
-    return d_w.to(weight.dtype)
+    return d_w if sink is not None else d_w.to(weight.dtype)
 
 
 RF_GATE_PARTS = 16   # LY_RF_GATE_PARTS of include/leadyolo.h

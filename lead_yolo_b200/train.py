@@ -116,6 +116,15 @@ class TrainEngine:
         self.ema_buf = self.flat_buf.clone() if self.flat_buf is not None else None
         for p, gv in zip(self.params, self.grad_views):
             p.grad = gv
+        # backward kernels write parameter gradients straight into their flat slice where they can (ops.grad_sink)
+        self._sink = {p.data_ptr(): gv for p, gv in zip(self.params, self.grad_views)}
+        # every BatchNorm's num_batches_tracked in one int64 buffer: one add per step instead of one per layer
+        self.nbt = [b for b in model.buffers() if b.dtype == torch.int64 and b.numel() == 1]
+        if self.nbt:
+            self.nbt_flat = torch.zeros(len(self.nbt), dtype=torch.int64, device=self.device)
+            for i, b in enumerate(self.nbt):
+                self.nbt_flat[i] = b.reshape(())
+                b.data = self.nbt_flat[i].view(b.shape)
 
         # ---- device-resident hyper-parameters and static inputs
         h = self.hyp
@@ -140,16 +149,32 @@ class TrainEngine:
     # -- the step, as enqueued work
     def _forward_backward(self):
         ops.arena_begin(self.device)
+        self.flat_grad.zero_()            # gradient sinks accumulate (weight-gradient atomics land there directly)
         ops.BYPASS_PARAM_CACHE = True     # replayed launches must re-derive everything that depends on a parameter
+        ops.GRAD_SINK = self._sink
+        ops._SINK_USED.clear()
+        ops.NBT_EXTERNAL = bool(self.nbt)
         try:
             raw = self.model(self.images)
+            if self.nbt:
+                self.nbt_flat.add_(1)
             loss, _ = self.compute_loss(raw, self.targets)
             total = loss * float(self.world)                      # train.py:321-322
             grads = torch.autograd.grad(total, self.params, allow_unused=False)
         finally:
             ops.BYPASS_PARAM_CACHE = False
+            ops.GRAD_SINK = {}
+            ops.NBT_EXTERNAL = False
             ops.arena_end()
-        torch._foreach_copy_(self.grad_views, list(grads))
+        # whatever did not go through a sink is copied into its slice
+        dst, src = [], []
+        for gv, g in zip(self.grad_views, grads):
+            if g.data_ptr() != gv.data_ptr():
+                dst.append(gv)
+                src.append(g)
+        if dst:
+            torch._foreach_copy_(dst, src)
+        self.sunk = len(self.grad_views) - len(dst)
         return loss.detach()
 
     def _optimizer(self):
