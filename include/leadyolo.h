@@ -102,11 +102,13 @@ int ly_scale_shift_act(const void* x, long ldx, long M, int C, const float* scal
  * parts == NULL: the sums are ADDED into s1/s2 with float atomics (zero them first; order-dependent rounding).
  * parts != NULL: fp32 scratch [ly_reduce_blocks(M, C)][2*C]; every block stores its partial sums and a small second
  * launch adds them in block order into s1/s2 (written, no zeroing needed) — bit-reproducible, which matters because
- * s1/n and s2/n are subtracted from EVERY element of dz. */
+ * s1/n and s2/n are subtracted from EVERY element of dz.
+ * sync != NULL (with parts): two ZEROED 32-bit words; for large tensors (>= 48 Mi elements) the three phases then run as
+ * ONE cooperatively launched kernel separated by grid barriers (same arithmetic, same order); NULL keeps the launches. */
 int ly_reduce_blocks(long M, int C);
 int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz, long M, int C, const float* scale,
                   const float* shift, const float* mean, const float* rstd, int act, int training, float* s1,
-                  float* s2, float* parts, void* dz, long lddz, ly_stream_t stream);
+                  float* s2, float* parts, unsigned* sync, void* dz, long lddz, ly_stream_t stream);
 /* dz = dy * act'(.) with the derivative taken from the activation OUTPUT y (none / relu / sigmoid). */
 int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, long ldy, long M, int C, int act, void* dz,
                         long lddz, ly_stream_t stream);
@@ -123,6 +125,7 @@ int ly_bn_stats(const void* x, long ld, long M, int C, float* acc, ly_stream_t s
 int ly_bn_apply_train(const void* z, long ldz, long M, int C, const float* acc, const float* gamma, const float* beta,
                       float eps, float momentum, float* running_mean, float* running_var, float* stats, int act,
                       void* y, long ldy, ly_stream_t stream);
+
 
 /* ------------------------------------------------------------------------------------------------------
  * Weight layouts of the training path.  nn.Conv2d keeps fp32 OIHW parameters (optimizer, EMA, DDP and checkpoints

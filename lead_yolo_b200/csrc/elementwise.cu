@@ -5,6 +5,8 @@
 // The launch makes (gridDim.x * blockDim.x) a multiple of V = C/8, so every thread keeps ONE fixed channel
 // vector (its scale/shift/mean live in registers) while consecutive threads touch consecutive vectors
 // (fully coalesced).  HBM-bound: algorithmic bytes = each operand read or written once.
+#include <stdlib.h>
+
 #include "ly_common.cuh"
 
 namespace ly {
@@ -396,33 +398,6 @@ extern "C" int ly_reduce_blocks(long M, int C) {
   return flat_grid_reduce(M, C / 8, 256);
 }
 
-extern "C" int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz, long M, int C, const float* scale,
-                             const float* shift, const float* mean, const float* rstd, int act, int training,
-                             float* s1, float* s2, float* parts, void* dz, long lddz, ly_stream_t st) {
-  int rc = check_mat(dy, lddy, M, C, "ly_bn_act_bwd(dy)");
-  if (rc) return rc;
-  rc = check_mat(z, ldz, M, C, "ly_bn_act_bwd(z)");
-  if (rc) return rc;
-  rc = check_mat(dz, lddz, M, C, "ly_bn_act_bwd(dz)");
-  if (rc) return rc;
-  LY_REQUIRE(scale && shift && mean && rstd && s1 && s2, "ly_bn_act_bwd: null statistics");
-  const int V = C / 8;
-  const int grid = flat_grid(M, V, 256);
-  const int rgrid = flat_grid_reduce(M, V, 256);
-  LY_CUDA(launch(bn_act_bwd_reduce_kernel, rgrid, 256, 0, (cudaStream_t)st, 
-      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2, parts));
-  LY_LAUNCH_CHECK();
-  if (parts != nullptr) {
-    LY_CUDA(launch(ordered_finalize_kernel, ceil_div(2L * C * 32, 256), 256, 0, (cudaStream_t)st, parts, rgrid, C, s1, s2));
-    LY_LAUNCH_CHECK();
-  }
-  LY_CUDA(launch(bn_act_bwd_apply_kernel, grid, 256, 0, (cudaStream_t)st, 
-      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2,
-      1.f / (float)M, training, (__nv_bfloat16*)dz, lddz));
-  LY_LAUNCH_CHECK();
-  return LY_OK;
-}
-
 extern "C" int ly_act_bwd_from_out(const void* dy, long lddy, const void* y, long ldy, long M, int C, int act,
                                    void* dz, long lddz, ly_stream_t st) {
   int rc = check_mat(dy, lddy, M, C, "ly_act_bwd_from_out(dy)");
@@ -561,6 +536,157 @@ __global__ void __launch_bounds__(256) bn_apply_train_kernel(
   for (; row < M; row += rstep) apply(row, ld16(z + row * ldz + v * 8));
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// Training-mode BatchNorm BACKWARD of a large tensor as ONE kernel: reduce | grid barrier | ordered finalize | grid
+// barrier | apply.  The grid is launched cooperatively (all blocks co-resident); the barrier is an arrival counter in
+// zeroed memory, bounded like every wait in this library.  What a later phase reads that an earlier phase of the SAME
+// kernel wrote goes through __ldcg (L2), never through the read-only path.
+// Measured (tests/dev/bn_time.py, in a replayed graph): the fused kernel wins 8-15 % from 50 M elements up (349 -> 299 us
+// at 118 M) and loses ~5 us per layer below (two barriers, no programmatic overlap with its neighbours, a smaller grid);
+// the same fusion of the FORWARD pair (statistics | barrier | normalise) lost at every size and was removed.
+// ------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void grid_barrier(unsigned* counter) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(counter, 1u);
+    const long long t0 = clock64();
+    unsigned seen;
+    do {
+      asm volatile("ld.acquire.gpu.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
+      if (seen >= gridDim.x) break;
+      __nanosleep(32);
+      if (clock64() - t0 > 4000000000LL) __trap();   // a grid that is not co-resident must not hang the GPU
+    } while (true);
+  }
+  __syncthreads();
+}
+
+// sync: two zeroed barrier counters.  parts: [gridDim.x][2*C] block partials (ordered sum -> s1, s2).
+__global__ void __launch_bounds__(256, 2) bn_bwd_fused_kernel(
+    const __nv_bfloat16* __restrict__ dy, long lddy, const __nv_bfloat16* __restrict__ z, long ldz, long M, int V,
+    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
+    const float* __restrict__ rstd, int act, int training, float* s1, float* s2, float* parts, unsigned* sync,
+    __nv_bfloat16* __restrict__ dz, long lddz) {
+  pdl_enter();
+  const int C = V * 8;
+  LY_FLAT_SETUP(V)
+  float sc[8], sh[8], mu[8], rs[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale[v * 8 + j]; sh[j] = shift[v * 8 + j];
+    mu[j] = mean[v * 8 + j]; rs[j] = rstd[v * 8 + j];
+  }
+  {   // ---- phase 1: Σ d, Σ d·x̂ per block (bn_act_bwd_reduce_kernel)
+    float a1[8], a2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a1[j] = a2[j] = 0.f;
+    auto accum = [&](const uint4& ug, const uint4& uf) {
+      float g[8], f[8];
+      unpack8(ug, g);
+      unpack8(uf, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = g[j] * act_grad(fmaf(f[j], sc[j], sh[j]), act);
+        a1[j] += d;
+        a2[j] = fmaf(d, (f[j] - mu[j]) * rs[j], a2[j]);
+      }
+    };
+    long row = row0;
+    for (; row + 3 * rstep < M; row += 4 * rstep) {
+      uint4 ug[4], uf[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        ug[i] = ld16(dy + (row + i * rstep) * lddy + v * 8);
+        uf[i] = ld16(z + (row + i * rstep) * ldz + v * 8);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) accum(ug[i], uf[i]);
+    }
+    for (; row < M; row += rstep) accum(ld16(dy + row * lddy + v * 8), ld16(z + row * ldz + v * 8));
+    block_channel_reduce(a1, a2, V, (long)blockIdx.x * blockDim.x, nullptr, nullptr, parts);
+  }
+  grid_barrier(sync);
+  {   // ---- phase 2: ordered sum of the block partials, one warp per output (ordered_finalize_kernel)
+    const int lane = threadIdx.x & 31;
+    const int B = (int)gridDim.x;
+    for (int i = (int)blockIdx.x * 8 + (threadIdx.x >> 5); i < 2 * C; i += B * 8) {
+      float a = 0.f;
+      for (int b = lane; b < B; b += 32) a += __ldcg(parts + (long)b * 2 * C + i);
+      a = warp_sum(a);
+      if (lane == 0) {
+        if (i < C) s1[i] = a;
+        else s2[i - C] = a;
+      }
+    }
+  }
+  grid_barrier(sync + 1);
+  // ---- phase 3: dz (bn_act_bwd_apply_kernel)
+  const float inv_n = 1.f / (float)M;
+  float m1[8], m2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    m1[j] = training ? __ldcg(s1 + v * 8 + j) * inv_n : 0.f;
+    m2[j] = training ? __ldcg(s2 + v * 8 + j) * inv_n : 0.f;
+  }
+  auto apply = [&](long row, const uint4& ug, const uint4& uf) {
+    float g[8], f[8];
+    unpack8(ug, g);
+    unpack8(uf, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = g[j] * act_grad(fmaf(f[j], sc[j], sh[j]), act);
+      const float xh = (f[j] - mu[j]) * rs[j];
+      f[j] = sc[j] * (d - m1[j] - xh * m2[j]);
+    }
+    st16(dz + row * lddz + v * 8, pack8(f));
+  };
+  long row = row0;
+  for (; row + rstep < M; row += 2 * rstep) {
+    const uint4 g0 = ld16(dy + row * lddy + v * 8), f0 = ld16(z + row * ldz + v * 8);
+    const uint4 g1 = ld16(dy + (row + rstep) * lddy + v * 8), f1 = ld16(z + (row + rstep) * ldz + v * 8);
+    apply(row, g0, f0);
+    apply(row + rstep, g1, f1);
+  }
+  if (row < M) apply(row, ld16(dy + row * lddy + v * 8), ld16(z + row * ldz + v * 8));
+}
+
+// Cooperative launch: every block of the grid is resident at once (the launch fails otherwise), which is what the
+// grid barrier needs.  `blocks_per_sm` of the kernel is queried once per device.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_coop(void (*kernel)(KArgs...), int grid, int block, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
+}
+
+template <typename K>
+static int coop_capacity(K kernel, int block) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, 0) != cudaSuccess || per_sm < 1) return 0;
+  return per_sm * device_sm_count();
+}
+
+// largest grid <= cap that keeps the (row, channel-vector) mapping of LY_FLAT_SETUP consistent (multiple of V / gcd)
+static int fused_grid(long M, int V, int cap) {
+  const int m = V / gcd_i(V, 256);
+  long want = flat_grid_reduce(M, V, 256);
+  if (want > cap) want = cap / m * m;
+  return (int)want;
+}
+
+static const bool g_bn_unfused = getenv("LY_BN_UNFUSED") != nullptr;   // dev knob: the separate kernels
+constexpr long kBnFuseMin = 48L << 20;                                  // elements from which the fused backward wins
+
 }  // namespace ly
 
 extern "C" int ly_bn_stats(const void* x, long ld, long M, int C, float* acc, ly_stream_t st) {
@@ -587,6 +713,45 @@ extern "C" int ly_bn_apply_train(const void* z, long ldz, long M, int C, const f
   LY_CUDA(launch(bn_apply_train_kernel, flat_grid(M, V, 256), 256, 0, (cudaStream_t)st, 
       (const __nv_bfloat16*)z, ldz, M, V, acc, gamma, beta, eps, momentum, running_mean, running_var, stats, act,
       (__nv_bfloat16*)y, ldy));
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_bn_act_bwd(const void* dy, long lddy, const void* z, long ldz, long M, int C, const float* scale,
+                             const float* shift, const float* mean, const float* rstd, int act, int training,
+                             float* s1, float* s2, float* parts, unsigned* sync, void* dz, long lddz, ly_stream_t st) {
+  int rc = check_mat(dy, lddy, M, C, "ly_bn_act_bwd(dy)");
+  if (rc) return rc;
+  rc = check_mat(z, ldz, M, C, "ly_bn_act_bwd(z)");
+  if (rc) return rc;
+  rc = check_mat(dz, lddz, M, C, "ly_bn_act_bwd(dz)");
+  if (rc) return rc;
+  LY_REQUIRE(scale && shift && mean && rstd && s1 && s2, "ly_bn_act_bwd: null statistics");
+  const int V = C / 8;
+  if (parts != nullptr && sync != nullptr && !g_bn_unfused && M * (long)C >= kBnFuseMin) {
+    // one cooperative kernel: reduce | grid barrier | ordered finalize | grid barrier | apply
+    static const int cap = coop_capacity(bn_bwd_fused_kernel, 256);
+    const int fg = fused_grid(M, V, cap);
+    if (fg >= 1) {
+      LY_CUDA(launch_coop(bn_bwd_fused_kernel, fg, 256, (cudaStream_t)st, (const __nv_bfloat16*)dy, lddy,
+                          (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, training, s1, s2, parts, sync,
+                          (__nv_bfloat16*)dz, lddz));
+      LY_LAUNCH_CHECK();
+      return LY_OK;
+    }
+  }
+  const int grid = flat_grid(M, V, 256);
+  const int rgrid = flat_grid_reduce(M, V, 256);
+  LY_CUDA(launch(bn_act_bwd_reduce_kernel, rgrid, 256, 0, (cudaStream_t)st, 
+      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2, parts));
+  LY_LAUNCH_CHECK();
+  if (parts != nullptr) {
+    LY_CUDA(launch(ordered_finalize_kernel, ceil_div(2L * C * 32, 256), 256, 0, (cudaStream_t)st, parts, rgrid, C, s1, s2));
+    LY_LAUNCH_CHECK();
+  }
+  LY_CUDA(launch(bn_act_bwd_apply_kernel, grid, 256, 0, (cudaStream_t)st, 
+      (const __nv_bfloat16*)dy, lddy, (const __nv_bfloat16*)z, ldz, M, V, scale, shift, mean, rstd, act, s1, s2,
+      1.f / (float)M, training, (__nv_bfloat16*)dz, lddz));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

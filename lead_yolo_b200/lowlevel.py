@@ -149,7 +149,7 @@ _SIGS = {
     "ly_bn_finalize": "ppilffpppppppp",
     "ly_bn_fold": "ifppppppppp",
     "ly_scale_shift_act": "pllippipl",
-    "ly_bn_act_bwd": "plpllippppiippppl",
+    "ly_bn_act_bwd": "plpllippppiipppppl",
     "ly_bn_stats": "pllip",
     "ly_bn_apply_train": "pllipppffpppipl",
     "ly_pack_weight": "piiiiiiiip",

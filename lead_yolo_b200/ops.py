@@ -290,7 +290,8 @@ class BnActFn(torch.autograd.Function):
         parts = torch.empty(ll.reduce_blocks(m, c) * 2 * c, dtype=torch.float32, device=z.device)
         dz = torch.empty_like(z, memory_format=CL)
         ll.call("ly_bn_act_bwd", dy, ll.pixel_ld(dy), z, ll.pixel_ld(z), m, c, stats[2], stats[3], stats[0],
-                stats[1], ll.ACT[act], 1 if training else 0, d_beta, d_gamma, parts, dz, ll.pixel_ld(dz))
+                stats[1], ll.ACT[act], 1 if training else 0, d_beta, d_gamma, parts, zeros_f32(2, z.device), dz,
+                ll.pixel_ld(dz))
         return dz, d_gamma, d_beta, None, None, None, None, None, None
 
 
@@ -724,7 +725,7 @@ class MlpBlockFn(torch.autograd.Function):
         parts = torch.empty(ll.reduce_blocks(m, hid) * 2 * hid, dtype=torch.float32, device=dev)
         du = torch.empty_like(u, memory_format=CL)
         ll.call("ly_bn_act_bwd", dv, ll.pixel_ld(dv), u, ll.pixel_ld(u), m, hid, stats[2], stats[3], stats[0], stats[1],
-                ll.ACT["relu"], 1, d_beta, d_gamma, parts, du, ll.pixel_ld(du))
+                ll.ACT["relu"], 1, d_beta, d_gamma, parts, zeros_f32(2, dev), du, ll.pixel_ld(du))
         # mlp.0: gradient of the x source lands on top of the residual gradient; t1 source separately
         dx = ll.conv_gemm([du], packed_weight_dgrad(wcat, hid, cpp + c, 1, False, cpp, c), c, residual=dy)
         dt1 = ll.conv_gemm([du], packed_weight_dgrad(wcat, hid, cpp + c, 1, False, 0, cpp), cpp)
