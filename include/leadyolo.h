@@ -153,6 +153,10 @@ int ly_stem_fwd(const void* img, int img_is_u8, int N, int H, int W, int Cout, c
                 const float* shift, float in_scale, void* out, long ld_out, ly_stream_t stream);
 int ly_stem_wgrad(const void* img, int img_is_u8, int N, int H, int W, int Cout, const void* dz, long ld_dz,
                   float in_scale, float* dwk, ly_stream_t stream);
+/* Patch matrix of the stem: P bf16 [N*(H/4)*(W/4)][64], column c*16+ky*4+kx = img[n][c][4y+ky][4x+kx] (raw values, no
+ * in_scale; uint8 is exact in bf16), columns 48..63 zero.  With it the stem's weight gradient is ly_conv_wgrad of a 1x1
+ * convolution over P (tensor cores) instead of ly_stem_wgrad (CUDA cores): dW[o][c][ky][kx] = in_scale * dWp[o][c*16+ky*4+kx]. */
+int ly_stem_im2col(const void* img, int img_is_u8, int N, int H, int W, void* P, ly_stream_t stream);
 
 /* Fused FasterNet block, inference (models/common.py:1432-1437,1478-1482): y = x + W2 relu(scale*(W1 [pconv3x3(x[:,:C/4])
  * | x[:,C/4:]]) + shift) in ONE persistent kernel; x and y are dense NHWC bf16 [N][H][W][C], C in {24, 40, 80} (y 32-byte aligned for C = 80).  The 2C-wide

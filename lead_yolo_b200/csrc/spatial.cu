@@ -441,6 +441,48 @@ static int stem_wgrad_dispatch(const Tin* img, int N, int H, int W, int Cout, co
   return LY_OK;
 }
 
+
+// Patch matrix of the stem for its weight gradient: P bf16 [N*(H/4)*(W/4)][64], column c*16 + ky*4 + kx = the raw pixel
+// img[n][c][4y+ky][4x+kx] (uint8 values are exact in bf16), columns 48..63 zero.  The stem's weight gradient is then a
+// 1x1 convolution's: dW[o][k] = Σ_pixels dz[pixel][o] * P[pixel][k] on the tensor cores (ly_conv_wgrad) instead of
+// 48*Cout fp32 FMAs per pixel on the CUDA cores.  Four threads per patch, one per 32-byte quarter of its row.
+template <typename Tin>
+__global__ void __launch_bounds__(256) stem_im2col_kernel(const Tin* __restrict__ img, int N, int H, int W,
+                                                          __nv_bfloat16* __restrict__ P) {
+  pdl_enter();
+  const int Ho = H / 4, Wo = W / 4;
+  const long total = (long)N * Ho * Wo * 4;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int c = (int)(tid & 3);
+  const long pix = tid >> 2;
+  const int x = (int)(pix % Wo), y = (int)((pix / Wo) % Ho);
+  const long n = pix / ((long)Wo * Ho);
+  uint32_t w[8];
+  if (c == 3) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = 0u;
+  } else {
+    const Tin* base = img + ((n * 3 + c) * H + (long)y * 4) * W + (long)x * 4;
+#pragma unroll
+    for (int ky = 0; ky < 4; ++ky) {
+      float f[4];
+      if (sizeof(Tin) == 1) {
+        const uchar4 u = *reinterpret_cast<const uchar4*>(base + (long)ky * W);
+        f[0] = (float)u.x; f[1] = (float)u.y; f[2] = (float)u.z; f[3] = (float)u.w;
+      } else {
+        const float4 u = *reinterpret_cast<const float4*>(base + (long)ky * W);
+        f[0] = u.x; f[1] = u.y; f[2] = u.z; f[3] = u.w;
+      }
+      w[ky * 2] = pack_bf16x2(f[0], f[1]);
+      w[ky * 2 + 1] = pack_bf16x2(f[2], f[3]);
+    }
+  }
+  uint4* dst = reinterpret_cast<uint4*>(P + pix * 64 + c * 16);
+  dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+}
+
 }  // namespace ly
 
 namespace ly {
@@ -478,6 +520,22 @@ extern "C" int ly_stem_wgrad(const void* img, int img_is_u8, int N, int H, int W
                                         in_scale, dwk, (cudaStream_t)st);
   return stem_wgrad_dispatch<float>((const float*)img, N, H, W, Cout, (const __nv_bfloat16*)dz, ld_dz, in_scale,
                                     dwk, (cudaStream_t)st);
+}
+
+extern "C" int ly_stem_im2col(const void* img, int img_is_u8, int N, int H, int W, void* P, ly_stream_t st) {
+  LY_REQUIRE(img && P, "ly_stem_im2col: null pointer");
+  LY_REQUIRE(N > 0 && H % 4 == 0 && W % 4 == 0 && H > 0 && W > 0, "ly_stem_im2col: H,W must be multiples of 4");
+  LY_REQUIRE(reinterpret_cast<uintptr_t>(img) % 16 == 0 && reinterpret_cast<uintptr_t>(P) % 16 == 0,
+             "ly_stem_im2col: pointers must be 16-byte aligned");
+  const long total = (long)N * (H / 4) * (W / 4) * 4;
+  if (img_is_u8)
+    LY_CUDA(launch(stem_im2col_kernel<uint8_t>, ceil_div(total, 256), 256, 0, (cudaStream_t)st, (const uint8_t*)img, N, H, W,
+                   (__nv_bfloat16*)P));
+  else
+    LY_CUDA(launch(stem_im2col_kernel<float>, ceil_div(total, 256), 256, 0, (cudaStream_t)st, (const float*)img, N, H, W,
+                   (__nv_bfloat16*)P));
+  LY_LAUNCH_CHECK();
+  return LY_OK;
 }
 
 extern "C" int ly_maxpool5_fwd(const void* x, long ldx, int N, int H, int W, int C, void* y, long ldy,

@@ -161,6 +161,7 @@ _SIGS = {
     "ly_act_bwd_from_out": "plplliipl",
     "ly_stem_fwd": "piiiiipppfpl",
     "ly_stem_wgrad": "piiiiiplfp",
+    "ly_stem_im2col": "piiiip",
     "ly_fasternet_block_infer": "ppiiiipiiipp",
     "ly_maxpool5_fwd": "pliiiiplp",
     "ly_maxpool5_bwd": "plpiiiipli",

@@ -345,6 +345,9 @@ def bn_fold(bn, conv_bias=None, perm=None):
 # ---------------------------------------------------------------------------------------------------------
 # Stem
 # ---------------------------------------------------------------------------------------------------------
+STEM_WGRAD_CUDA_CORES = bool(os.environ.get("LY_STEM_WGRAD_CUDA"))   # dev knob: fp32 CUDA-core stem weight gradient
+
+
 class StemFn(torch.autograd.Function):
     """4x4/s4 patch embedding straight from the NCHW image (fp32, or uint8 with the /255 folded in)."""
 
@@ -363,6 +366,7 @@ class StemFn(torch.autograd.Function):
         in_scale = 1.0 / 255.0 if is_u8 else 1.0
         ll.call("ly_stem_fwd", img, 1 if is_u8 else 0, n, h, w, cout, wk, scale, shift, in_scale, out, cout)
         ctx.save_for_backward(img)
+        ctx.weight_ref = weight
         ctx.cfg = (is_u8, in_scale, cout, weight.dtype)
         return out
 
@@ -372,6 +376,15 @@ class StemFn(torch.autograd.Function):
         is_u8, in_scale, cout, wdt = ctx.cfg
         dz = to_act(dz)
         n, _, h, w = img.shape
+        if cout % 8 == 0 and not STEM_WGRAD_CUDA_CORES:
+            # patch matrix (bf16, exact for uint8 images) + the 1x1 weight-gradient GEMM on the tensor cores
+            pm = ll.empty_cl(n, 64, h // 4, w // 4, device=dz.device)
+            ll.call("ly_stem_im2col", img, 1 if is_u8 else 0, n, h, w, pm)
+            dwp = ll.conv_wgrad([pm], dz, cout, k=1, zeros=zeros_f32)            # [cout][64], column c*16 + ky*4 + kx
+            sink = grad_sink(ctx.weight_ref)
+            d_w = sink if sink is not None else torch.empty((cout, 3, 4, 4), dtype=torch.float32, device=dz.device)
+            torch.mul(dwp[:, :48].reshape(cout, 3, 4, 4), in_scale, out=d_w)
+            return None, (d_w if sink is not None else d_w.to(wdt)), None, None
         dwk = zeros_f32(48 * cout, dz.device).view(48, cout)
         ll.call("ly_stem_wgrad", img, 1 if is_u8 else 0, n, h, w, cout, dz, ll.pixel_ld(dz), in_scale, dwk)
         return None, dwk.t().reshape(cout, 3, 4, 4).to(wdt), None, None
