@@ -266,6 +266,15 @@ int ly_rf_tc_apply(const void* x, long ldx, int N, int H, int W, int C, int s, i
  * the difference to ly_rf_generate's fp32 weights is below the bf16 rounding of Z).  Z 32-byte aligned. */
 int ly_rf_tc_generate(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
                       const void* shift, void* Z, ly_stream_t stream);
+/* Backward of that generation with respect to x, on the same kernel (k = 3): ly_rf_tc_taps computes the gradient of every
+ * output pixel's 3x3 input patch, R bf16 [N*ho*wo][9 (ij)][C], R[m][ij][c] = Σ_t wcT[t][ij][c] * dZ[m][t][c] (+ shift: pass
+ * zeros); wcT bf16 [C/16][9 t][9 ij][16] = the forward image with its two 9-axes swapped; dZ bf16 [N*ho*wo][9][C].
+ * ly_rf_col2im then folds the patches into dx[n,y,x,c] = Σ R[m(h,w)][ij][c] over h*s+i-1 == y, w*s+j-1 == x (+ extra[n][c],
+ * may be NULL).  Together they replace the dx half of ly_rf_generate_bwd (fp32 weights on the CUDA cores). */
+int ly_rf_tc_taps(const void* dZ, int N, int ho, int wo, int C, const void* wcT, const void* shift, void* R,
+                  ly_stream_t stream);
+int ly_rf_col2im(const void* R, int N, int H, int W, int C, int s, int ho, int wo, const float* extra, void* dx, long lddx,
+                 ly_stream_t stream);
 /* ly_rf_tc_apply fused with RFCBAMConv.conv + its BatchNorm + ReLU (models/rfa.py:121-129): the gated receptive-field
  * matrix (9*C wide) never reaches HBM — each [128 pixels][144] tile goes from the gating epilogue through shared memory
  * straight into a second tcgen05 accumulation over the channel groups.  out: bf16 NHWC [N][ho][wo][Cout] (pixel stride

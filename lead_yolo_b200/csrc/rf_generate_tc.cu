@@ -65,6 +65,8 @@ struct alignas(64) RfTcParams {
   int tiles_w, tiles_h, n_img, groups;
   int Wt, Ht, ho, wo, C, s;
   int items, per_cta;
+  int tap_slices;           // 1: the nine "taps" are the nine slices of dimension 2 of a_map[0] at the SAME pixels
+                            // (input-gradient pass: A = dZ[m][t][16 channels], t = 0..8), not spatial neighbours
   uint32_t a_bytes;
   const __nv_bfloat16* wc;  // [C/16][9 taps][144]: the diagonal values, BatchNorm scale folded in
   const uint32_t* shift;    // [C/16][144]: BatchNorm shift as two bf16 (hi | lo << 16), hi + lo = shift to 16 bits
@@ -166,7 +168,12 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
           RT_WAIT(0, &empty_bar[s], ph);
           mbar_arrive_expect_tx(&full_bar[s], 3u * p.a_bytes);
           uint8_t* dst = sA + s * 3 * kRtA;
-          if (p.s == 2) {   // input row 2h + ti - 1: parity (ti + 1) & 1, plane row h - (ti == 0)
+          if (p.tap_slices) {
+            const int row = th * p.Ht, col = tw * p.Wt;
+            tma_load_5d(dst, &p.a_map[0], &full_bar[s], c0, col, ti * 3, row, n);
+            tma_load_5d(dst + kRtA, &p.a_map[0], &full_bar[s], c0, col, ti * 3 + 1, row, n);
+            tma_load_5d(dst + 2 * kRtA, &p.a_map[0], &full_bar[s], c0, col, ti * 3 + 2, row, n);
+          } else if (p.s == 2) {   // input row 2h + ti - 1: parity (ti + 1) & 1, plane row h - (ti == 0)
             const int row = th * p.Ht - (ti == 0), col = tw * p.Wt;
             const CUtensorMap* m0 = &p.a_map[((ti + 1) & 1) * 2];
             tma_load_5d(dst, m0 + 1, &full_bar[s], c0, col - 1, 0, row, n);
@@ -833,6 +840,62 @@ static int rf_tc_launch(int mode, const void* x, long ldx, int N, int H, int W, 
   return LY_OK;
 }
 
+// Input-gradient pass of the receptive-field generation: R[m][ij][c] = Σ_t wT[t][ij][c] * dZ[m][t][c] — the same nine
+// K = 16 MMAs per item as the forward, with the nine feature slices of dZ (bf16 [N*ho*wo][9][C]) as the "taps".
+static int rf_tc_launch_taps(const void* dZ, int N, int ho, int wo, int C, const void* wc, const void* shift, void* R,
+                             cudaStream_t stream) {
+  LY_REQUIRE(dZ && wc && shift && R, "ly_rf_tc_taps: null pointer");
+  LY_REQUIRE(C % 16 == 0 && C > 0 && N > 0 && ho > 0 && wo > 0, "ly_rf_tc_taps: bad shape");
+  LY_REQUIRE(reinterpret_cast<uintptr_t>(dZ) % 16 == 0 && reinterpret_cast<uintptr_t>(R) % 32 == 0 &&
+                 reinterpret_cast<uintptr_t>(wc) % 16 == 0,
+             "ly_rf_tc_taps: alignment");
+  RfTcParams p;
+  memset(&p, 0, sizeof(p));
+  int bw = 16, bh = 8;
+  double best = -1;
+  const int cand[6] = {8, 16, 32, 64, 128, wo <= 128 ? wo : 128};
+  for (int i = 0; i < 6; ++i) {
+    const int wt = cand[i];
+    if (wt <= 0 || wt > 128) continue;
+    int ht = 128 / wt;
+    if (ht > ho) ht = ho;
+    const double eff = (double)ho * wo / ((double)ceil_div(wo, wt) * ceil_div(ho, ht) * 128.0);
+    if (eff > best + 1e-9) { best = eff; bw = wt; bh = ht; }
+  }
+  p.Wt = bw; p.Ht = bh;
+  p.tiles_w = ceil_div(wo, bw); p.tiles_h = ceil_div(ho, bh); p.n_img = N;
+  p.groups = C / 16;
+  p.ho = ho; p.wo = wo; p.C = C; p.s = 1;
+  p.tap_slices = 1;
+  p.a_bytes = (uint32_t)(16 * bw * bh * 2);
+  p.wc = (const __nv_bfloat16*)wc; p.shift = (const uint32_t*)shift; p.A = (__nv_bfloat16*)R;
+  {
+    uint64_t dims[5] = {(uint64_t)C, (uint64_t)wo, 9, (uint64_t)ho, (uint64_t)N};
+    uint64_t str[4] = {(uint64_t)9 * C * 2, (uint64_t)C * 2, (uint64_t)wo * 9 * C * 2, (uint64_t)ho * wo * 9 * C * 2};
+    uint32_t box[5] = {16, (uint32_t)bw, 1, (uint32_t)bh, 1};
+    uint32_t es[5] = {1, 1, 1, 1, 1};
+    int rc = rt_encode(&p.a_map[0], dZ, 5, dims, str, box, es);
+    if (rc) return rc;
+  }
+  const long items = (long)p.tiles_w * p.tiles_h * N * p.groups;
+  LY_REQUIRE(items < (1L << 30), "ly_rf_tc_taps: problem too large");
+  const int sms = device_sm_count();
+  p.items = (int)items;
+  p.per_cta = (int)ceil_div(items, (long)sms);
+  const unsigned grid = (unsigned)ceil_div(items, (long)p.per_cta);
+  const size_t smem0 = (size_t)6 * 3 * kRtA + kRtA + 2 * kRtB1 + 1024;
+  static std::atomic<bool> attr_done[64];
+  int dev = 0;
+  LY_CUDA(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63].load()) {
+    LY_CUDA(cudaFuncSetAttribute(rf_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem0));
+    attr_done[dev & 63].store(true);
+  }
+  LY_CUDA(launch(rf_tc_kernel<2>, grid, kRtThreads, smem0, stream, p));
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
 static int rf_fused_launch(const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo, const void* wc,
                            const void* shift, const float* se, const float* att, const void* w2, const float* scale2,
                            const float* shift2, int Cout, void* out, long ld_out, cudaStream_t stream) {
@@ -929,6 +992,14 @@ extern "C" int ly_rf_tc_generate(const void* x, long ldx, int N, int H, int W, i
                                  const void* shift, void* Z, ly_stream_t st) {
   LY_REQUIRE(Z && reinterpret_cast<uintptr_t>(Z) % 32 == 0, "ly_rf_tc_generate: null or misaligned pointer");
   return rf_tc_launch(2, x, ldx, N, H, W, C, s, ho, wo, wc, shift, nullptr, nullptr, Z, nullptr, (cudaStream_t)st);
+}
+
+// Backward of the generation with respect to its input, first half: R bf16 [N*ho*wo][9 (ij)][C],
+// R[m][ij][c] = Σ_t wcT[t][ij][c] * dZ[m][t][c] (+ shift, pass zeros): the per-output-pixel gradient of the 3x3 input patch.
+// wcT: bf16 [C/16][9 t][9 ij][16] (the forward's weight image with its two 9-axes swapped).  ly_rf_col2im folds R into dx.
+extern "C" int ly_rf_tc_taps(const void* dZ, int N, int ho, int wo, int C, const void* wcT, const void* shift, void* R,
+                             ly_stream_t st) {
+  return rf_tc_launch_taps(dZ, N, ho, wo, C, wcT, shift, R, (cudaStream_t)st);
 }
 
 // Pass 2 fused with RFCBAMConv.conv (models/rfa.py:121-129): out bf16 NHWC [N][ho][wo][Cout] = relu(scale2 * (gated

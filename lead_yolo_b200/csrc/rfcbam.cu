@@ -462,6 +462,54 @@ __global__ void __launch_bounds__(128) rf_generate_dx_kernel(const __nv_bfloat16
   *reinterpret_cast<uint4*>(dx + pix * lddx + v * 8) = pack8(acc);
 }
 
+// col2im of the patch gradients: dx[n,y,x,c] = Σ_{(i,j)} R[m(h,w)][i*3+j][c] over the (h,w) with h*s + i - 1 == y,
+// w*s + j - 1 == x (at most four terms for s = 2), plus extra[n,c].  R comes from ly_rf_tc_taps (tensor cores); this pass
+// only gathers.  One thread per (input pixel, 8-channel vector).
+template <int S>
+__global__ void __launch_bounds__(256) rf_col2im_kernel(const __nv_bfloat16* __restrict__ R, int N, int H, int W, int V,
+                                                        int ho, int wo, const float* __restrict__ extra,
+                                                        __nv_bfloat16* __restrict__ dx, long lddx) {
+  pdl_enter();
+  const int C = V * 8;
+  const long total = (long)N * H * W * V;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int v = (int)(tid % V);
+  const long pix = tid / V;
+  const int x = (int)(pix % W), y = (int)((pix / W) % H), n = (int)(pix / ((long)W * H));
+  // (i, j) contributes when y + 1 - i and x + 1 - j are non-negative multiples of S inside the output
+  uint4 u[9];
+  unsigned on = 0u;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const int hn = y + 1 - i;
+    const int h = S == 2 ? hn >> 1 : hn;
+    const bool hv = hn >= 0 && (S == 1 || (hn & 1) == 0) && h < ho;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int wn = x + 1 - j;
+      const int w = S == 2 ? wn >> 1 : wn;
+      if (hv && wn >= 0 && (S == 1 || (wn & 1) == 0) && w < wo) {
+        on |= 1u << (i * 3 + j);
+        u[i * 3 + j] = ldg16(R + ((((long)n * ho + h) * wo + w) * 9 + (i * 3 + j)) * (long)C + v * 8);
+      }
+    }
+  }
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = extra != nullptr ? __ldg(extra + (long)n * C + v * 8 + e) : 0.f;
+#pragma unroll
+  for (int q = 0; q < 9; ++q) {
+    if (on & (1u << q)) {
+      float f[8];
+      unpack8(u[q], f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += f[e];
+    }
+  }
+  *reinterpret_cast<uint4*>(dx + pix * lddx + v * 8) = pack8(acc);
+}
+
 // dwgk[t][ij][c] += Σ_m dZ[m][t*C+c] * x[n, h*s+i-k/2, w*s+j-k/2, c].
 // One thread per (8-channel vector v, feature t) and pixel lane, consecutive threads on consecutive v (every load of a
 // warp is a contiguous run of a pixel's channels); each thread keeps its k*k x 8 sums in registers over its pixels.
@@ -676,6 +724,25 @@ extern "C" int ly_rf_attention_bwd(const float* datt, const float* att, const fl
     else if (V <= 32) LY_CUDA(launch(rf_poolc_bwd_kernel<8>, ceil_div(rows * 8, 256), 256, 0, s_, dg_, M, KK, k, V, ho, wo, dmaps, amax));
     else LY_CUDA(launch(rf_poolc_bwd_kernel<32>, ceil_div(rows * 32, 256), 256, 0, s_, dg_, M, KK, k, V, ho, wo, dmaps, amax));
   }
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_rf_col2im(const void* R, int N, int H, int W, int C, int s, int ho, int wo, const float* extra, void* dx,
+                            long lddx, ly_stream_t st) {
+  LY_REQUIRE(R && dx && C % 8 == 0 && C > 0 && (s == 1 || s == 2) && N > 0, "ly_rf_col2im: bad arguments");
+  LY_REQUIRE(ho == (H + 2 - 3) / s + 1 && wo == (W + 2 - 3) / s + 1, "ly_rf_col2im: output size mismatch");
+  LY_REQUIRE(reinterpret_cast<uintptr_t>(R) % 16 == 0 && reinterpret_cast<uintptr_t>(dx) % 16 == 0 && lddx % 8 == 0 &&
+                 lddx >= C,
+             "ly_rf_col2im: alignment / ld");
+  const int V = C / 8;
+  const long total = (long)N * H * W * V;
+  if (s == 2)
+    LY_CUDA(launch(rf_col2im_kernel<2>, ceil_div(total, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)R, N, H, W, V, ho,
+                   wo, extra, (__nv_bfloat16*)dx, lddx));
+  else
+    LY_CUDA(launch(rf_col2im_kernel<1>, ceil_div(total, 256), 256, 0, (cudaStream_t)st, (const __nv_bfloat16*)R, N, H, W, V, ho,
+                   wo, extra, (__nv_bfloat16*)dx, lddx));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

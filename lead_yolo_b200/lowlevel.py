@@ -184,6 +184,8 @@ _SIGS = {
     "ly_rf_tc_stats": "pliiiiiiippp",
     "ly_rf_tc_apply": "pliiiiiiippppp",
     "ly_rf_tc_generate": "pliiiiiiippp",
+    "ly_rf_tc_taps": "piiiippp",
+    "ly_rf_col2im": "piiiiiiippl",
     "ly_rfcbam_fused_infer": "pliiiiiiipppppppipl",
     "ly_rf_gap_sum": "pliiip",
     "ly_gap_mean": "pliiipp",

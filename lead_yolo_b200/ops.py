@@ -600,14 +600,38 @@ def _rf_generate_raw(x, wgk, k, s, ho, wo):
     g = ll.empty_cl(n, k * k * c, ho, wo, device=x.device)
     if k == 3 and c % 16 == 0 and not RF_GENERATE_CUDA_CORES:
         wc = wgk.view(9, 9, c // 16, 16).permute(2, 1, 0, 3).reshape(c // 16, 1296).to(BF16).contiguous()
-        key = ("rfzero", c, x.device)
-        zero = _cache.get(key)
-        if zero is None:
-            zero = _cache[key] = torch.zeros((c // 16, 144), dtype=torch.int32, device=x.device)
-        ll.call("ly_rf_tc_generate", x, ll.pixel_ld(x), n, h, w, c, s, ho, wo, wc, zero, g)
+        ll.call("ly_rf_tc_generate", x, ll.pixel_ld(x), n, h, w, c, s, ho, wo, wc, _rf_zero_shift(c, x.device), g)
     else:
         ll.call("ly_rf_generate", x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, None, ll.ACT["none"], g)
     return g
+
+
+def _rf_zero_shift(c, device):
+    key = ("rfzero", c, device)
+    zero = _cache.get(key)
+    if zero is None:
+        zero = _cache[key] = torch.zeros((c // 16, 144), dtype=torch.int32, device=device)
+    return zero
+
+
+def _rf_generate_bwd(dz, x, wgk, k, s, ho, wo, extra, need_dx, need_dw):
+    """(dx, dwgk) of the receptive-field generation.  k = 3 with C % 16 == 0: the input gradient runs on the tensor cores
+    (ly_rf_tc_taps: patch gradients, ly_rf_col2im: fold), the weight gradient on ly_rf_generate_bwd; otherwise both there."""
+    n, c, h, w = x.shape
+    dev = x.device
+    dx = ll.empty_cl(n, c, h, w, device=dev) if need_dx else None
+    tc = need_dx and k == 3 and c % 16 == 0 and not RF_GENERATE_CUDA_CORES
+    if tc:
+        wct = wgk.view(9, 9, c // 16, 16).permute(2, 0, 1, 3).reshape(c // 16, 1296).to(BF16).contiguous()
+        r = ll.empty_cl(n, 9 * c, ho, wo, device=dev)
+        ll.call("ly_rf_tc_taps", dz, n, ho, wo, c, wct, _rf_zero_shift(c, dev), r)
+        ll.call("ly_rf_col2im", r, n, h, w, c, s, ho, wo, extra, dx, c)
+    dwgk = zeros_f32(wgk.numel(), dev).view(wgk.shape) if need_dw else None
+    if dwgk is not None or (need_dx and not tc):
+        scr = ll.rf_wgrad_scratch(c, k, dev) if dwgk is not None else None
+        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, extra, None if tc else dx, c,
+                dwgk, scr, 0 if scr is None else scr.numel())
+    return dx, dwgk
 
 
 class RfGenerateFn(torch.autograd.Function):
@@ -635,11 +659,7 @@ class RfGenerateFn(torch.autograd.Function):
         assert not fused, "fused affine epilogue is inference-only"
         dz = to_act(dz).contiguous(memory_format=CL)
         n, c, h, w = x.shape
-        dx = ll.empty_cl(n, c, h, w, device=x.device) if ctx.needs_input_grad[0] else None
-        dwgk = zeros_f32(wgk.numel(), wgk.device).view(wgk.shape) if ctx.needs_input_grad[1] else None
-        scr = ll.rf_wgrad_scratch(c, k, x.device) if dwgk is not None else None
-        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, None, dx, c, dwgk, scr,
-                0 if scr is None else scr.numel())
+        dx, dwgk = _rf_generate_bwd(dz, x, wgk, k, s, ho, wo, None, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
         dwg = None
         if dwgk is not None:
             dwg = dwgk.permute(2, 0, 1).reshape(c * k * k, 1, k, k).to(wdt)
@@ -672,11 +692,7 @@ class RfFrontFn(torch.autograd.Function):
         extra = None
         if dgap is not None:
             extra = (dgap.float() * (1.0 / (h * w))).reshape(n, c).contiguous()
-        dx = ll.empty_cl(n, c, h, w, device=x.device) if ctx.needs_input_grad[0] else None
-        dwgk = zeros_f32(wgk.numel(), wgk.device).view(wgk.shape) if ctx.needs_input_grad[1] else None
-        scr = ll.rf_wgrad_scratch(c, k, x.device) if dwgk is not None else None
-        ll.call("ly_rf_generate_bwd", dz, x, ll.pixel_ld(x), n, h, w, c, k, s, ho, wo, wgk, extra, dx, c, dwgk, scr,
-                0 if scr is None else scr.numel())
+        dx, dwgk = _rf_generate_bwd(dz, x, wgk, k, s, ho, wo, extra, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
         dwg = None
         if dwgk is not None:
             dwg = dwgk.permute(2, 0, 1).reshape(c * k * k, 1, k, k).to(wdt)

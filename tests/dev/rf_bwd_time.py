@@ -24,6 +24,13 @@ for (N, C, H, k, s) in ((64, 128, 80, 3, 2), (64, 256, 40, 3, 2), (64, 160, 20, 
     a = t(lambda: ll.call("ly_rf_generate_bwd", dz, x, C, N, H, H, C, k, s, ho, wo, wgk, None, dx, C, None, None, 0))
     b = t(lambda: ll.call("ly_rf_generate_bwd", dz, x, C, N, H, H, C, k, s, ho, wo, wgk, None, None, C, dw, scr, scr.numel()))
     print(f"C={C} {H}x{H} k={k} s={s}: dx {a:7.1f} us   wgrad {b:7.1f} us   (dZ {dz.numel()*2/1e6:.0f} MB)")
+    if k == 3:
+        wct = torch.randn(C // 16, 1296, device="cuda").bfloat16()
+        zero = torch.zeros(C // 16, 144, dtype=torch.int32, device="cuda")
+        r = torch.empty_like(dz, memory_format=torch.channels_last)
+        c1 = t(lambda: ll.call("ly_rf_tc_taps", dz, N, ho, wo, C, wct, zero, r))
+        c2 = t(lambda: ll.call("ly_rf_col2im", r, N, H, H, C, s, ho, wo, None, dx, C))
+        print(f"   tensor-core dx: taps {c1:6.1f} us + col2im {c2:6.1f} us")
 
 print("forward / gating pieces")
 for (N, C, H, k, s) in ((64, 128, 80, 3, 2), (64, 256, 40, 3, 2), (64, 160, 20, 1, 1), (64, 256, 40, 1, 1)):
