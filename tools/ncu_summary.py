@@ -2,7 +2,7 @@
 """Summarise ncu CSV output for profiles/: per-kernel share of one forward step from a launch list
 (--metrics gpu__time_duration.sum), and DRAM traffic / utilisation per launch from a --set full raw page.
 
-  python tools/ncu_summary.py launches <launches.csv> [anchor-kernel-substring]
+  python tools/ncu_summary.py launches <launches.csv> [anchor-kernel-substring [kernel the segment must contain]]
   python tools/ncu_summary.py raw <raw.csv>
 """
 import collections
@@ -11,7 +11,7 @@ import re
 import sys
 
 
-def launches(path, anchor="stem_"):
+def launches(path, anchor="stem_", must=None):
     rows = []
     with open(path) as f:
         lines = [l for l in f if not l.startswith("==")]
@@ -19,8 +19,14 @@ def launches(path, anchor="stem_"):
         if row.get("Metric Name") == "gpu__time_duration.sum":
             rows.append((row["Kernel Name"], row["Grid Size"], row["Block Size"],
                          float(row["Metric Value"].replace(",", ""))))
+    rows = [r for r in rows if "spin_kernel" not in r[0]]     # bench.py's clock-sampling keep-busy kernel
     idx = [i for i, r in enumerate(rows) if anchor in r[0]]
     seg = rows[idx[-2]:idx[-1]] if len(idx) >= 2 else rows
+    if must is not None:     # the last anchor-to-anchor segment that contains a kernel named `must`
+        for a, b in reversed(list(zip(idx[:-1], idx[1:]))):
+            if any(must in r[0] for r in rows[a:b]):
+                seg = rows[a:b]
+                break
     tot = sum(r[3] for r in seg)
     print(f"# one forward step (between the last two '{anchor}' launches): {len(seg)} kernels, "
           f"{tot / 1e3:.1f} us serialised, cold cache (compare SHARES, not absolutes)")
@@ -89,6 +95,6 @@ def raw(path):
 
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
-        launches(sys.argv[2], *(sys.argv[3:4]))
+        launches(sys.argv[2], *(sys.argv[3:5]))
     else:
         raw(sys.argv[2])
