@@ -46,7 +46,10 @@ __device__ __forceinline__ bool iou_over(const Box& a, const Box& b, float thr) 
   return inter / (sa + sb - inter) > thr;
 }
 
-// one block per image; dynamic shared memory: keys [cap2] (8 B) | boxes [cap2] (16 B) | removed bitmap [cap2/32]
+// one block per image; dynamic shared memory: keys [cap2] (8 B) | boxes [cap2] (16 B) | class [cap2] (2 B) | removed
+// bitmap [cap2/32].  The boxes are stored WITH their class offset; the serial keep loop (one thread) reads only shared
+// memory — when it re-read the prediction rows from global memory, its ~40 dependent round trips per image were most
+// of the kernel's 58 us.
 __global__ void __launch_bounds__(1024) nms_select_kernel(const float* __restrict__ pred, int rows, int no,
                                                           const unsigned long long* __restrict__ keys,
                                                           const int* __restrict__ ncand, int cap, int cap2,
@@ -56,7 +59,9 @@ __global__ void __launch_bounds__(1024) nms_select_kernel(const float* __restric
   extern __shared__ __align__(16) unsigned char smraw[];
   unsigned long long* sk = reinterpret_cast<unsigned long long*>(smraw);
   Box* sb = reinterpret_cast<Box*>(smraw + (size_t)cap2 * 8);
-  unsigned* removed = reinterpret_cast<unsigned*>(smraw + (size_t)cap2 * 24);
+  unsigned short* scls = reinterpret_cast<unsigned short*>(smraw + (size_t)cap2 * 24);
+  unsigned* removed = reinterpret_cast<unsigned*>(smraw + (size_t)cap2 * 26);
+  short* keep_idx = reinterpret_cast<short*>(smraw + (size_t)cap2 * 26 + (size_t)cap2 / 8 + 16);   // [max_det]
   __shared__ unsigned long long cm[64];
   __shared__ unsigned long long keepmask;
   __shared__ int nkept;
@@ -99,6 +104,7 @@ __global__ void __launch_bounds__(1024) nms_select_kernel(const float* __restric
     const float off = (float)cls * max_wh;
     const float hw = p[2] / 2, hh = p[3] / 2;
     sb[i] = Box{p[0] - hw + off, p[1] - hh + off, p[0] + hw + off, p[1] + hh + off};
+    scls[i] = (unsigned short)cls;
   }
   __syncthreads();
   for (int c0 = 0; c0 < n; c0 += 64) {
@@ -122,18 +128,7 @@ __global__ void __launch_bounds__(1024) nms_select_kernel(const float* __restric
         if (!((rem >> i) & 1ull)) {
           km |= 1ull << i;
           rem |= cm[i];
-          float* o = det + ((long)img * max_det + kept) * 6;
-          const unsigned long long key = sk[c0 + i];
-          const unsigned r = 0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull);
-          const float* p = pimg + (long)r * no;
-          int cls = 0;
-          float best = p[5];
-          for (int c = 1; c < no - 5; ++c)
-            if (p[5 + c] > best) { best = p[5 + c]; cls = c; }
-          const float hw = p[2] / 2, hh = p[3] / 2;
-          o[0] = p[0] - hw; o[1] = p[1] - hh; o[2] = p[0] + hw; o[3] = p[1] + hh;
-          o[4] = __uint_as_float((unsigned)(key >> 32));
-          o[5] = (float)cls;
+          keep_idx[kept] = (short)(c0 + i);   // written out by the whole block after the loop
           ++kept;
         }
       }
@@ -160,6 +155,20 @@ __global__ void __launch_bounds__(1024) nms_select_kernel(const float* __restric
     }
     __syncthreads();
   }
+  __syncthreads();
+  // the kept boxes, in rank order: one thread each (the un-shifted coordinates come from the prediction row again,
+  // bit for bit what the reference returns)
+  for (int k = tid; k < nkept; k += nth) {
+    const int idx = keep_idx[k];
+    const unsigned long long key = sk[idx];
+    const unsigned r = 0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull);
+    const float* p = pimg + (long)r * no;
+    const float hw = p[2] / 2, hh = p[3] / 2;
+    float* o = det + ((long)img * max_det + k) * 6;
+    o[0] = p[0] - hw; o[1] = p[1] - hh; o[2] = p[0] + hw; o[3] = p[1] + hh;
+    o[4] = __uint_as_float((unsigned)(key >> 32));
+    o[5] = (float)scls[idx];
+  }
   if (tid == 0) det_count[img] = nkept;
 }
 
@@ -181,7 +190,9 @@ extern "C" int ly_detect_nms(const float* pred, int bs, int rows, int no, float 
              "ly_detect_nms: max_candidates=%d must be in [64, 8192] (shared-memory sort)", max_candidates);
   int cap2 = 64;
   while (cap2 < max_candidates) cap2 <<= 1;
-  const size_t smem = (size_t)cap2 * 24 + (size_t)cap2 / 8 + 16;
+  LY_REQUIRE(max_det <= 4096, "ly_detect_nms: max_det=%d exceeds 4096", max_det);
+  LY_REQUIRE(no - 5 <= 65535, "ly_detect_nms: too many classes");
+  const size_t smem = (size_t)cap2 * 26 + (size_t)cap2 / 8 + 16 + (size_t)max_det * 2 + 16;
   static std::atomic<size_t> attr_set[64];
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
