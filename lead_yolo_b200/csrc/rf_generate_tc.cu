@@ -399,6 +399,147 @@ __global__ void __launch_bounds__(kRtThreads, 1) rf_tc_kernel(const __grid_const
 }
 
 // ------------------------------------------------------------------------------------------------------------------
+// Weight gradient of the receptive-field generation (k = 3) on the tensor cores:
+//     dW[t][ij][c] = Σ_pixels dZ[m][t][c] * x_tap_ij[m][c]
+// Per 16-channel group this is the DIAGONAL (c == c') of D[(t,c)][(ij,c')] = dZ_gᵀ · Xtaps_g, a 144 x 144 product whose
+// contraction runs over pixels — both operands are "MN-major" for the tensor core, and the nine SW32 boxes of a pixel
+// tile ([128 pixels][16 channels], exactly what the forward loads) laid side by side ARE the canonical MN-major operand:
+// 16-element atoms 4096 B apart (LBO), 8-pixel groups 256 B apart (SBO).  One CTA owns (group, slice of the pixel
+// tiles), accumulates every tile into the same two TMEM accumulators (t = 0..7 → rows 0..127; t = 8 → rows 0..15 of the
+// second) — 16 MMAs per tile — and writes its 81 x 16 diagonal values as one row segment of parts[slice][81*C];
+// rf_wgrad_finalize adds the slices in order (bit-reproducible).  15/16 of the MMA work is off-diagonal waste and still
+// a fraction of what the loads cost; the CUDA-core kernel spent 473 us on L17 reading the same 340 MB.
+// ------------------------------------------------------------------------------------------------------------------
+struct alignas(64) RfWgParams {
+  CUtensorMap dz_map;   // dZ as (C, wo, 9, ho, N), box (16, Wt, 1, Ht, 1), SW32
+  CUtensorMap x_map[4]; // as RfTcParams::a_map
+  int tiles_w, tiles_h, n_img, groups, Wt, Ht, s, C;
+  int tiles, slices;
+  float* parts;         // [slices][81 * C]
+};
+constexpr int kWgStages = 2;
+constexpr int kWgStage = 18 * kRtA;   // nine dZ slices + nine input taps of one pixel tile
+constexpr int kWgThreads = 192;
+
+__host__ __device__ constexpr uint64_t rt_desc_sw32_mn(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
+         ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46) | (6ull << 61);
+}
+
+__global__ void __launch_bounds__(kWgThreads, 1) rf_wgrad_tc_kernel(const __grid_constant__ RfWgParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[kWgStages], empty_bar[kWgStages], tfull;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.dz_map);
+    tma_prefetch_desc(&p.x_map[0]);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kWgStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&tfull, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(&tmem_base_s, 512);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  pdl_trigger();
+  pdl_wait();
+  const uint32_t tmem = tmem_base_s;
+
+  const int g = (int)blockIdx.x % p.groups, sl = (int)blockIdx.x / p.groups;
+  const int t_begin = (int)((long)p.tiles * sl / p.slices), t_end = (int)((long)p.tiles * (sl + 1) / p.slices);
+  const int mine = t_end - t_begin;
+  const int tiles_img = p.tiles_w * p.tiles_h;
+  const uint32_t a_bytes = (uint32_t)(16 * p.Wt * p.Ht * 2);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t s = 0, ph = 1;
+      for (int i = 0; i < mine; ++i) {
+        const int mt = t_begin + i;
+        const int n = mt / tiles_img, tr = mt - n * tiles_img, th = tr / p.tiles_w, tw = tr - th * p.tiles_w;
+        const int c0 = g * 16, row0 = th * p.Ht, col0 = tw * p.Wt;
+        mbar_wait(&empty_bar[s], ph);
+        mbar_arrive_expect_tx(&full_bar[s], 18u * a_bytes);
+        uint8_t* st = smem + s * kWgStage;
+        for (int t = 0; t < 9; ++t) tma_load_5d(st + t * kRtA, &p.dz_map, &full_bar[s], c0, col0, t, row0, n);
+        uint8_t* sx = st + 9 * kRtA;
+        for (int ti = 0; ti < 3; ++ti) {
+          uint8_t* dst = sx + ti * 3 * kRtA;
+          if (p.s == 2) {   // as the forward: input row 2h + ti - 1 lives in parity plane (ti + 1) & 1
+            const int row = row0 - (ti == 0);
+            const CUtensorMap* m0 = &p.x_map[((ti + 1) & 1) * 2];
+            tma_load_5d(dst, m0 + 1, &full_bar[s], c0, col0 - 1, 0, row, n);
+            tma_load_5d(dst + kRtA, m0, &full_bar[s], c0, col0, 0, row, n);
+            tma_load_5d(dst + 2 * kRtA, m0 + 1, &full_bar[s], c0, col0, 0, row, n);
+          } else {
+            const int row = row0 + ti - 1;
+            tma_load_5d(dst, &p.x_map[0], &full_bar[s], c0, col0 - 1, 0, row, n);
+            tma_load_5d(dst + kRtA, &p.x_map[0], &full_bar[s], c0, col0, 0, row, n);
+            tma_load_5d(dst + 2 * kRtA, &p.x_map[0], &full_bar[s], c0, col0 + 1, 0, row, n);
+          }
+        }
+        if (++s == kWgStages) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && mine > 0) {
+      const uint32_t idesc = umma_idesc_bf16_f32(128, 144, 1, 1);
+      uint32_t s = 0, ph = 0;
+      for (int i = 0; i < mine; ++i) {
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after_sync();
+        const uint32_t base = smem_u32(smem + s * kWgStage);
+        for (int k = 0; k < 8; ++k) {   // 16 pixels per MMA
+          const uint64_t a1 = rt_desc_sw32_mn(base + k * 512, kRtA, 256);
+          const uint64_t a2 = rt_desc_sw32_mn(base + 8 * kRtA + k * 512, kRtA, 256);   // t = 8 (+ 7 boxes of don't-care rows)
+          const uint64_t b = rt_desc_sw32_mn(base + 9 * kRtA + k * 512, kRtA, 256);
+          const uint32_t acc = (uint32_t)((i | k) != 0);
+          umma_bf16(tmem, a1, b, idesc, acc);
+          umma_bf16(tmem + 256u, a2, b, idesc, acc);
+        }
+        umma_commit(&empty_bar[s]);
+        if (++s == kWgStages) { s = 0; ph ^= 1u; }
+      }
+      umma_commit(&tfull);
+    }
+  } else {
+    const int q = warp & 3;
+    const int r = q * 32 + lane, t = r >> 4, c = r & 15;
+    float* prow = p.parts + (long)sl * 81 * p.C + g * 16 + c;
+    if (mine > 0) {
+      mbar_wait(&tfull, 0);
+      tc_fence_after_sync();
+    }
+    for (int half = 0; half < 2; ++half) {
+      if (half == 1 && q != 0) break;                 // second accumulator: rows 0..15 (t = 8) only
+      for (int ij = 0; ij < 9; ++ij) {
+        uint32_t acc[16];
+        float v = 0.f;
+        if (mine > 0) {
+          tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 256 + ij * 16), acc);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (j == c) v = __uint_as_float(acc[j]);
+        }
+        const int tt = half == 0 ? t : 8;
+        if (half == 0 || lane < 16) prow[(long)(tt * 9 + ij) * p.C] = v;
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+
+// ------------------------------------------------------------------------------------------------------------------
 // FUSED pass 2 (inference): generate -> BN -> ReLU -> SE x spatial-attention gate -> the k x k / stride-k convolution of
 // RFCBAMConv (models/rfa.py:121-129) -> its BatchNorm + ReLU, in ONE kernel.  The gated receptive-field matrix (9*C wide,
 // the largest tensor of the module) never exists in HBM: an item's gated [128 pixels][144] tile is written by the epilogue
@@ -893,6 +1034,69 @@ static int rf_tc_launch_taps(const void* dZ, int N, int ho, int wo, int C, const
   }
   LY_CUDA(launch(rf_tc_kernel<2>, grid, kRtThreads, smem0, stream, p));
   LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+// Launch of rf_wgrad_tc_kernel; `parts` holds at least `max_rows` rows of 81*C floats.  Returns the number of rows (slices)
+// written through *rows_out; the caller adds them in order (rf_wgrad_finalize).
+int rf_wgrad_tc_launch(const void* dZ, const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo,
+                       float* parts, long max_rows, int* rows_out, cudaStream_t stream) {
+  LY_REQUIRE(dZ && x && parts && rows_out, "rf_wgrad_tc: null pointer");
+  LY_REQUIRE(C % 16 == 0 && C > 0 && (s == 1 || s == 2) && ldx % 8 == 0 && ldx >= C, "rf_wgrad_tc: bad C/s/ld");
+  RfWgParams p;
+  memset(&p, 0, sizeof(p));
+  // 128-pixel tiles exactly (the pixel count is the K extent of the MMAs): power-of-two widths; overhang = zero fill
+  int bw = 16;
+  double best = -1;
+  const int cand[5] = {8, 16, 32, 64, 128};
+  for (int i = 0; i < 5; ++i) {
+    const int wt = cand[i], ht = 128 / wt;
+    const double eff = (double)ho * wo / ((double)ceil_div(wo, wt) * ceil_div(ho, ht) * 128.0);
+    if (eff > best + 1e-9) { best = eff; bw = wt; }
+  }
+  const int bh = 128 / bw;
+  p.Wt = bw; p.Ht = bh;
+  p.tiles_w = ceil_div(wo, bw); p.tiles_h = ceil_div(ho, bh); p.n_img = N;
+  p.groups = C / 16; p.s = s; p.C = C;
+  const long tiles = (long)p.tiles_w * p.tiles_h * N;
+  LY_REQUIRE(tiles < (1L << 30), "rf_wgrad_tc: problem too large");
+  p.tiles = (int)tiles;
+  long slices = device_sm_count() / p.groups;
+  if (slices < 1) slices = 1;
+  if (slices > tiles) slices = tiles;
+  if (slices > max_rows) slices = max_rows;
+  LY_REQUIRE(slices >= 1, "rf_wgrad_tc: no scratch rows");
+  p.slices = (int)slices;
+  p.parts = parts;
+  uint32_t es[5] = {1, 1, 1, 1, 1};
+  {
+    uint64_t dims[5] = {(uint64_t)C, (uint64_t)wo, 9, (uint64_t)ho, (uint64_t)N};
+    uint64_t str[4] = {(uint64_t)9 * C * 2, (uint64_t)C * 2, (uint64_t)wo * 9 * C * 2, (uint64_t)ho * wo * 9 * C * 2};
+    uint32_t box[5] = {16, (uint32_t)bw, 1, (uint32_t)bh, 1};
+    int rc = rt_encode(&p.dz_map, dZ, 5, dims, str, box, es);
+    if (rc) return rc;
+  }
+  for (int par = 0; par < (s == 2 ? 4 : 1); ++par) {
+    const int ph = par >> 1, pw = par & 1;
+    const uint64_t Hp = (uint64_t)(H - ph + s - 1) / s, Wp = (uint64_t)(W - pw + s - 1) / s;
+    if (Hp == 0 || Wp == 0) { memcpy(&p.x_map[par], &p.x_map[0], sizeof(CUtensorMap)); continue; }
+    uint64_t dims[5] = {(uint64_t)C, Wp, 1, Hp, (uint64_t)N};
+    uint64_t str[4] = {(uint64_t)s * ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)s * W * ldx * 2, (uint64_t)H * W * ldx * 2};
+    uint32_t box[5] = {16, (uint32_t)bw, 1, (uint32_t)bh, 1};
+    int rc = rt_encode(&p.x_map[par], (const __nv_bfloat16*)x + ((long)ph * W + pw) * ldx, 5, dims, str, box, es);
+    if (rc) return rc;
+  }
+  const size_t smem = (size_t)kWgStages * kWgStage + 1024;
+  static std::atomic<bool> attr_done[64];
+  int dev = 0;
+  LY_CUDA(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63].load()) {
+    LY_CUDA(cudaFuncSetAttribute(rf_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_done[dev & 63].store(true);
+  }
+  LY_CUDA(launch(rf_wgrad_tc_kernel, dim3((unsigned)(slices * p.groups)), dim3(kWgThreads), smem, stream, p));
+  LY_LAUNCH_CHECK();
+  *rows_out = (int)slices;
   return LY_OK;
 }
 

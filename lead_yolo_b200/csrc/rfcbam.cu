@@ -7,6 +7,8 @@
 //   maps   : fp32 [N][h*k][w*k][2]  (0: max over c, 1: mean over c), argmax int16 [N][h*k][w*k]
 //   att    : fp32 [N][h*k][w*k]
 //   wgk    : fp32 [k*k (t)][k*k (i*k+j)][C]  (generate.0.weight[c*k*k+t, 0, i, j])
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "ly_common.cuh"
@@ -613,6 +615,9 @@ __global__ void __launch_bounds__(256) rf_wgrad_finalize_kernel(const float* __r
   if (lane == 0) dwgk[o] += a;
 }
 
+int rf_wgrad_tc_launch(const void* dZ, const void* x, long ldx, int N, int H, int W, int C, int s, int ho, int wo,
+                       float* parts, long max_rows, int* rows_out, cudaStream_t stream);   // rf_generate_tc.cu
+
 struct RfGeo {
   int N, H, W, C, K, s, ho, wo;
 };
@@ -780,6 +785,16 @@ extern "C" int ly_rf_generate_bwd(const void* dZ, const void* x, long ldx, int N
     const long work = (long)V * KK * k;
     const long outs = (long)KK * KK * C;
     cudaStream_t stream = (cudaStream_t)st;
+    static const bool wgrad_cuda = getenv("LY_RF_WGRAD_CUDA") != nullptr;   // dev knob: the CUDA-core kernel
+    if (k == 3 && C % 16 == 0 && wscratch != nullptr && wscratch_floats >= outs && !wgrad_cuda) {
+      // tensor cores: per-slice partial rows, then the ordered sum
+      int rows = 0;
+      rc = rf_wgrad_tc_launch(dZ, x, ldx, N, H, W, C, s, ho, wo, wscratch, wscratch_floats / outs, &rows, stream);
+      if (rc) return rc;
+      LY_CUDA(launch(rf_wgrad_finalize_kernel, ceil_div(outs * 32, 256), 256, 0, stream, wscratch, rows, outs, dwgk));
+      LY_LAUNCH_CHECK();
+      return LY_OK;
+    }
     // pixel lanes: three 288-thread blocks per SM, every lane a row of `parts`
     long lanes = ((long)device_sm_count() * 3 * 288) / work;
     if (lanes > M) lanes = M;

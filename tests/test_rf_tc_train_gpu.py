@@ -1,6 +1,7 @@
 """Tensor-core training kernels against their CUDA-core counterparts at RAGGED sizes (tiles overhanging the image, odd
 H / W): the receptive-field generation (ly_rf_tc_generate vs ly_rf_generate), its input gradient (ly_rf_tc_taps +
-ly_rf_col2im vs the dx half of ly_rf_generate_bwd) and the stem's weight gradient (ly_stem_im2col + ly_conv_wgrad vs
+ly_rf_col2im vs the dx half of ly_rf_generate_bwd), its weight gradient (rf_wgrad_tc_kernel vs rf_generate_wgrad_kernel)
+and the stem's weight gradient (ly_stem_im2col + ly_conv_wgrad vs
 ly_stem_wgrad).  The CUDA-core kernels are themselves held to the oracle by the module tests (tests/test_modules_gpu.py);
 weights are pre-rounded to bf16 here so that both sides multiply the same numbers."""
 import pytest
@@ -40,6 +41,14 @@ def test_rf_generate_tc_matches_cuda_cores(case):
     ll.call("ly_rf_generate_bwd", dz, x, c, n, h, w, c, 3, s, ho, wo, wgk, extra, dx_cc, c, None, None, 0)
     # the tensor-core path rounds the nine patch gradients to bf16 before folding up to four of them
     assert rel_l2(dx_tc.float(), dx_cc.float()) < 6e-3
+
+    # weight gradient: tensor cores (scratch rows given) against the CUDA-core kernel (no scratch: atomics)
+    dw_tc = torch.zeros_like(wgk)
+    scr = ll.rf_wgrad_scratch(c, 3, "cuda")
+    ll.call("ly_rf_generate_bwd", dz, x, c, n, h, w, c, 3, s, ho, wo, wgk, None, None, c, dw_tc, scr, scr.numel())
+    dw_cc = torch.zeros_like(wgk)
+    ll.call("ly_rf_generate_bwd", dz, x, c, n, h, w, c, 3, s, ho, wo, wgk, None, None, c, dw_cc, None, 0)
+    assert rel_l2(dw_tc, dw_cc) < 1e-4
 
 
 @pytest.mark.parametrize("u8", [True, False])
