@@ -143,6 +143,20 @@ int ly_pack_weight_dgrad(const float* w, int Cout, int Cin, int kh, int kw, int 
                          ly_stream_t stream);
 int ly_unpack_wgrad(const float* dwp, int Cout, int kh, int kw, int patch, int c0, int c1, int c2, int c3, float* dw,
                     int accumulate, ly_stream_t stream);
+/* ly_pack_weight / ly_pack_weight_dgrad for MANY weights in one launch (a captured training step packs every parameter
+ * once per replay).  jobs: DEVICE array; kind 0 = forward layout (c = source split, Kp = packed K), kind 1 = input-gradient
+ * layout (coff, cs, P = pad64 of the 8-aligned Cout); total = elements of dst; first_block = prefix sum of
+ * ceil(total / 256) over the jobs before this one; total_blocks = that sum over all jobs. */
+typedef struct ly_pack_job {
+  const void* w;     /* fp32 OIHW parameter */
+  void* dst;         /* bf16 packed matrix */
+  int kind, Cout, Cin, kh, kw, patch;
+  int c[4];
+  int coff, cs, P, Kp;
+  long total;
+  long first_block;
+} ly_pack_job;
+int ly_pack_batch(const ly_pack_job* jobs, int njobs, long total_blocks, ly_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
  * Stem: PatchEmbed_FasterNet.proj on the raw image (models/common.py:1531,1537): 4x4/s4 conv, 3 -> Cout,

@@ -69,6 +69,17 @@ def ptr(t) -> C.c_void_p | None:
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
+class PackJob(C.Structure):
+    """ly_pack_job of include/leadyolo.h."""
+    _fields_ = [
+        ("w", C.c_void_p), ("dst", C.c_void_p),
+        ("kind", C.c_int), ("Cout", C.c_int), ("Cin", C.c_int), ("kh", C.c_int), ("kw", C.c_int), ("patch", C.c_int),
+        ("c", C.c_int * 4),
+        ("coff", C.c_int), ("cs", C.c_int), ("P", C.c_int), ("Kp", C.c_int),
+        ("total", C.c_long), ("first_block", C.c_long),
+    ]
+
+
 class LossDesc(C.Structure):
     """ly_loss_desc of include/leadyolo.h."""
     _fields_ = [

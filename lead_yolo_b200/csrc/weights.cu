@@ -33,11 +33,8 @@ __device__ __forceinline__ int packed_col(const SrcSplit& sp, int kh, int kw, in
 }
 
 // forward pack: wp[o][Kp] bf16 <- w[o][ci][ky][kx]; one thread per packed element (zero padding included)
-__global__ void pack_fwd_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw, int patch, SrcSplit sp,
-                                int Kp, __nv_bfloat16* __restrict__ wp) {
-  pdl_enter();
-  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (long)Cout * Kp) return;
+__device__ __forceinline__ void pack_fwd_elem(const float* __restrict__ w, int Cin, int kh, int kw, int patch,
+                                              const SrcSplit& sp, int Kp, __nv_bfloat16* __restrict__ wp, long i) {
   const int o = (int)(i / Kp);
   int col = (int)(i % Kp);
   float val = 0.f;
@@ -61,16 +58,20 @@ __global__ void pack_fwd_kernel(const float* __restrict__ w, int Cout, int Cin, 
   wp[i] = __float2bfloat16(val);
 }
 
+__global__ void pack_fwd_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw, int patch, SrcSplit sp,
+                                int Kp, __nv_bfloat16* __restrict__ wp) {
+  pdl_enter();
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long)Cout * Kp) return;
+  pack_fwd_elem(w, Cin, kh, kw, patch, sp, Kp, wp, i);
+}
+
 // input-gradient weights of source channels [coff, coff+cs):
 //   stride-1 conv: rows ci (cs of them), K = taps x pad64(cpad): wd[ci][t*P + co] = w[co][coff+ci][kh-1-ty][kw-1-tx]
 //   patch conv   : rows (ky, kx, c) (kh*kw*cs), K = pad64(cpad):  wd[(ky*kw+kx)*cs + c][co] = w[co][coff+c][ky][kx]
-__global__ void pack_dgrad_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw, int patch, int coff,
-                                  int cs, int P, __nv_bfloat16* __restrict__ wd) {
-  pdl_enter();
-  const int rows = patch ? kh * kw * cs : cs;
+__device__ __forceinline__ void pack_dgrad_elem(const float* __restrict__ w, int Cout, int Cin, int kh, int kw, int patch,
+                                                int coff, int cs, int P, __nv_bfloat16* __restrict__ wd, long i) {
   const int Kp = patch ? P : kh * kw * P;
-  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (long)rows * Kp) return;
   const int r = (int)(i / Kp), col = (int)(i % Kp);
   float val = 0.f;
   if (patch) {
@@ -87,6 +88,44 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ w, int Cout, int Cin
     }
   }
   wd[i] = __float2bfloat16(val);
+}
+
+__global__ void pack_dgrad_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw, int patch, int coff,
+                                  int cs, int P, __nv_bfloat16* __restrict__ wd) {
+  pdl_enter();
+  const int rows = patch ? kh * kw * cs : cs;
+  const int Kp = patch ? P : kh * kw * P;
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long)rows * Kp) return;
+  pack_dgrad_elem(w, Cout, Cin, kh, kw, patch, coff, cs, P, wd, i);
+}
+
+// Every parameter of a training step in every packed layout it is needed in, ONE launch: jobs[j] describes one
+// (weight, layout) pair and owns the blocks [first_block, first_block of the next job).  A captured training step packs
+// ~150 weights; as separate launches they cost ~3.5 us each on the replay's critical path.
+__global__ void __launch_bounds__(256) pack_batch_kernel(const ly_pack_job* __restrict__ jobs, int njobs) {
+  pdl_enter();
+  int lo = 0, hi = njobs - 1;
+  const long b = blockIdx.x;
+  while (lo < hi) {   // last job whose first block is <= b
+    const int mid = (lo + hi + 1) >> 1;
+    if (jobs[mid].first_block <= b) lo = mid;
+    else hi = mid - 1;
+  }
+  const ly_pack_job& j = jobs[lo];
+  const long i = (b - j.first_block) * 256 + threadIdx.x;
+  if (i >= j.total) return;
+  if (j.kind == 0) {
+    SrcSplit sp;
+    sp.n = 0;
+    for (int s = 0; s < 4; ++s) {
+      sp.c[s] = j.c[s];
+      if (j.c[s] > 0) sp.n = s + 1;
+    }
+    pack_fwd_elem((const float*)j.w, j.Cin, j.kh, j.kw, j.patch, sp, j.Kp, (__nv_bfloat16*)j.dst, i);
+  } else {
+    pack_dgrad_elem((const float*)j.w, j.Cout, j.Cin, j.kh, j.kw, j.patch, j.coff, j.cs, j.P, (__nv_bfloat16*)j.dst, i);
+  }
 }
 
 // weight gradient back to OIHW: dw[o][ci][ky][kx] (+)= dwp[o][packed_col]
@@ -167,6 +206,13 @@ extern "C" int ly_unpack_wgrad(const float* dwp, int Cout, int kh, int kw, int p
   const long total = (long)Cout * cin * kh * kw;
   LY_CUDA(launch(unpack_wgrad_kernel, ceil_div(total, 256), 256, 0, (cudaStream_t)st, dwp, Cout, cin, kh, kw, patch, sp, Kp, dw,
                                                                            accumulate));
+  LY_LAUNCH_CHECK();
+  return LY_OK;
+}
+
+extern "C" int ly_pack_batch(const ly_pack_job* jobs, int njobs, long total_blocks, ly_stream_t st) {
+  LY_REQUIRE(jobs != nullptr && njobs > 0 && total_blocks > 0 && total_blocks < (1L << 31), "ly_pack_batch: bad arguments");
+  LY_CUDA(launch(pack_batch_kernel, dim3((unsigned)total_blocks), 256, 0, (cudaStream_t)st, jobs, njobs));
   LY_LAUNCH_CHECK();
   return LY_OK;
 }

@@ -155,6 +155,7 @@ _SIGS = {
     "ly_pack_weight": "piiiiiiiip",
     "ly_pack_weight_dgrad": "piiiiiiip",
     "ly_unpack_wgrad": "piiiiiiiipi",
+    "ly_pack_batch": "pil",
     "ly_sq_sum": "plp",
     "ly_sgd_ema_step": "pppplllpp",
     "ly_ema_update": "pplp",

@@ -131,17 +131,42 @@ def _w32(weight):
     return w if (w.dtype == torch.float32 and w.is_contiguous()) else w.float().contiguous()
 
 
+# Batched weight packing (train.TrainEngine).  While PACK_RECORD is a list, every pack of a leaf fp32 parameter of the
+# running step is remembered as (key, packed tensor, job fields); the engine turns the list into ONE ly_pack_batch launch at
+# the start of its captured step and sets PACK_PLAN = {key: packed tensor}: the Functions then find their operand ready.
+PACK_RECORD = None
+PACK_PLAN = None
+
+
+def _pack_key(kind, weight, *geom):
+    return (kind, weight.data_ptr()) + tuple(geom)
+
+
+def _plannable(weight):
+    return weight.grad_fn is None and weight.is_leaf and weight.dtype == torch.float32 and weight.is_contiguous() and \
+        weight.data_ptr() in GRAD_SINK
+
+
 def packed_weight(weight, chans, k, patch):
     """bf16 [Cout][Kp] forward operand of `weight` for K-concatenated sources `chans`: one kernel launch, memoised on
     the parameter's version (training: once per optimiser step; inference: once)."""
     chans = tuple(int(c) for c in chans)
+    key = None
+    if (PACK_PLAN is not None or PACK_RECORD is not None) and _plannable(weight):
+        key = _pack_key("f", weight, chans, k, patch)
+        if PACK_PLAN is not None and key in PACK_PLAN:
+            return PACK_PLAN[key]
 
     def build():
         cout = weight.shape[0]
         from .packing import packed_k
-        wp = torch.empty((cout, packed_k(list(chans), k, k, patch)), dtype=BF16, device=weight.device)
+        kp = packed_k(list(chans), k, k, patch)
+        wp = torch.empty((cout, kp), dtype=BF16, device=weight.device)
         c4 = list(chans) + [0] * (4 - len(chans))
         ll.call("ly_pack_weight", _w32(weight), cout, k, k, 1 if patch else 0, c4[0], c4[1], c4[2], c4[3], wp)
+        if key is not None and PACK_RECORD is not None:
+            PACK_RECORD.append((key, wp, dict(kind=0, w=weight.data_ptr(), Cout=cout, Cin=sum(chans), kh=k, kw=k,
+                                              patch=1 if patch else 0, c=c4, coff=0, cs=0, P=0, Kp=kp, total=cout * kp)))
         return wp
 
     if weight.grad_fn is not None:          # derived tensor (e.g. a masked / permuted view): nothing stable to key on
@@ -151,16 +176,51 @@ def packed_weight(weight, chans, k, patch):
 
 def packed_weight_dgrad(weight, cout, cin, k, patch, coff, cs):
     """bf16 weights of the GEMM that maps dZ to the gradient of source channels [coff, coff+cs) (one launch)."""
+    key = None
+    if (PACK_PLAN is not None or PACK_RECORD is not None) and _plannable(weight):
+        key = _pack_key("d", weight, cout, cin, k, patch, coff, cs)
+        if PACK_PLAN is not None and key in PACK_PLAN:
+            return PACK_PLAN[key]
+
     def build():
         p64 = ((cout + 7) // 8 * 8 + 63) // 64 * 64
         rows, kp = (k * k * cs, p64) if patch else (cs, k * k * p64)
         wd = torch.empty((rows, kp), dtype=BF16, device=weight.device)
         ll.call("ly_pack_weight_dgrad", _w32(weight), cout, cin, k, k, 1 if patch else 0, coff, cs, wd)
+        if key is not None and PACK_RECORD is not None:
+            PACK_RECORD.append((key, wd, dict(kind=1, w=weight.data_ptr(), Cout=cout, Cin=cin, kh=k, kw=k,
+                                              patch=1 if patch else 0, c=[0, 0, 0, 0], coff=coff, cs=cs, P=p64, Kp=kp,
+                                              total=rows * kp)))
         return wd
 
     if weight.grad_fn is not None:
         return build()
     return cached([weight], ("pwd", k, patch, coff, cs), build)
+
+
+def pack_batch_table(records, device):
+    """(device table, n jobs, total blocks, plan dict) for ly_pack_batch from PACK_RECORD entries (first of each key)."""
+    import ctypes as C
+    from ._lib import PackJob
+    seen, jobs = {}, []
+    for key, buf, f in records:
+        if key not in seen:
+            seen[key] = buf
+            jobs.append((buf, f))
+    arr = (PackJob * len(jobs))()
+    blocks = 0
+    for i, (buf, f) in enumerate(jobs):
+        j = arr[i]
+        j.w, j.dst = f["w"], buf.data_ptr()
+        j.kind, j.Cout, j.Cin, j.kh, j.kw, j.patch = f["kind"], f["Cout"], f["Cin"], f["kh"], f["kw"], f["patch"]
+        for q in range(4):
+            j.c[q] = f["c"][q]
+        j.coff, j.cs, j.P, j.Kp = f["coff"], f["cs"], f["P"], f["Kp"]
+        j.total, j.first_block = f["total"], blocks
+        blocks += (f["total"] + 255) // 256
+    raw = bytes(arr)
+    table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(device)
+    return table, len(jobs), blocks, seen
 
 
 class ConvFn(torch.autograd.Function):

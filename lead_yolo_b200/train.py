@@ -134,6 +134,7 @@ class TrainEngine:
         self.images = torch.zeros((batch, 3, img, img), dtype=torch.uint8, device=self.device)
         self.targets = torch.full((self.max_targets, 6), -1.0, dtype=torch.float32, device=self.device)
         self.loss_out = None
+        self._pack = None                 # (device job table, jobs, blocks, {key: packed tensor}) of the captured step
         self.graphs = None
         self.use_graph = graph
         self.launches_per_step = 0
@@ -150,6 +151,9 @@ class TrainEngine:
     def _forward_backward(self):
         ops.arena_begin(self.device)
         self.flat_grad.zero_()            # gradient sinks accumulate (weight-gradient atomics land there directly)
+        if self._pack is not None:        # every parameter in every packed layout of the step: one launch
+            ll.call("ly_pack_batch", self._pack[0], self._pack[1], self._pack[2])
+            ops.PACK_PLAN = self._pack[3]
         ops.BYPASS_PARAM_CACHE = True     # replayed launches must re-derive everything that depends on a parameter
         ops.GRAD_SINK = self._sink
         ops._SINK_USED.clear()
@@ -164,6 +168,7 @@ class TrainEngine:
         finally:
             ops.BYPASS_PARAM_CACHE = False
             ops.GRAD_SINK = {}
+            ops.PACK_PLAN = None
             ops.NBT_EXTERNAL = False
             ops.arena_end()
         # whatever did not go through a sink is copied into its slice
@@ -191,6 +196,15 @@ class TrainEngine:
         with torch.cuda.stream(side):
             for _ in range(3):           # warm-up: caches, arena high-water mark, cuBLAS-free but allocator-heavy
                 self._forward_backward()
+            # one more pass that records which parameter is packed into which layout: the captured step packs them all
+            # with ONE launch (ops.PACK_PLAN) instead of ~150 small ones
+            ops.PACK_RECORD = []
+            try:
+                self._forward_backward()
+            finally:
+                rec, ops.PACK_RECORD = ops.PACK_RECORD, None
+            if rec:
+                self._pack = ops.pack_batch_table(rec, self.device)
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
         g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
