@@ -21,7 +21,7 @@ namespace ly {
 
 constexpr int kWMaxK = 96;
 constexpr int kSlot = 128 * 128;  // one 64-channel x 128-pixel box
-constexpr int kWStages = 2;
+constexpr int kWMaxStages = 8;   // ring depth = 192 KB / stage size: 2 for (2 dZ + 4 activation) boxes, up to 6 for (1 + 1)
 
 struct WEntry {
   int16_t src;
@@ -35,14 +35,15 @@ struct alignas(64) WgradParams {
   int tiles_w, tiles_h, n_img;
   int Wt, Ht, P;  // P = Wt*Ht pixel rows per tile (multiple of 16)
   int num_k, Cout, Kp;
+  int stages, ndz, slots;   // ring depth; dZ boxes per stage (1 when Cout <= 64); boxes per stage = ndz + min(4, num_k)
   float* dw;
   WEntry sched[kWMaxK];
 };
 
 __global__ void __launch_bounds__(192) wgrad_gemm_kernel(const __grid_constant__ WgradParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t full_bar[kWStages];
-  __shared__ uint64_t empty_bar[kWStages];
+  __shared__ uint64_t full_bar[kWMaxStages];
+  __shared__ uint64_t empty_bar[kWMaxStages];
   __shared__ uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_s;
 
@@ -50,7 +51,9 @@ __global__ void __launch_bounds__(192) wgrad_gemm_kernel(const __grid_constant__
   const int lane = threadIdx.x & 31;
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
-  constexpr int kStageBytes = 6 * kSlot;  // 2 dZ boxes + 4 activation boxes
+  // A stage = the dZ boxes + the activation boxes of one pixel tile.  The ring is as deep as 192 KB allow: a tile is a
+  // handful of MMAs, so what bounds a small-K layer is how many tiles' loads are in flight (two stages: ~2 us per tile).
+  const int kStageBytes = p.slots * kSlot;
 
   const int ct = blockIdx.y;   // 128-wide output-channel tile
   const int kg = blockIdx.z;   // group of 4 K chunks
@@ -64,7 +67,7 @@ __global__ void __launch_bounds__(192) wgrad_gemm_kernel(const __grid_constant__
     tma_prefetch_desc(&p.a_map[0]);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kWStages; ++s) {
+    for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
@@ -82,9 +85,9 @@ __global__ void __launch_bounds__(192) wgrad_gemm_kernel(const __grid_constant__
 
   if (my_tiles > 0) {
     if (warp == 0) {
+      int s = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < my_tiles; ++i) {
-        const int s = i % kWStages;
-        const uint32_t ph = (uint32_t)(i / kWStages) & 1u;
         mbar_wait(&empty_bar[s], ph ^ 1u);
         if (lane == 0) {
           const int tile = (int)blockIdx.x + i * (int)gridDim.x;
@@ -93,27 +96,30 @@ __global__ void __launch_bounds__(192) wgrad_gemm_kernel(const __grid_constant__
           const int n = tile / (p.tiles_w * p.tiles_h);
           const int w0 = tw * p.Wt, h0 = th * p.Ht;
           uint8_t* st = smem + s * kStageBytes;
-          mbar_arrive_expect_tx(&full_bar[s], box_bytes * (uint32_t)(2 + nch));
+          mbar_arrive_expect_tx(&full_bar[s], box_bytes * (uint32_t)(p.ndz + nch));
           tma_load_5d(st, &p.dz_map, &full_bar[s], ct * 128, w0, 0, h0, n);
-          tma_load_5d(st + kSlot, &p.dz_map, &full_bar[s], ct * 128 + 64, w0, 0, h0, n);
+          if (p.ndz == 2) tma_load_5d(st + kSlot, &p.dz_map, &full_bar[s], ct * 128 + 64, w0, 0, h0, n);
           for (int c = 0; c < nch; ++c) {
             const WEntry e = p.sched[k_begin + c];
-            tma_load_5d(st + (2 + c) * kSlot, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
+            tma_load_5d(st + (p.ndz + c) * kSlot, &p.a_map[e.src], &full_bar[s], e.c0, w0 + e.dw, e.tz, h0 + e.dh, n);
           }
         }
         __syncwarp();
+        if (++s == p.stages) { s = 0; ph ^= 1u; }
       }
     } else if (warp == 1) {
       const uint32_t idesc = umma_idesc_bf16_f32(128, nch * 64, 1, 1);
       const int ksteps = p.P / 16;
+      int s = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < my_tiles; ++i) {
-        const int s = i % kWStages;
-        const uint32_t ph = (uint32_t)(i / kWStages) & 1u;
         mbar_wait(&full_bar[s], ph);
         tc_fence_after_sync();
         if (lane == 0) {
+          // Cout <= 64: one dZ box; rows 64..127 of the M = 128 operand then run into the first activation box and fill
+          // accumulator rows that are never stored
           const uint32_t a_base = smem_u32(smem + s * kStageBytes);
-          const uint32_t b_base = a_base + 2 * kSlot;
+          const uint32_t b_base = a_base + p.ndz * kSlot;
           for (int k = 0; k < ksteps; ++k) {
             const uint64_t adesc = umma_smem_desc_sw128(a_base + k * 2048, kSlot, 1024);
             const uint64_t bdesc = umma_smem_desc_sw128(b_base + k * 2048, kSlot, 1024);
@@ -123,6 +129,7 @@ __global__ void __launch_bounds__(192) wgrad_gemm_kernel(const __grid_constant__
           if (i == my_tiles - 1) umma_commit(&tmem_full_bar);
         }
         __syncwarp();
+        if (++s == p.stages) { s = 0; ph ^= 1u; }
       }
     } else {
       const int q = warp & 3;
@@ -281,9 +288,13 @@ extern "C" int ly_conv_wgrad(const ly_conv_desc* d, const void* dz, long dz_ld, 
   static std::atomic<bool> done[64];
   int dev = 0;
   LY_CUDA(cudaGetDevice(&dev));
-  const size_t smem_bytes = (size_t)kWStages * 6 * kSlot + 1024;
+  p.ndz = d->Cout > 64 ? 2 : 1;
+  p.slots = p.ndz + (p.num_k < 4 ? p.num_k : 4);
+  p.stages = 12 / p.slots;                      // 12 boxes of 16 KB = 192 KB
+  if (p.stages > kWMaxStages) p.stages = kWMaxStages;
+  const size_t smem_bytes = (size_t)p.stages * p.slots * kSlot + 1024;
   if (!done[dev & 63].load()) {
-    LY_CUDA(cudaFuncSetAttribute(wgrad_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    LY_CUDA(cudaFuncSetAttribute(wgrad_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 12 * kSlot + 1024));
     done[dev & 63].store(true);
   }
   dim3 grid((unsigned)split, (unsigned)cts, (unsigned)kgs);
