@@ -294,6 +294,11 @@ def train_measure(batch, steps, warm, rank, local, world, dev, profile=True, var
     for i in range(warm):
         eng.step(dimg[i % nbuf], tgt[i % nbuf])
     barrier()
+    if os.environ.get("LY_PROFILE_STEP"):     # ncu --profile-from-start off: exactly ONE training step is profiled
+        torch.cuda.profiler.start()
+        eng.step(dimg[0], tgt[0])
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ar = []
     e0.record()
