@@ -226,3 +226,50 @@ def test_training_forward_is_bit_reproducible_and_gradients_agree():
         assert all(torch.equal(a, b) for a, b in zip(raw, outs[0][0]))
         assert torch.equal(loss, outs[0][1])
         assert ((grad - outs[0][2]).norm() / outs[0][2].norm()).item() < 1e-4
+
+
+def test_pack_batch_matches_single_launches():
+    """ly_pack_batch (every weight of a captured training step in one launch) writes exactly what ly_pack_weight /
+    ly_pack_weight_dgrad write one weight at a time: forward layouts with one and several K-concatenated sources, 3x3 and
+    k = stride patch convolutions, input-gradient layouts of channel slices."""
+    from lead_yolo_b200 import lowlevel as ll, ops
+    g = torch.Generator(device="cuda").manual_seed(3)
+    ws = {
+        "a": torch.randn(128, 336, 1, 1, device="cuda", generator=g, requires_grad=True),
+        "b": torch.randn(64, 64, 3, 3, device="cuda", generator=g, requires_grad=True),
+        "c": torch.randn(80, 40, 2, 2, device="cuda", generator=g, requires_grad=True),
+        "d": torch.randn(18, 128, 1, 1, device="cuda", generator=g, requires_grad=True),
+    }
+    calls = [
+        ("f", "a", ([256, 80], 1, False)), ("f", "b", ([64], 3, False)), ("f", "c", ([40], 2, True)), ("f", "d", ([128], 1, False)),
+        ("d", "a", (128, 336, 1, False, 0, 256)), ("d", "a", (128, 336, 1, False, 256, 80)), ("d", "b", (64, 64, 3, False, 0, 64)),
+        ("d", "c", (80, 40, 2, True, 0, 40)), ("d", "d", (18, 128, 1, False, 0, 128)),
+    ]
+
+    def run_all():
+        out = []
+        for kind, name, a in calls:
+            out.append(ops.packed_weight(ws[name], *a) if kind == "f" else ops.packed_weight_dgrad(ws[name], *a))
+        return out
+
+    ops.GRAD_SINK = {w.data_ptr(): w for w in ws.values()}      # marks the weights as parameters of a running step
+    ops.BYPASS_PARAM_CACHE = True
+    ops.PACK_RECORD = []
+    try:
+        single = [t.clone() for t in run_all()]
+        table, njobs, blocks, plan = ops.pack_batch_table(ops.PACK_RECORD, "cuda")
+    finally:
+        ops.PACK_RECORD = None
+    assert njobs == len(calls)
+    for buf in plan.values():
+        buf.fill_(float("nan"))
+    ll.call("ly_pack_batch", table, njobs, blocks)
+    ops.PACK_PLAN = plan
+    try:
+        batched = run_all()
+    finally:
+        ops.PACK_PLAN = None
+        ops.GRAD_SINK = {}
+        ops.BYPASS_PARAM_CACHE = False
+    for s, b in zip(single, batched):
+        assert torch.equal(s.view(torch.int16), b.view(torch.int16))
