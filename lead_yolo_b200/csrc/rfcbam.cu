@@ -479,34 +479,49 @@ __global__ void __launch_bounds__(256) rf_col2im_kernel(const __nv_bfloat16* __r
   const int v = (int)(tid % V);
   const long pix = tid / V;
   const int x = (int)(pix % W), y = (int)((pix / W) % H), n = (int)(pix / ((long)W * H));
-  // (i, j) contributes when y + 1 - i and x + 1 - j are non-negative multiples of S inside the output
-  uint4 u[9];
-  unsigned on = 0u;
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    const int hn = y + 1 - i;
-    const int h = S == 2 ? hn >> 1 : hn;
-    const bool hv = hn >= 0 && (S == 1 || (hn & 1) == 0) && h < ho;
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      const int wn = x + 1 - j;
-      const int w = S == 2 ? wn >> 1 : wn;
-      if (hv && wn >= 0 && (S == 1 || (wn & 1) == 0) && w < wo) {
-        on |= 1u << (i * 3 + j);
-        u[i * 3 + j] = ldg16(R + ((((long)n * ho + h) * wo + w) * 9 + (i * 3 + j)) * (long)C + v * 8);
-      }
-    }
-  }
   float acc[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = extra != nullptr ? __ldg(extra + (long)n * C + v * 8 + e) : 0.f;
+  if (S == 2) {
+    // stride 2: an even coordinate is the centre tap of one output pixel, an odd one the first tap of the next output
+    // pixel and the last tap of the previous — at most 2 x 2 terms, all four loads in flight together
+    int hh[2], ih[2], ww[2], jw[2];
+    bool vh[2], vw[2];
+    if ((y & 1) == 0) { hh[0] = y >> 1; ih[0] = 1; vh[0] = true; hh[1] = 0; ih[1] = 0; vh[1] = false; }
+    else { hh[0] = (y + 1) >> 1; ih[0] = 0; vh[0] = hh[0] < ho; hh[1] = (y - 1) >> 1; ih[1] = 2; vh[1] = true; }
+    if ((x & 1) == 0) { ww[0] = x >> 1; jw[0] = 1; vw[0] = true; ww[1] = 0; jw[1] = 0; vw[1] = false; }
+    else { ww[0] = (x + 1) >> 1; jw[0] = 0; vw[0] = ww[0] < wo; ww[1] = (x - 1) >> 1; jw[1] = 2; vw[1] = true; }
+    uint4 u[4];
 #pragma unroll
-  for (int q = 0; q < 9; ++q) {
-    if (on & (1u << q)) {
-      float f[8];
-      unpack8(u[q], f);
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += f[e];
+      for (int b = 0; b < 2; ++b)
+        if (vh[a] && vw[b])
+          u[a * 2 + b] = ldg16(R + ((((long)n * ho + hh[a]) * wo + ww[b]) * 9 + (ih[a] * 3 + jw[b])) * (long)C + v * 8);
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b)
+        if (vh[a] && vw[b]) {
+          float f[8];
+          unpack8(u[a * 2 + b], f);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[e] += f[e];
+        }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int h = y + 1 - i;
+      if (h < 0 || h >= ho) continue;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int w = x + 1 - j;
+        if (w < 0 || w >= wo) continue;
+        float f[8];
+        unpack8(ldg16(R + ((((long)n * ho + h) * wo + w) * 9 + (i * 3 + j)) * (long)C + v * 8), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] += f[e];
+      }
     }
   }
   *reinterpret_cast<uint4*>(dx + pix * lddx + v * 8) = pack8(acc);
