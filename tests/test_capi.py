@@ -136,3 +136,29 @@ int main() {
     assert r.returncode == 0, r.stderr[-2000:]
     r = subprocess.run([str(exe)], capture_output=True, text=True)
     assert r.returncode == 0 and "MATCH" in r.stdout
+
+
+def test_ctypes_struct_mirrors_match_the_header(tmp_path):
+    """ly_conv_desc / ly_loss_desc / ly_pack_job as gcc lays them out from include/leadyolo.h against the ctypes mirrors in
+    lead_yolo_b200/_lib.py: same size, same offset for every field (an ABI drift here corrupts launches silently)."""
+    from lead_yolo_b200 import _lib
+    pairs = [("ly_conv_desc", _lib.ConvDesc), ("ly_loss_desc", _lib.LossDesc), ("ly_pack_job", _lib.PackJob)]
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "leadyolo.h"', "int main(void) {"]
+    for cname, cls in pairs:
+        lines.append(f'  printf("{cname} size %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'  printf("{cname} {fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ["  return 0;", "}"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout
+    got = {}
+    for ln in out.strip().splitlines():
+        s, f, v = ln.split()
+        got[(s, f)] = int(v)
+    for cname, cls in pairs:
+        assert got[(cname, "size")] == C.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert got[(cname, fname)] == getattr(cls, fname).offset, (cname, fname)
