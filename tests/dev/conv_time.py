@@ -1,5 +1,5 @@
 """Dev: time single convolutions (eval, fused BN+SiLU) — run once per LY_CONV_* knob setting.
-   python tests/dev/conv_pair_time.py            (on a B200)"""
+   python tests/dev/conv_time.py            (on a B200)"""
 import os
 import sys
 
